@@ -1,0 +1,307 @@
+"""CPU oracle for the PPMStereo hot path (TEST INFRASTRUCTURE ONLY).
+
+This module restates, from the math, what the reference computes on the path
+named by BASELINE.json's north_star: correlation pyramid build, radius-r
+lookup, and the Pick-and-Play Memory (PPM) read.  It is NOT part of the
+product: only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s
+``cpu_baseline`` / ``--impl reference`` legs may import it.  The product
+(``ppmstereo_b200``) never imports this file and has no CPU fallback.
+
+Parity pinning: the reference ships no tests or golden vectors,
+so this oracle is pinned against outputs of the reference itself, imported
+unmodified from /root/reference in the build container by
+``tests/golden/make_golden.py``; the resulting fixtures live in
+``tests/golden/*.npz`` and ``tests/test_oracle_golden.py`` checks every
+function below against them.  The attention arithmetic of the reference lives
+in the un-vendored, un-pinned third-party ``flash_attn`` package
+(reference models/core/ppmstereo.py:38-41, call site :550); its published
+algorithm (softmax(scale * Q K^T) V with bf16 operands, fp32 softmax,
+P rounded to bf16 before P.V, bf16 output) is restated in
+``attention_bf16``; for that one function parity is "unpinned" by reference
+tests and is anchored on the reference's own call site instead.
+
+Every function cites the reference file:line it follows (paths relative to
+/root/reference).  All math is fp32 on CPU unless a bf16 rounding is stated.
+"""
+from __future__ import annotations
+
+import math
+from typing import List, Optional, Sequence, Tuple
+
+import torch
+
+# --------------------------------------------------------------------------
+# helpers
+# --------------------------------------------------------------------------
+
+def bf16_round(x: torch.Tensor) -> torch.Tensor:
+    """Round-to-nearest-even to bfloat16 and come back to fp32."""
+    return x.to(torch.bfloat16).to(torch.float32)
+
+
+def tf32_trunc(x: torch.Tensor) -> torch.Tensor:
+    """Drop the 13 low mantissa bits of fp32 (what a TF32 tensor-core read keeps)."""
+    return (x.contiguous().view(torch.int32) & ~0x1FFF).view(torch.float32)
+
+
+# --------------------------------------------------------------------------
+# K1: correlation pyramid build   (models/core/corr.py:56-72, 96-104)
+# --------------------------------------------------------------------------
+
+def corr_volume(fmap1: torch.Tensor, fmap2: torch.Tensor) -> torch.Tensor:
+    """corr[b,h,i,j] = sum_d fmap1[b,d,h,i] * fmap2[b,d,h,j] / sqrt(D).
+
+    Follows CorrBlock1D.corr (models/core/corr.py:96-104): an einsum over the
+    channel axis per image row, then a division by sqrt(D).  fp32 throughout.
+    Returns (B, H, W1, W2).
+    """
+    B, D, H, W1 = fmap1.shape
+    a = fmap1.float().permute(0, 2, 3, 1)          # B,H,W1,D
+    b = fmap2.float().permute(0, 2, 1, 3)          # B,H,D,W2
+    vol = torch.matmul(a, b)                       # B,H,W1,W2
+    return vol / math.sqrt(D)
+
+
+def pool_level(level: torch.Tensor) -> torch.Tensor:
+    """Average adjacent pairs along the last axis, dropping an odd last column.
+
+    Follows F.avg_pool2d(corr, [1,2], stride=[1,2]) at models/core/corr.py:71.
+    """
+    w = level.shape[-1] // 2
+    return (level[..., 0:2 * w:2] + level[..., 1:2 * w:2]) / 2
+
+
+def corr_pyramid(fmap1: torch.Tensor, fmap2: torch.Tensor, num_levels: int = 4,
+                 mode: str = "fp32") -> List[torch.Tensor]:
+    """The (num_levels+1)-level pyramid of CorrBlock1D.__init__ (corr.py:56-72).
+
+    Each level is returned as (B*H*W1, W2 >> l) fp32.
+
+    mode "fp32": exact fp32 (the reference's CPU path).
+    mode "bf16": what the reference's GPU autocast path stores
+      (models/core/ppmstereo.py:617 puts the einsum under bf16 autocast):
+      inputs rounded to bf16, fp32 accumulation, the einsum result rounded to
+      bf16, the division by sqrt(D) rounded to bf16 again, and every pooled
+      level rounded to bf16 (cascaded rounding).
+    mode "tf32": inputs truncated to TF32, fp32 accumulate, fp32 output.
+    """
+    B, D, H, W1 = fmap1.shape
+    W2 = fmap2.shape[-1]
+    if mode == "fp32":
+        vol = corr_volume(fmap1, fmap2)
+    elif mode == "tf32":
+        vol = corr_volume(tf32_trunc(fmap1.float()), tf32_trunc(fmap2.float()))
+    elif mode == "bf16":
+        a = bf16_round(fmap1.float()).permute(0, 2, 3, 1)
+        b = bf16_round(fmap2.float()).permute(0, 2, 1, 3)
+        acc = bf16_round(torch.matmul(a, b))
+        vol = bf16_round(acc / torch.sqrt(torch.tensor(float(D))))
+    else:
+        raise ValueError(mode)
+    levels = [vol.reshape(B * H * W1, W2)]
+    for _ in range(num_levels):
+        nxt = pool_level(levels[-1])
+        if mode == "bf16":
+            nxt = bf16_round(nxt)
+        levels.append(nxt)
+    return levels
+
+
+# --------------------------------------------------------------------------
+# K2: radius-r lookup   (models/core/corr.py:74-94, bilinear_sampler :10-27)
+# --------------------------------------------------------------------------
+
+def corr_lookup(levels: Sequence[torch.Tensor], flow: torch.Tensor, radius: int = 4,
+                num_levels: int = 4) -> torch.Tensor:
+    """out[b, l*(2r+1) + (k+r), y, x] = lerp of level l's row (b,y,x) at
+    (x + flow_x[b,y,x]) / 2**l + k, taps outside [0, W_l-1] contributing zero.
+
+    Closed form of CorrBlock1D.__call__ (corr.py:74-94): grid_sample with
+    align_corners=True, zeros padding, H == 1, y pinned to 0.  Only the x
+    channel of ``flow`` is used (corr.py:77).  flow: (B,2,H,W1) fp32.
+    Returns (B, num_levels*(2r+1), H, W1) fp32.
+    """
+    B, _, H, W1 = flow.shape
+    xs = torch.arange(W1, dtype=torch.float32).view(1, 1, W1)
+    center = (xs + flow[:, 0].float()).reshape(-1)            # (B*H*W1,)
+    rows = torch.arange(center.numel())
+    out = []
+    for l in range(num_levels):
+        lvl = levels[l].float()
+        Wl = lvl.shape[-1]
+        c = center / (2 ** l)
+        for k in range(-radius, radius + 1):
+            x = c + k
+            x0 = torch.floor(x)
+            a = x - x0
+            i0 = x0.long()
+            i1 = i0 + 1
+            v0 = torch.where((i0 >= 0) & (i0 < Wl), lvl[rows, i0.clamp(0, Wl - 1)], torch.zeros(()))
+            v1 = torch.where((i1 >= 0) & (i1 < Wl), lvl[rows, i1.clamp(0, Wl - 1)], torch.zeros(()))
+            out.append((1 - a) * v0 + a * v1)
+    out = torch.stack(out, 0).reshape(num_levels * (2 * radius + 1), B, H, W1)
+    return out.permute(1, 0, 2, 3).contiguous()
+
+
+# --------------------------------------------------------------------------
+# K3: Pick-and-Play Memory read   (models/core/ppmstereo.py:397-423, 443-555)
+# --------------------------------------------------------------------------
+
+def temporal_pe(T: int, c: int) -> torch.Tensor:
+    """Sinusoidal table PE[t, 2i] = sin(pos_t * w_i), PE[t, 2i+1] = cos(pos_t * w_i),
+    pos_t = t / (T-1), w_i = 10000^(-2i/c).  Follows
+    get_temporal_positional_encoding(is_normalize=True, scale=1.)
+    (models/core/ppmtereo_update.py:25-88; call site ppmstereo.py:453-461).
+    Returns (T, c) fp32.  T == 1 gives NaN, as in the reference (0/0).
+    """
+    pos = torch.arange(T, dtype=torch.float32)
+    pos = pos / pos[-1] * 1.0
+    w = 1.0 / (10000.0 ** (torch.arange(0, c, 2).float() / c))
+    ang = pos[:, None] * w[None, :]
+    pe = torch.zeros(T, c)
+    pe[:, 0::2] = torch.sin(ang)
+    pe[:, 1::2] = torch.cos(ang)
+    return pe
+
+
+def _adaptive_bounds(n_in: int, n_out: int) -> List[Tuple[int, int]]:
+    return [((i * n_in) // n_out, -((-(i + 1) * n_in) // n_out)) for i in range(n_out)]
+
+
+def qk_similarity(query: torch.Tensor, key: torch.Tensor) -> torch.Tensor:
+    """sim[b,0,i,j] = cos(k_[b,i], q_[b,j]) where x_ is the channel-mean of the
+    adaptive max pool of frame x to (h//4, w//4).  Follows
+    PPMStereo.compute_qk_similarity (models/core/ppmstereo.py:397-423), with
+    F.cosine_similarity's eps = 1e-8 clamp on each norm.
+    query, key: (b, c, T, h, w).  Returns (b, 1, T, T) fp32.
+    """
+    b, c, T, h, w = query.shape
+    oh, ow = h // 4, w // 4
+
+    def pooled(x):
+        x = x.float()
+        rows = []
+        for (r0, r1) in _adaptive_bounds(h, oh):
+            cols = []
+            for (c0, c1) in _adaptive_bounds(w, ow):
+                cols.append(x[..., r0:r1, c0:c1].amax(dim=(-2, -1)))
+            rows.append(torch.stack(cols, -1))
+        p = torch.stack(rows, -2)                  # b,c,T,oh,ow
+        return p.mean(dim=1).reshape(b, T, oh * ow)
+
+    q_, k_ = pooled(query), pooled(key)
+    dots = torch.einsum("bin,bjn->bij", k_, q_)
+    nk = k_.norm(dim=-1).clamp_min(1e-8)
+    nq = q_.norm(dim=-1).clamp_min(1e-8)
+    return (dots / (nk[:, :, None] * nq[:, None, :])).unsqueeze(1)
+
+
+def qam_frame_score(sim: torch.Tensor, strive: torch.Tensor,
+                    uncertainty: torch.Tensor) -> torch.Tensor:
+    """frame_score[b,0,i,j] = exp(-S_ij / (sum_j S_ij + T)) * sim_ij + conf_j with
+    conf_j the mean over pixels of frame j's uncertainty map.
+    Follows models/core/ppmstereo.py:501-507.
+    sim, strive: (b,1,T,T); uncertainty: (b*T, 1, h, w).
+    """
+    b, _, T, _ = sim.shape
+    penalty = torch.exp(-strive / (strive.sum(3, keepdim=True) + T))
+    conf = uncertainty.float().reshape(b, 1, 1, T, -1).mean(-1)
+    return penalty * sim + conf
+
+
+def topk_pick(frame_score: torch.Tensor, top_k: int = 5) -> torch.Tensor:
+    """Boolean mask (b,1,T,T): per (b, i) row, the top_k largest scores.
+    Follows models/core/ppmstereo.py:509-512 (argsort descending, first top_k,
+    scatter into a mask).  Ties broken towards the lower frame index (the
+    reference's argsort is unstable, so exact ties are undefined there).
+    """
+    T = frame_score.shape[-1]
+    order = torch.sort(frame_score, dim=-1, descending=True, stable=True).indices
+    mask = torch.zeros_like(frame_score, dtype=torch.bool)
+    mask.scatter_(3, order[..., :min(top_k, T)], True)
+    return mask
+
+
+def attention_bf16(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, scale: float,
+                   round_p: bool = True, chunk: int = 8192) -> torch.Tensor:
+    """softmax(scale * q k^T) v with FlashAttention-2 rounding: q, k, v rounded
+    to bf16, scores/softmax in fp32, P rounded to bf16 before P.v (round_p),
+    fp32 accumulation, normalisation by the fp32 row sum, output rounded to
+    bf16 and returned as fp32.  Restates flash_attn.flash_attn_func as called
+    at models/core/ppmstereo.py:550 (single head, no mask, no dropout).
+    q: (Lq, d), k, v: (Lk, d).  Query-chunked so that scores stay small.
+    """
+    q, k, v = bf16_round(q.float()), bf16_round(k.float()), bf16_round(v.float())
+    out = torch.empty(q.shape[0], v.shape[1])
+    for s in range(0, q.shape[0], chunk):
+        sc = (q[s:s + chunk] @ k.t()) * scale
+        m = sc.amax(dim=-1, keepdim=True)
+        p = torch.exp(sc - m)
+        l = p.sum(-1, keepdim=True)
+        if round_p:
+            p = bf16_round(p)
+        out[s:s + chunk] = (p @ v) / l
+    return bf16_round(out)
+
+
+def ppm_softmax_scale(c: int = 128) -> float:
+    """scale = c^-0.5 * log_12000(2c)  (models/core/ppmstereo.py:494; the key
+    carries 2c channels after the PE concat at :475)."""
+    return c ** -0.5 * math.log(2 * c, 12000)
+
+
+def ppm_memory_read(query, key, pe, value, motion_features, sim, strive, uncertainty,
+                    beta, scale: Optional[float] = None, top_k: int = 5,
+                    rows: Optional[torch.Tensor] = None):
+    """One iteration of the PPM read (models/core/ppmstereo.py:501-555).
+
+    query, key, value, motion_features: (b, c, T, h, w); pe: (T, c);
+    sim, strive: (b,1,T,T) (strive is NOT modified; the new one is returned);
+    uncertainty: (b*T,1,h,w); beta: float.
+    rows: optional 1-D LongTensor of query pixel indices to evaluate (for
+    large shapes); other pixels of the output are left equal to motion_features.
+
+    Returns dict with frame_score, mask, strive (updated), picked (b,T,K) ascending
+    int64 (-1 padded), score_norm (b,T,K), hidden (b,T,c,hw) and
+    motion_features_global (b*T, c, h, w).
+    """
+    b, c, T, h, w = query.shape
+    hw = h * w
+    if scale is None:
+        scale = ppm_softmax_scale(c)
+    score = qam_frame_score(sim, strive, uncertainty)
+    mask = topk_pick(score, top_k)
+    strive_new = strive.clone()
+    strive_new[mask] += 1                                     # ppmstereo.py:513
+    K = min(top_k, T)
+    picked = torch.full((b, T, K), -1, dtype=torch.long)
+    score_norm = torch.zeros(b, T, K)
+    qf = query.float().reshape(b, c, T, hw)
+    kf = key.float().reshape(b, c, T, hw)
+    vf = value.float().reshape(b, c, T, hw)
+    mf = motion_features.float().reshape(b, c, T, hw)
+    hidden = torch.zeros(b, T, c, hw)
+    out = mf.permute(0, 2, 1, 3).clone()                      # b,T,c,hw
+    sel = slice(None) if rows is None else rows
+    for i in range(T):
+        # picked set in temporal order (masked_select semantics, :524-529)
+        idx = [torch.nonzero(mask[bb, 0, i]).flatten() for bb in range(b)]
+        sel_scores = torch.stack([score[bb, 0, i, idx[bb]] for bb in range(b)])   # b,K
+        norm = sel_scores / sel_scores.mean()                 # mean over b*K (:533)
+        for bb in range(b):
+            picked[bb, i] = idx[bb]
+            score_norm[bb, i] = norm[bb]
+            qi = (qf[bb, :, i] + pe[i][:, None]).t()          # hw,c   (:518-522)
+            ks, vs = [], []
+            for n, j in enumerate(idx[bb].tolist()):
+                ks.append((kf[bb, :, j] * norm[bb, n] + pe[j][:, None]).t())   # (:541)
+                vs.append(vf[bb, :, j].t())
+            kk, vv = torch.cat(ks, 0), torch.cat(vs, 0)       # K*hw, c (:547-548)
+            hid = attention_bf16(qi[sel], kk, vv, scale)      # (:550)
+            hidden[bb, i][:, sel] = hid.t()
+            out[bb, i][:, sel] = mf[bb, :, i][:, sel] + beta * hid.t()         # (:552)
+    return {
+        "frame_score": score, "mask": mask, "strive": strive_new, "picked": picked,
+        "score_norm": score_norm, "hidden": hidden,
+        "motion_features_global": out.reshape(b * T, c, h, w),
+    }

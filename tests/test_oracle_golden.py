@@ -1,0 +1,83 @@
+"""Pin the CPU oracle against fixtures produced by the unmodified reference
+(tests/golden/make_golden.py).  CPU only."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import ppm_oracle as O
+
+CORR_CASES = ["corr_d256_w82", "corr_d128_w64", "corr_d256_w160"]
+
+
+def _load(golden_dir, name):
+    return {k: v for k, v in np.load(os.path.join(golden_dir, name + ".npz")).items()}
+
+
+@pytest.mark.parametrize("name", CORR_CASES)
+def test_corr_pyramid_matches_reference(golden_dir, name):
+    g = _load(golden_dir, name)
+    lv = O.corr_pyramid(torch.from_numpy(g["fmap1"]), torch.from_numpy(g["fmap2"]))
+    assert len(lv) == 5
+    for l in range(5):
+        ref = torch.from_numpy(g[f"level{l}"])
+        assert lv[l].shape == ref.shape
+        # fp32 matmul summation order differs from einsum's: 1e-5 relative to the level's scale
+        assert (lv[l] - ref).abs().max() <= 1e-5 * ref.abs().max()
+
+
+@pytest.mark.parametrize("name", CORR_CASES)
+def test_corr_lookup_matches_reference(golden_dir, name):
+    g = _load(golden_dir, name)
+    levels = [torch.from_numpy(g[f"level{l}"]) for l in range(5)]
+    out = O.corr_lookup(levels, torch.from_numpy(g["flow"]))
+    ref = torch.from_numpy(g["lookup"])
+    assert out.shape == ref.shape
+    # north_star bar: 1e-4 abs vs grid_sample (its normalise/denormalise round trip is ~2e-5)
+    assert (out - ref).abs().max() <= 1e-4
+
+
+@pytest.mark.parametrize("name", ["ppm_read_l16", "ppm_read_l08"])
+def test_ppm_read_matches_reference(golden_dir, name):
+    g = _load(golden_dir, name)
+    t = {k: torch.from_numpy(v) for k, v in g.items() if v.dtype != np.uint16 and v.ndim > 0}
+    b, c, T, h, w = t["query"].shape
+    pe = O.temporal_pe(T, c)
+    sim = O.qk_similarity(t["query"], t["key"])
+    assert (sim - t["sim"]).abs().max() <= 1e-5
+    assert abs(O.ppm_softmax_scale(c) - float(g["scale"])) < 1e-12
+    r = O.ppm_memory_read(t["query"], t["key"], pe, t["value"], t["motion_features"], t["sim"],
+                          t["strive_before"], t["uncertainty"], float(g["beta"]))
+    assert (r["frame_score"] - t["frame_score"]).abs().max() <= 1e-6
+    assert torch.equal(r["mask"], t["mask"])                       # bit-exact top-k sets
+    top5 = torch.sort(t["argsort"][..., :5], dim=-1).values[:, 0]
+    assert torch.equal(r["picked"], top5)
+    # modulated keys as fed to flash_attn (bf16 bits), frame-major then pixel
+    kmod = torch.from_numpy(g["kmod_bf16"].astype(np.int16)).view(torch.bfloat16).float()
+    hw = h * w
+    for i in range(T):
+        for n, j in enumerate(r["picked"][0, i].tolist()):
+            mine = O.bf16_round((t["key"][0, :, j].reshape(c, hw) * r["score_norm"][0, i, n]
+                                 + pe[j][:, None]).t())
+            ref = kmod[i, n * hw:(n + 1) * hw]
+            # one bf16 ulp: the reference forms score_norm with a different op order
+            assert (mine - ref).abs().max() <= 2.0 ** -7 * ref.abs().max()
+    hid = torch.from_numpy(g["hidden_bf16"].astype(np.int16)).view(torch.bfloat16).float()
+    mine = r["hidden"][0].permute(0, 2, 1)                           # T,hw,c
+    assert (mine - hid).abs().max() <= 2e-2 * hid.abs().max()
+    assert (mine - hid).abs().mean() <= 2e-3 * hid.abs().mean() + 1e-6
+    out = r["motion_features_global"]
+    assert (out - t["motion_features_global"]).abs().max() <= 2e-2 * hid.abs().max()
+
+
+def test_temporal_pe_endpoints():
+    pe = O.temporal_pe(20, 128)
+    assert torch.equal(pe[0, 0::2], torch.zeros(64)) and torch.equal(pe[0, 1::2], torch.ones(64))
+    assert abs(float(pe[-1, 0]) - np.sin(1.0)) < 1e-6
+    assert torch.isnan(O.temporal_pe(1, 8)).all()
+
+
+def test_topk_no_op_when_T_le_k():
+    s = torch.rand(2, 1, 4, 4)
+    assert O.topk_pick(s, 5).all()
