@@ -1,0 +1,117 @@
+/* ppm_b200.h — C ABI of libppm_sm100.so: the B200 (sm_100a) drop-in for the PPMStereo
+ * correlation + Pick-and-Play-Memory hot path.
+ *
+ * The reference (cocowy1/PPMStereo) is pure Python/PyTorch and has no FFI for this path;
+ * each entry point below replaces a Python call surface of the reference, cited as
+ * file:line under /root/reference.  All pointers are DEVICE pointers unless stated, all
+ * tensors are caller-allocated and densely packed as described, outputs are fully
+ * overwritten, nothing is retained across calls, no call synchronises the host and every
+ * kernel is launched on `stream` (a cudaStream_t passed as void*), so sequences of calls are
+ * CUDA-graph capturable.  Every function returns 0 on success or a PPM_ERR_* code;
+ * ppm_last_error() then returns a thread-local description.  There is no CPU fallback.
+ */
+#ifndef PPM_B200_H_
+#define PPM_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PPM_ABI_VERSION 1
+
+enum ppm_dtype { PPM_F32 = 0, PPM_BF16 = 1 };
+
+enum ppm_status {
+  PPM_OK = 0,
+  PPM_ERR_ARG = 1,         /* bad shape / dtype / null pointer / misalignment */
+  PPM_ERR_CUDA = 2,        /* a CUDA runtime or driver call failed */
+  PPM_ERR_UNSUPPORTED = 3  /* valid request the kernels do not cover (e.g. T > 64) */
+};
+
+int ppm_abi_version(void);
+const char* ppm_last_error(void);
+
+/* ---------------------------------------------------------------------------------------
+ * K1  correlation pyramid build.
+ * Replaces CorrBlock1D.__init__ + CorrBlock1D.corr (models/core/corr.py:56-72, :96-104):
+ *   L0[(b,h,i), j] = sum_d fmap1[b,d,h,i] * fmap2[b,d,h,j] / sqrt(D)
+ *   L(l+1)[r, j]   = (L(l)[r, 2j] + L(l)[r, 2j+1]) / 2, j < floor(W(l)/2)
+ * fmap1 (B,D,H,ld1), fmap2 (B,D,H,ld2): NCHW with row pitch ld >= W (elements), the first W
+ * entries of each row valid, dtype `in_dtype`.
+ * levels[l], l = 0..n_levels: (B*H*W1, W2 >> l) row-major, dtype `out_dtype`.
+ * PPM_BF16 inputs run on tcgen05 kind::f16 (bf16 x bf16 -> fp32); PPM_F32 inputs on
+ * kind::tf32.  With out_dtype == PPM_BF16 the result is rounded the way the reference's
+ * autocast path rounds it (accumulator -> bf16, / sqrt(D) -> bf16, every level -> bf16).
+ * Requires ld % 8 == 0 for bf16 (4 for f32) and 16-byte aligned fmaps (TMA row pitch),
+ * W2 >> n_levels >= 1, n_levels <= 4.  `levels` is a HOST array of device pointers. */
+int ppm_corr_build(const void* fmap1, const void* fmap2, int in_dtype, int B, int D, int H,
+                   int W1, int W2, int ld1, int ld2, void* const* levels, int n_levels,
+                   int out_dtype, void* stream);
+
+/* ---------------------------------------------------------------------------------------
+ * K2  radius-r correlation lookup.
+ * Replaces CorrBlock1D.__call__ + bilinear_sampler (models/core/corr.py:74-94, :10-27):
+ *   x_l = (x + flow[b,0,y,x]) / 2^l
+ *   out[b, l*(2r+1) + k + r, y, x] = lerp(L_l row (b,y,x), x_l + k), zero outside [0, W_l-1]
+ * levels[l], l = 0..n_levels-1 as written by ppm_corr_build (dtype vol_dtype); `levels` is a
+ * HOST array of device pointers.  flow (B,2,H,W1) fp32 (only channel 0 is read).
+ * out (B, n_levels*(2r+1), H, W1) fp32.  radius <= 4, n_levels <= 4. */
+int ppm_corr_lookup(const void* const* levels, int vol_dtype, const float* flow, int B, int H,
+                    int W1, int W2, int radius, int n_levels, float* out, void* stream);
+
+/* ---------------------------------------------------------------------------------------
+ * K3a  QAM frame scoring + top-k pick (models/core/ppmstereo.py:501-513, :532-533).
+ *   conf[b,j]      = mean_{hw} uncertainty[b*T + j]
+ *   score[b,i,j]   = exp(-S[b,i,j] / (sum_j S[b,i,j] + T)) * sim[b,i,j] + conf[b,j]
+ *   picked[b,i,:]  = indices of the top_k largest score[b,i,:] in ASCENDING index order
+ *                    (ties -> lower index); -1 padded when T < top_k
+ *   S[b,i,j]      += 1 for picked j                       (strive_time, in/out)
+ *   score_norm[b,i,n] = score[b,i,picked n] / mean_{b,n} score[b,i,picked n]
+ * sim, strive, frame_score: (b,T,T) fp32; uncertainty (b*T, hw) dtype unc_dtype;
+ * picked (b,T,top_k) int32; score_norm (b,T,top_k) fp32; mask (b,T,T) uint8 (may be NULL).
+ * conf_ws: (b*T) fp32 scratch.  T <= 64, top_k <= 16. */
+int ppm_qam_pick(const float* sim, float* strive, const void* uncertainty, int unc_dtype, int b,
+                 int T, int hw, int top_k, float* frame_score, int32_t* picked,
+                 float* score_norm, uint8_t* mask, float* conf_ws, void* stream);
+
+/* ---------------------------------------------------------------------------------------
+ * K3b  operand packing for the memory read (models/core/ppmstereo.py:518-548).
+ * Source tensors are indexed src[b*sb + c*sc + t*st + p] (element strides, pixel stride 1),
+ * c = 128 channels, dtype src_dtype.
+ *   ppm_pack_query : Q[(b*T+t), p, c]            = bf16(query + pe[t,c])            (:518-522)
+ *   ppm_pack_key   : K[((b*T+i)*Kp+n), p, c]     = bf16(key[b,c,j,p]*score_norm[b,i,n] + pe[j,c]),
+ *                    j = picked[b,i,n]; rows with j < 0 are zero-filled             (:524-548)
+ *   ppm_pack_value : V[(b*T+t), c, p_pad]        = bf16(value), p_pad = round_up(hw, 8) (:529)
+ * pe: (T,128) fp32. */
+int ppm_pack_query(const void* query, int src_dtype, int64_t sb, int64_t sc, int64_t st,
+                   const float* pe, int b, int T, int hw, void* q_out, void* stream);
+int ppm_pack_key(const void* key, int src_dtype, int64_t sb, int64_t sc, int64_t st,
+                 const float* pe, const int32_t* picked, const float* score_norm, int b, int T,
+                 int Kp, int hw, void* k_out, void* stream);
+int ppm_pack_value(const void* value, int src_dtype, int64_t sb, int64_t sc, int64_t st, int b,
+                   int T, int hw, void* v_out, void* stream);
+
+/* ---------------------------------------------------------------------------------------
+ * K3c  query-adaptive softmax aggregation over the picked frames + residual
+ * (flash_attn_func call at models/core/ppmstereo.py:550, residual :551-555).
+ *   hidden[b,i,p,:] = bf16( softmax_{n,p'}(scale * Q[b,i,p] . K[b,i,n,p']) V[picked[b,i,n], :, p'] )
+ *   out[(b*T+i), c, p] = mf[b*mb + c*mc + i*mt + p] + beta[0] * hidden[b,i,p,c]
+ * Q, K, V as written by the pack calls; mf dtype mf_dtype; beta: device fp32 scalar;
+ * out (b*T, 128, hw) fp32.  bf16 operands, fp32 scores/softmax, P rounded to bf16 before
+ * P.V (FlashAttention-2 rounding), tcgen05 MMAs with TMEM accumulators. */
+int ppm_memory_attend(const void* Q, const void* K, const void* V, const int32_t* picked,
+                      const void* mf, int mf_dtype, int64_t mb, int64_t mc, int64_t mt,
+                      const float* beta, float scale, int b, int T, int Kp, int hw, float* out,
+                      void* stream);
+
+/* Bytes of the packed operands for (b, T, Kp, hw): q, k, v in that order. */
+int ppm_pack_bytes(int b, int T, int Kp, int hw, size_t* q_bytes, size_t* k_bytes,
+                   size_t* v_bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PPM_B200_H_ */

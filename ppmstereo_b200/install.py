@@ -1,0 +1,65 @@
+"""Rewire a loaded reference PPMStereo onto the B200 kernels without touching its signatures.
+
+``install(module)`` takes the imported ``models.core.ppmstereo`` module of the reference and
+  * rebinds the name ``CorrBlock1D`` used at models/core/ppmstereo.py:707, :743, :776, and
+  * replaces ``PPMStereo.forward_update_block`` (models/core/ppmstereo.py:426-594) by the
+    function below: same arguments, same return value, same side effects on ``predictions`` /
+    ``uncertainties``; the block :501-555 becomes one PPMMemory.read call.
+``PPMStereoModel.forward`` / ``PPMStereo.forward`` and all state-dict keys are unchanged.
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn.functional as F
+
+from .corr import CorrBlock1D
+from .memory import C, PPMMemory, softmax_scale
+
+
+def forward_update_block(self, image1, update_block, corr_fn, flow, net, inp, motion_hidden_state,
+                         attn_block, predictions, uncertainties, iters, interp_scale, t):
+    bt, c, h, w = inp.shape
+    b = bt // t
+    if c != C:
+        raise RuntimeError(f"context dim {c} != {C}")
+    # once per level: q/k projections, QAM similarity, pick counter (ppmstereo.py:447-476)
+    qk = attn_block.to_qk(inp)
+    query = qk[:, :c].reshape(b, t, c, h, w).permute(0, 2, 1, 3, 4)
+    key = qk[:, c:].reshape(b, t, c, h, w).permute(0, 2, 1, 3, 4)
+    sim_score = self.compute_qk_similarity(query, key, t=t).float().contiguous()
+    strive_time = torch.ones_like(sim_score)
+    memory = PPMMemory(query, key, None, top_k=5)
+    scale = softmax_scale(c)
+    autocast = torch.autocast("cuda", dtype=torch.bfloat16, enabled=bool(self.mixed_precision))
+    flow_out = flow
+    for _ in range(iters):
+        flow = flow.detach()
+        out_corrs = corr_fn(flow)
+        motion_features, motion_hidden_state, value = update_block.get_motion_and_value(
+            flow, out_corrs, motion_hidden_state, inp)
+        uncertainty_score = update_block.get_uncertainty(torch.cat([net, value], dim=1))
+        mf5 = motion_features.reshape(b, t, c, h, w).permute(0, 2, 1, 3, 4)
+        v5 = value.reshape(b, t, c, h, w).permute(0, 2, 1, 3, 4)
+        motion_features_global, _ = memory.read(v5, mf5, sim_score, strive_time, uncertainty_score,
+                                                update_block.aggregator.beta, scale)
+        with autocast:
+            net, up_mask, delta_flow = update_block(net, inp, motion_features, motion_features_global, t=t)
+        flow = flow + delta_flow
+        if self.use_convex_3d:
+            flow_up = flow_out = self.convex_upsample_3d(flow, up_mask, rate=4, T=t)
+        else:
+            flow_up = flow_out = self.convex_upsample(flow, up_mask, rate=4)
+        uncertainty_up = F.interpolate(uncertainty_score, scale_factor=4 * interp_scale, mode="bilinear")
+        if interp_scale > 1:
+            size = (interp_scale * flow_out.shape[2], interp_scale * flow_out.shape[3])
+            flow_up = interp_scale * F.interpolate(flow_out, size=size, mode="bilinear", align_corners=True)
+        predictions.append(flow_up[:, :1])
+        uncertainties.append(uncertainty_up)
+    return flow_out, net, motion_hidden_state
+
+
+def install(ppmstereo_module):
+    """Patch the reference module in place; returns it."""
+    ppmstereo_module.CorrBlock1D = CorrBlock1D
+    ppmstereo_module.PPMStereo.forward_update_block = forward_update_block
+    return ppmstereo_module

@@ -1,0 +1,77 @@
+"""CPU-side checks of the drop-in boundary: the C-ABI library loads and exports every symbol
+that include/ppm_b200.h declares, argument errors are reported without a GPU, and the host
+logic mirrors the reference.  No compute calls."""
+import ctypes
+import os
+import re
+
+import pytest
+import torch
+
+import ppmstereo_b200 as P
+from ppmstereo_b200 import _lib, build
+from oracle import ppm_oracle as O
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def lib():
+    build.build()
+    return _lib.load()
+
+
+def test_exports_every_declared_symbol(lib):
+    header = open(os.path.join(ROOT, "include", "ppm_b200.h")).read()
+    declared = set(re.findall(r"^(?:int|const char\*)\s+(ppm_\w+)\s*\(", header, flags=re.M))
+    assert len(declared) >= 10
+    assert declared == set(_lib.SIGNATURES), (declared ^ set(_lib.SIGNATURES))
+    for name in declared:
+        assert hasattr(lib, name), name
+    assert lib.ppm_abi_version() == 1
+
+
+def test_argument_errors_are_reported(lib):
+    rc = lib.ppm_corr_build(None, None, 0, 1, 1, 1, 8, 8, 8, 8, None, 4, 0, None)
+    assert rc == 1 and b"null" in lib.ppm_last_error()
+    buf = ctypes.create_string_buffer(64)
+    arr = (ctypes.c_void_p * 5)(*[ctypes.addressof(buf)] * 5)
+    rc = lib.ppm_corr_build(ctypes.addressof(buf), ctypes.addressof(buf), 1, 1, 8, 1, 8, 8, 8, 8, arr, 4, 1, None)
+    assert rc == 1 and b"too small" in lib.ppm_last_error()      # reference: W/16 >= 1 (corr.py:71)
+    rc = lib.ppm_corr_lookup(arr, 0, ctypes.addressof(buf), 1, 1, 8, 16, 5, 4, ctypes.addressof(buf), None)
+    assert rc == 3 and b"radius" in lib.ppm_last_error()
+    rc = lib.ppm_qam_pick(*[ctypes.addressof(buf)] * 3, 0, 1, 65, 4, 5, *[ctypes.addressof(buf)] * 5, None)
+    assert rc == 3 and b"T = 65" in lib.ppm_last_error()
+    q, k, v = ctypes.c_size_t(), ctypes.c_size_t(), ctypes.c_size_t()
+    assert lib.ppm_pack_bytes(1, 20, 5, 3680, ctypes.byref(q), ctypes.byref(k), ctypes.byref(v)) == 0
+    assert (q.value, k.value, v.value) == (20 * 3680 * 256, 100 * 3680 * 256, 20 * 128 * 3680 * 2)
+    assert lib.ppm_pack_bytes(1, 1, 1, 5, ctypes.byref(q), None, ctypes.byref(v)) == 0 and v.value == 128 * 8 * 2
+
+
+def test_cpu_tensors_are_rejected():
+    f = torch.zeros(1, 8, 2, 16)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        P.CorrBlock1D(f, f)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        P.PPMMemory(torch.zeros(1, 128, 2, 2, 2), torch.zeros(1, 128, 2, 2, 2))
+
+
+def test_host_helpers_match_oracle():
+    assert torch.allclose(P.temporal_pe_table(20, 128, "cpu"), O.temporal_pe(20, 128), atol=1e-7)
+    assert abs(P.softmax_scale(128) - O.ppm_softmax_scale(128)) < 1e-15
+    assert abs(P.softmax_scale(128) - 0.05218212637175694) < 1e-15
+
+
+def test_missing_library_fails_loudly(monkeypatch, tmp_path):
+    monkeypatch.setattr(_lib, "_lib", None)
+    monkeypatch.setattr(_lib, "LIB_PATH", str(tmp_path / "nope.so"))
+    with pytest.raises(RuntimeError, match="no CPU or PyTorch fallback"):
+        _lib.load()
+
+
+def test_product_does_not_import_oracle():
+    pkg = os.path.join(ROOT, "ppmstereo_b200")
+    for fn in os.listdir(pkg):
+        if fn.endswith(".py"):
+            src = open(os.path.join(pkg, fn)).read()
+            assert "oracle" not in src.replace("no oracle", ""), fn

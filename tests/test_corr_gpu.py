@@ -1,0 +1,153 @@
+"""GPU parity tests for K1 (correlation pyramid build) and K2 (lookup), through the C ABI.
+
+Checked against (i) golden vectors produced by the unmodified reference (tests/golden), (ii) the CPU
+oracle on seeded inputs, (iii) size-independent properties at BASELINE.json's full shapes.
+Tolerances (north_star): volumes <= 1e-3 relative with the operand precision stated per test
+(bf16 operands / TF32 operands vs the fp32 oracle); lookup <= 1e-4 abs vs grid_sample.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import ppm_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+CASES = ["corr_d256_w82", "corr_d128_w64", "corr_d256_w160"]
+
+
+@pytest.fixture(scope="module")
+def P():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import ppmstereo_b200 as P
+    return P
+
+
+def load(golden_dir, name):
+    return {k: torch.from_numpy(v) for k, v in np.load(os.path.join(golden_dir, name + ".npz")).items()}
+
+
+def rel(a, b):
+    return float((a - b).norm() / b.norm())
+
+
+def flat(levels):
+    return [l.reshape(l.shape[0], l.shape[-1]).float().cpu() for l in levels]
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_build_tf32_vs_reference_golden(P, golden_dir, name):
+    """fp32 feature maps -> kind::tf32 MMA, fp32 output; vs the reference's fp32 CPU pyramid."""
+    g = load(golden_dir, name)
+    blk = P.CorrBlock1D(g["fmap1"].cuda(), g["fmap2"].cuda())
+    assert len(blk.corr_pyramid) == 5
+    got = flat(blk.corr_pyramid)
+    want_tf32 = O.corr_pyramid(g["fmap1"], g["fmap2"], mode="tf32")
+    for l in range(5):
+        ref = g[f"level{l}"]
+        assert tuple(blk.corr_pyramid[l].shape) == (ref.shape[0], 1, 1, ref.shape[1])
+        assert rel(got[l], ref) <= 1e-3, (l, rel(got[l], ref))          # TF32 operands vs fp32
+        assert rel(got[l], want_tf32[l]) <= 2e-5, (l, rel(got[l], want_tf32[l]))
+    assert tuple(blk.coords.shape) == tuple(g["flow"].shape)
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_build_bf16_operands(P, golden_dir, name):
+    """bf16 feature maps (what autocast hands over on the GPU) -> kind::f16 MMA."""
+    g = load(golden_dir, name)
+    f1, f2 = g["fmap1"].bfloat16(), g["fmap2"].bfloat16()
+    # fp32 output: exact products, fp32 accumulation
+    got = flat(P.build_pyramid(f1.cuda(), f2.cuda(), 4, out_dtype=torch.float32))
+    want = O.corr_pyramid(f1.float(), f2.float(), mode="fp32")
+    for l in range(5):
+        assert rel(got[l], want[l]) <= 1e-5, (l, rel(got[l], want[l]))
+        assert rel(got[l], g[f"level{l}"]) <= 5e-3        # bf16 operands vs the fp32 reference
+    # bf16 output with the reference's cascaded rounding
+    got = flat(P.build_pyramid(f1.cuda(), f2.cuda(), 4))
+    want = O.corr_pyramid(f1.float(), f2.float(), mode="bf16")
+    for l in range(5):
+        d = (got[l] - want[l]).abs()
+        ulp = want[l].abs().clamp_min(1e-30) * 2.0 ** -7
+        assert bool((d <= ulp).all()), (l, float((d / ulp).max()))      # within one bf16 ulp
+        assert float((d == 0).float().mean()) >= 0.995, (l, float((d == 0).float().mean()))
+
+
+@pytest.mark.parametrize("name", CASES)
+@pytest.mark.parametrize("vol", ["fp32", "bf16"])
+def test_lookup_vs_reference_golden(P, golden_dir, name, vol):
+    g = load(golden_dir, name)
+    levels = [g[f"level{l}"] for l in range(5)]
+    if vol == "bf16":
+        levels = [l.bfloat16() for l in levels]
+    dev = [l.reshape(l.shape[0], 1, 1, l.shape[1]).cuda() for l in levels]
+    got = P.lookup(dev, g["flow"].cuda(), W2=levels[0].shape[1]).cpu()
+    assert got.shape == g["lookup"].shape and got.dtype == torch.float32
+    if vol == "fp32":
+        assert float((got - g["lookup"]).abs().max()) <= 1e-4
+        assert float((got - g["lookup"]).abs().max()) <= 5e-6       # same round trip as grid_sample
+    else:
+        want = O.corr_lookup([l.float() for l in levels], g["flow"])
+        assert float((got - want).abs().max()) <= 1e-4
+
+
+def test_block_end_to_end_G5(P):
+    """BASELINE config 2 shape: (5, D, 80, 128), D in {128, 256}, flow in [-40, 0], r=4, 4 levels."""
+    for D, seed in ((128, 1), (256, 2)):
+        g = torch.Generator().manual_seed(seed)
+        f1 = torch.randn(5, D, 80, 128, generator=g).bfloat16()
+        f2 = torch.randn(5, D, 80, 128, generator=g).bfloat16()
+        flow = torch.zeros(5, 2, 80, 128)
+        flow[:, 0] = torch.rand(5, 80, 128, generator=g) * -40.0
+        blk = P.CorrBlock1D(f1.cuda(), f2.cuda())
+        out = blk(flow.cuda()).cpu()
+        want_lv = O.corr_pyramid(f1.float(), f2.float(), mode="bf16")
+        want = O.corr_lookup(want_lv, flow)
+        got_lv = flat(blk.corr_pyramid)
+        for l in range(5):
+            assert rel(got_lv[l], want_lv[l]) <= 1e-3
+        # lookup of the kernel's own volume, exact interpolation check
+        want_own = O.corr_lookup(got_lv, flow)
+        assert float((out - want_own).abs().max()) <= 1e-4
+        assert rel(out, want) <= 1e-3
+        c = P.CorrBlock1D.corr(f1.cuda(), f2.cuda())
+        assert tuple(c.shape) == (5, 80, 128, 1, 128)
+        assert torch.equal(c.reshape(-1, 128).float().cpu(), got_lv[0])
+
+
+def test_full_size_properties_G720(P):
+    """(20, 256, 184, 320) bf16: pooling identity on every level + sampled rows vs the oracle."""
+    g = torch.Generator(device="cuda").manual_seed(3)
+    f1 = torch.randn(20, 256, 184, 320, generator=g, device="cuda").bfloat16()
+    f2 = torch.randn(20, 256, 184, 320, generator=g, device="cuda").bfloat16()
+    lv = P.build_pyramid(f1, f2, 4, out_dtype=torch.float32)
+    for l in range(4):
+        a = lv[l].reshape(-1, lv[l].shape[-1])
+        w = a.shape[1] // 2
+        pooled = (a[:, 0:2 * w:2] + a[:, 1:2 * w:2]) * 0.5
+        assert torch.equal(pooled, lv[l + 1].reshape(-1, w)), l            # bit-exact in fp32
+    rows = torch.randint(0, 20 * 184, (48,), generator=torch.Generator().manual_seed(4))
+    L0 = lv[0].reshape(20 * 184, 320, 320)
+    for r in rows.tolist():
+        b, h = divmod(r, 184)
+        want = (f1[b, :, h].float().t().cpu() @ f2[b, :, h].float().cpu()) / 16.0
+        assert rel(L0[r].cpu(), want) <= 1e-5
+    # lookup at full size: out-of-range taps give exact zeros, in-range centre tap is a lerp of L0
+    flow = torch.zeros(20, 2, 184, 320, device="cuda")
+    flow[:, 0] = -1000.0
+    blk_out = P.lookup(lv, flow, W2=320)
+    assert float(blk_out.abs().max()) == 0.0
+    flow[:, 0] = 0.0
+    out = P.lookup(lv, flow, W2=320)
+    diag = L0[:, torch.arange(320), torch.arange(320)].reshape(20, 184, 320)
+    assert float((out[:, 4] - diag).abs().max()) <= 1e-5                  # level 0, k = 0 -> corr[i, i]
+
+
+def test_errors(P):
+    f = torch.zeros(1, 16, 2, 8, device="cuda")
+    with pytest.raises(RuntimeError, match="too small"):
+        P.CorrBlock1D(f, f)                                                 # reference: W/16 >= 1
+    with pytest.raises(RuntimeError, match="dtype"):
+        P.CorrBlock1D(f.half(), f.half())

@@ -1,0 +1,181 @@
+"""GPU parity tests for K3 (QAM score, top-k pick, key modulation, softmax aggregation, residual),
+through the C ABI, against the reference-generated goldens and the CPU oracle.
+
+Bars (north_star): top-k frame indices bit-exact; aggregation within bf16 rounding of the
+FlashAttention-2 arithmetic the reference calls (P and the output are bf16 there), stated per test.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import ppm_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def P():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import ppmstereo_b200 as P
+    return P
+
+
+def bf16_from_bits(a):
+    return torch.from_numpy(a.astype(np.int16)).view(torch.bfloat16).float()
+
+
+def set_p_mode(in_tmem: bool):
+    from ppmstereo_b200 import _lib
+    lib = _lib.load()
+    import ctypes
+    lib.ppm_debug_set_p_in_tmem.restype = ctypes.c_int
+    lib.ppm_debug_set_p_in_tmem.argtypes = [ctypes.c_int]
+    lib.ppm_debug_set_p_in_tmem(1 if in_tmem else 0)
+
+
+def run_read(P, t, top_k=5, scale=None, beta=0.5):
+    mem = P.PPMMemory(t["query"].cuda(), t["key"].cuda(), None, top_k=top_k)
+    strive = t["strive_before"].clone().cuda()
+    out, mask = mem.read(t["value"].cuda(), t["motion_features"].cuda(), t["sim"].cuda(), strive,
+                         t["uncertainty"].cuda(), torch.tensor([beta], device="cuda"), scale)
+    torch.cuda.synchronize()
+    return mem, out.cpu(), mask.cpu(), strive.cpu()
+
+
+@pytest.mark.parametrize("name", ["ppm_read_l16", "ppm_read_l08"])
+@pytest.mark.parametrize("p_in_tmem", [True, False])
+def test_read_vs_reference_golden(P, golden_dir, name, p_in_tmem):
+    g = dict(np.load(os.path.join(golden_dir, name + ".npz")))
+    t = {k: torch.from_numpy(v) for k, v in g.items() if v.dtype != np.uint16 and v.ndim > 0}
+    b, c, T, h, w = t["query"].shape
+    hw = h * w
+    set_p_mode(p_in_tmem)
+    try:
+        mem, out, mask, strive = run_read(P, t)
+    finally:
+        set_p_mode(True)
+    assert float((mem.frame_score.cpu() - t["frame_score"]).abs().max()) <= 1e-6
+    assert torch.equal(mask, t["mask"])                                    # bit-exact top-k sets
+    top5 = torch.sort(t["argsort"][..., :5], dim=-1).values[:, 0].int()
+    assert torch.equal(mem.picked.cpu(), top5)                             # bit-exact indices, ascending
+    assert torch.equal(strive, t["strive_before"] + t["mask"].float())
+    # modulated keys exactly as the reference fed them to flash_attn (bf16 bits)
+    kmod = bf16_from_bits(g["kmod_bf16"]).reshape(T, 5, hw, c)
+    mine = mem.k_packed.float().cpu().reshape(T, 5, hw, c)
+    assert float((mine - kmod).abs().max()) <= 2.0 ** -7 * float(kmod.abs().max())
+    assert float((mine == kmod).float().mean()) >= 0.99
+    # aggregation + residual vs the reference's motion_features_global
+    hid = bf16_from_bits(g["hidden_bf16"])                                 # T, hw, c
+    mine_hid = (out.reshape(T, c, hw) - t["motion_features"][0].permute(1, 0, 2, 3).reshape(T, c, hw)) / 0.5
+    d = (mine_hid.permute(0, 2, 1) - hid).abs()
+    assert float(d.max()) <= 2e-2 * float(hid.abs().max()), float(d.max())
+    assert float(d.mean()) <= 2e-3 * float(hid.abs().mean()) + 1e-6
+    ref = t["motion_features_global"]
+    assert float((out - ref).abs().max()) <= 1e-2 * float(hid.abs().max())
+
+
+def make_case(b, T, h, w, seed, peaky=False):
+    g = torch.Generator().manual_seed(seed)
+    q = torch.randn(b, 128, T, h, w, generator=g)
+    k = q + 0.1 * torch.randn(b, 128, T, h, w, generator=g) if peaky else torch.randn(b, 128, T, h, w, generator=g)
+    return {
+        "query": q, "key": k, "value": torch.randn(b, 128, T, h, w, generator=g),
+        "motion_features": torch.randn(b, 128, T, h, w, generator=g),
+        "uncertainty": torch.rand(b * T, 1, h, w, generator=g),
+        "sim": torch.rand(b, 1, T, T, generator=g) * 2 - 1,
+        "strive_before": torch.ones(b, 1, T, T) + torch.randint(0, 3, (b, 1, T, T), generator=g).float(),
+    }
+
+
+def check_vs_oracle(P, t, top_k=5, rows=None, scale=None):
+    b, c, T, h, w = t["query"].shape
+    want = O.ppm_memory_read(t["query"], t["key"], O.temporal_pe(T, c), t["value"], t["motion_features"],
+                             t["sim"], t["strive_before"], t["uncertainty"], 0.5, scale=scale, top_k=top_k,
+                             rows=rows)
+    mem, out, mask, strive = run_read(P, t, top_k=top_k, scale=scale)
+    assert float((mem.frame_score.cpu() - want["frame_score"]).abs().max()) <= 2e-6
+    gap = torch.sort(want["frame_score"], dim=-1, descending=True).values
+    K = min(top_k, T)
+    if K < T:
+        assert float((gap[..., K - 1] - gap[..., K]).min()) > 1e-5           # pick is well-posed
+    assert torch.equal(mask, want["mask"])
+    assert torch.equal(mem.picked.cpu().long()[..., :K], want["picked"])
+    assert torch.equal(strive, want["strive"])
+    assert float((mem.score_norm.cpu()[..., :K] - want["score_norm"]).abs().max()) <= 1e-6
+    got = out.reshape(b, T, c, h * w)
+    ref = want["motion_features_global"].reshape(b, T, c, h * w)
+    if rows is not None:
+        got, ref = got[..., rows], ref[..., rows]
+    hmax = float(want["hidden"].abs().max())
+    d = (got - ref).abs()
+    assert float(d.max()) <= 1e-2 * hmax + 1e-6, (float(d.max()), hmax)
+    assert float(d.mean()) <= 1e-3 * hmax + 1e-7
+    return out
+
+
+@pytest.mark.parametrize("p_in_tmem", [True, False])
+def test_ragged_tiles_batch2(P, p_in_tmem):
+    """hw = 13*23 = 299: partial query and key tiles; b = 2 couples score_norm across the batch."""
+    set_p_mode(p_in_tmem)
+    try:
+        check_vs_oracle(P, make_case(2, 8, 13, 23, seed=11))
+    finally:
+        set_p_mode(True)
+
+
+def test_peaky_softmax_rescale_path(P):
+    """key ~ query: sharply peaked rows; a large scale forces running-max growth > 2^8 (lazy rescale)."""
+    check_vs_oracle(P, make_case(1, 7, 16, 24, seed=12, peaky=True), scale=1.0)
+
+
+def test_T_below_topk_picks_everything(P):
+    t = make_case(1, 3, 8, 16, seed=13)
+    out = check_vs_oracle(P, t)
+    assert torch.isfinite(out).all()
+
+
+@pytest.mark.parametrize("top_k", [4, 8, 16])
+def test_config3_sweep_sampled_rows(P, top_k):
+    """BASELINE config 3: hw = 92*160 = 14720, T = 20, K in {4, 8, 16}; 192 sampled query rows per frame
+    against the oracle (full rows would be 0.4-1.8 TFLOP per frame on the CPU)."""
+    t = make_case(1, 20, 92, 160, seed=20 + top_k)
+    rows = torch.randperm(92 * 160, generator=torch.Generator().manual_seed(5))[:192]
+    check_vs_oracle(P, t, top_k=top_k, rows=rows)
+
+
+def test_qam_ties_and_strive(P):
+    """Exact ties resolve to the lower frame index; strive_time accumulates over iterations."""
+    b, T, h, w = 1, 6, 8, 16
+    t = make_case(b, T, h, w, seed=14)
+    t["sim"] = torch.zeros(b, 1, T, T)
+    t["uncertainty"] = torch.full((b * T, 1, h, w), 0.25)
+    t["strive_before"] = torch.ones(b, 1, T, T)
+    mem = P.PPMMemory(t["query"].cuda(), t["key"].cuda(), None, top_k=5)
+    strive = t["strive_before"].clone().cuda()
+    for it in range(3):
+        mask = mem.pick(t["sim"].cuda(), strive, t["uncertainty"].cuda()).cpu()
+        assert torch.equal(mem.picked.cpu()[0, 0], torch.arange(5, dtype=torch.int32))
+        assert int(mask.sum()) == T * 5
+    assert torch.equal(strive.cpu()[0, 0, 0], torch.tensor([4.0, 4, 4, 4, 4, 1]))
+
+
+def test_linearity_in_value_full_size(P):
+    """Size-independent property at the 1/8-res 720p shape: the read is linear in V (up to bf16)."""
+    t = make_case(1, 20, 92, 160, seed=30)
+    mem = P.PPMMemory(t["query"].cuda(), t["key"].cuda(), None, top_k=5)
+    strive = t["strive_before"].clone().cuda()
+    mem.pick(t["sim"].cuda(), strive, t["uncertainty"].cuda())
+    zero = torch.zeros_like(t["value"]).cuda()
+    one = torch.tensor([1.0], device="cuda")
+    v1, v2 = t["value"].cuda(), t["motion_features"].cuda()
+    a = mem.attend(v1, zero, one)
+    b2 = mem.attend(v2, zero, one)
+    ab = mem.attend(v1 + v2, zero, one)
+    const = mem.attend(torch.full_like(v1, 0.75), zero, one)
+    assert float((const - 0.75).abs().max()) <= 0.75 * 2.0 ** -7              # softmax weights sum to 1
+    scale = float(ab.abs().max())
+    assert float((a + b2 - ab).abs().max()) <= 3e-2 * scale
+    assert float((a + b2 - ab).abs().mean()) <= 3e-3 * scale
