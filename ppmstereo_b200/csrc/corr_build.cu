@@ -51,12 +51,20 @@ template <> struct CbTraits<__nv_bfloat16> {
   static constexpr int kKC = 32;        // channels per stage
   static constexpr int kUK = 16;        // channels per MMA
   static constexpr uint32_t kFmt = 1;   // BF16
+  static constexpr uint32_t kLayout = 2;     // SWIZZLE_128B (16-byte atoms), 8 channel rows per swizzle group
+  static constexpr uint32_t kSbo = 1024;
+  static constexpr CUtensorMapSwizzle kTmaSwizzle = CU_TENSOR_MAP_SWIZZLE_128B;
 };
 template <> struct CbTraits<float> {
   static constexpr int kChunkW = 32;
   static constexpr int kKC = 16;
   static constexpr int kUK = 8;
   static constexpr uint32_t kFmt = 2;   // TF32
+  // MN-major 32-bit operands must use the 32-byte-atom flavour of the 128-byte swizzle
+  // (UMMA SWIZZLE_128B_BASE32B == TMA SWIZZLE_128B_ATOM_32B): 4 channel rows per swizzle group.
+  static constexpr uint32_t kLayout = 1;
+  static constexpr uint32_t kSbo = 512;
+  static constexpr CUtensorMapSwizzle kTmaSwizzle = CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B;
 };
 
 __device__ __forceinline__ float cb_round(float v, float) { return v; }
@@ -128,9 +136,9 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
         const uint32_t b0 = a0 + kABytes;
         #pragma unroll
         for (int k = 0; k < Tr::kKC / Tr::kUK; ++k) {
-          // MN-major SW128: LBO = stride between 128-byte MN chunks, SBO = 8 channel rows
-          const uint64_t ad = umma_desc_sw128(a0 + k * Tr::kUK * 128, kChunkBytes, 1024);
-          const uint64_t bd = umma_desc_sw128(b0 + k * Tr::kUK * 128, kChunkBytes, 1024);
+          // MN-major: LBO = stride between 128-byte MN chunks, SBO = one swizzle group of channel rows
+          const uint64_t ad = umma_desc_sw128(a0 + k * Tr::kUK * 128, kChunkBytes, Tr::kSbo, Tr::kLayout);
+          const uint64_t bd = umma_desc_sw128(b0 + k * Tr::kUK * 128, kChunkBytes, Tr::kSbo, Tr::kLayout);
           if constexpr (Tr::kFmt == 2) umma_tf32_ss(tmem_base, ad, bd, idesc, (kc | k) != 0);
           else                         umma_f16_ss(tmem_base, ad, bd, idesc, (kc | k) != 0);
         }
@@ -228,14 +236,14 @@ static int launch_corr_build(const void* f1, const void* f2, int B, int D, int H
     const uint64_t dims[4] = {(uint64_t)W1, (uint64_t)H, (uint64_t)D, (uint64_t)B};
     const uint64_t str[3] = {(uint64_t)ld1 * sizeof(ElemT), (uint64_t)ld1 * H * sizeof(ElemT),
                              (uint64_t)ld1 * H * D * sizeof(ElemT)};
-    int rc = make_tensor_map(&m1, dt, 4, f1, dims, str, box, CU_TENSOR_MAP_SWIZZLE_128B);
+    int rc = make_tensor_map(&m1, dt, 4, f1, dims, str, box, Tr::kTmaSwizzle);
     if (rc) return rc;
   }
   {
     const uint64_t dims[4] = {(uint64_t)W2, (uint64_t)H, (uint64_t)D, (uint64_t)B};
     const uint64_t str[3] = {(uint64_t)ld2 * sizeof(ElemT), (uint64_t)ld2 * H * sizeof(ElemT),
                              (uint64_t)ld2 * H * D * sizeof(ElemT)};
-    int rc = make_tensor_map(&m2, dt, 4, f2, dims, str, box, CU_TENSOR_MAP_SWIZZLE_128B);
+    int rc = make_tensor_map(&m2, dt, 4, f2, dims, str, box, Tr::kTmaSwizzle);
     if (rc) return rc;
   }
   auto kern = corr_build_kernel<ElemT, OutT>;

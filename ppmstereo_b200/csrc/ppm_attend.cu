@@ -30,7 +30,7 @@ constexpr int kAtTileBytes = kAtTile * kAtTile * 2;   // 32 KB: two [128 rows][1
 constexpr int kAtHalfBytes = kAtTileBytes / 2;
 constexpr int kAtKStages = 2, kAtVStages = 2;
 constexpr uint32_t kTmemS = 0, kTmemO = 256, kTmemCols = 512;
-constexpr float kRescaleThreshold = 8.0f;         // log2 units
+constexpr float kRescaleThreshold = 8.0f;         // log2 units (default; see AttendParams::rescale_thr)
 
 struct AttendParams {
   const int32_t* picked;     // (b*T, Kp)
@@ -39,6 +39,7 @@ struct AttendParams {
   const float* beta;
   float* out;                // (b*T, 128, hw)
   float scale_log2;          // softmax_scale * log2(e)
+  float rescale_thr;         // lazy-rescale threshold, log2 units
   int T, Kp, hw;
 };
 
@@ -56,7 +57,7 @@ ppm_attend_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
   uint8_t* sV = sK + kAtKStages * kAtTileBytes;
   uint8_t* sP = sV + kAtVStages * kAtTileBytes;   // only used when !kPInTmem
   __shared__ uint64_t bar_q, bar_kf[kAtKStages], bar_ke[kAtKStages], bar_vf[kAtVStages], bar_ve[kAtVStages];
-  __shared__ uint64_t bar_sf[2], bar_pf[2], bar_o;
+  __shared__ uint64_t bar_sf[2], bar_pf[2], bar_o[2];
   __shared__ uint32_t tmem_slot;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -73,7 +74,7 @@ ppm_attend_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
     for (int s = 0; s < kAtKStages; ++s) { mbar_init(&bar_kf[s], 1); mbar_init(&bar_ke[s], 1); }
     for (int s = 0; s < kAtVStages; ++s) { mbar_init(&bar_vf[s], 1); mbar_init(&bar_ve[s], 1); }
     for (int s = 0; s < 2; ++s) { mbar_init(&bar_sf[s], 1); mbar_init(&bar_pf[s], 4); }
-    mbar_init(&bar_o, 1);
+    mbar_init(&bar_o[0], 1); mbar_init(&bar_o[1], 1);
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc<kTmemCols>(&tmem_slot);
@@ -146,7 +147,7 @@ ppm_attend_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
             umma_f16_ss(tmem + kTmemO, umma_desc_sw128(smem_u32(sP) + off, 16, 1024), vd, idesc, (j | k) != 0);
         }
         umma_commit(&bar_ve[vs]);
-        umma_commit(&bar_o);
+        umma_commit(&bar_o[j & 1]);
       }
     }
   } else {
@@ -155,7 +156,7 @@ ppm_attend_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
     const int row = quarter * 32 + lane;                 // query row in the tile == TMEM lane
     const uint32_t lane_base = static_cast<uint32_t>(quarter * 32) << 16;
     const float c1 = p.scale_log2;
-    const float thr = kRescaleThreshold / c1;            // in raw-score units
+    const float thr = p.rescale_thr / c1;            // in raw-score units
     float m_used = -INFINITY, l_sum = 0.f;
     for (int j = 0; j < n_tiles; ++j) {
       const int t = j % tiles_per_frame;
@@ -174,6 +175,9 @@ ppm_attend_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
         for (int e = 0; e < 32; ++e)
           if (c * 32 + e < valid) mx = fmaxf(mx, __uint_as_float(s[c][e]));
       const bool grow = mx > m_used + thr;               // also true on the first tile (-inf)
+      // "P.V of tile j-1 has landed in O" is waited for exactly once per tile by every warp (early
+      // when O must be rescaled, late otherwise), so no phase of bar_o is ever skipped.
+      bool o_waited = (j == 0);
       if (__any_sync(0xffffffffu, grow)) {
         float alpha = 1.f;
         if (grow) {
@@ -182,7 +186,8 @@ ppm_attend_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
           l_sum *= alpha;
         }
         if (j > 0) {
-          mbar_wait(&bar_o, (j - 1) & 1);                // P.V of tile j-1 has landed in O
+          mbar_wait(&bar_o[(j - 1) & 1], ((j - 1) >> 1) & 1);
+          o_waited = true;
           tc_fence_after();
           #pragma unroll
           for (int c = 0; c < 4; ++c) {
@@ -213,7 +218,7 @@ ppm_attend_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
         tmem_st_x32(s_addr + 32, *reinterpret_cast<const uint32_t(*)[32]>(&pk[32]));
         tmem_st_wait();
       } else {
-        if (j > 0) mbar_wait(&bar_o, (j - 1) & 1);       // P.V of tile j-1 no longer reads sP
+        if (!o_waited) { mbar_wait(&bar_o[(j - 1) & 1], ((j - 1) >> 1) & 1); o_waited = true; }   // sP is free again
         #pragma unroll
         for (int ch = 0; ch < 16; ++ch) {                 // 16-byte chunks of this row, SWIZZLE_128B
           uint8_t* dst = sP + (ch >> 3) * kAtHalfBytes + row * 128 + (((ch & 7) ^ (row & 7)) << 4);
@@ -222,13 +227,14 @@ ppm_attend_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
         fence_proxy_async_smem();
         tmem_st_wait();
       }
+      if (!o_waited) mbar_wait(&bar_o[(j - 1) & 1], ((j - 1) >> 1) & 1);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&bar_pf[j & 1]);
     }
     // ---- epilogue: out = mf + beta * bf16(O / l)
     if (n_tiles > 0) {
-      mbar_wait(&bar_o, (n_tiles - 1) & 1);
+      mbar_wait(&bar_o[(n_tiles - 1) & 1], ((n_tiles - 1) >> 1) & 1);
       tc_fence_after();
     }
     const float inv = n_tiles > 0 ? 1.f / l_sum : 0.f;
@@ -276,11 +282,14 @@ static int launch_attend(const CUtensorMap& mq, const CUtensorMap& mk, const CUt
 }
 
 static int g_p_in_tmem = 1;
+static float g_rescale_thr = kRescaleThreshold;
 
 }  // namespace ppm
 
 // Test hook: choose how P reaches the P.V MMA (1 = TMEM operand, 0 = shared memory operand).
 extern "C" int ppm_debug_set_p_in_tmem(int v) { ppm::g_p_in_tmem = v ? 1 : 0; return PPM_OK; }
+// Test hook: lazy-rescale threshold in log2 units (0 = rescale whenever the running max grows).
+extern "C" int ppm_debug_set_rescale_threshold(float v) { ppm::g_rescale_thr = v; return PPM_OK; }
 
 extern "C" int ppm_memory_attend(const void* Q, const void* K, const void* V, const int32_t* picked, const void* mf,
                                  int mf_dtype, int64_t mb, int64_t mc, int64_t mt, const float* beta, float scale,
@@ -313,6 +322,7 @@ extern "C" int ppm_memory_attend(const void* Q, const void* K, const void* V, co
   AttendParams p{};
   p.picked = picked; p.mf = mf; p.mb = mb; p.mc = mc; p.mt = mt; p.beta = beta; p.out = out;
   p.scale_log2 = scale * 1.4426950408889634f;
+  p.rescale_thr = g_rescale_thr;
   p.T = T; p.Kp = Kp; p.hw = hw;
   const int n_qtiles = (hw + kAtTile - 1) / kAtTile;
   cudaStream_t st = static_cast<cudaStream_t>(stream);

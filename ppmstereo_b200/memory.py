@@ -97,30 +97,44 @@ class PPMMemory:
                    "ppm_qam_pick")
         return self.mask.bool()
 
-    def attend(self, value: torch.Tensor, motion_features: torch.Tensor, beta: torch.Tensor,
-               scale: Optional[float] = None) -> torch.Tensor:
-        """Modulate + aggregate with the current pick; returns (b*T, 128, h, w) fp32."""
+    def pack_kv(self, value: torch.Tensor) -> None:
+        """Per-iteration operand prep: modulated keys for the current pick and bf16 values."""
         b, T, hw = self.b, self.T, self.hw
         value, *vs = _bcthw(value, "value")
-        mf, *ms = _bcthw(motion_features, "motion_features")
-        if value.shape != self.query.shape or mf.shape != self.query.shape:
-            raise RuntimeError("value / motion_features must have the query's (b, c, T, h, w) shape")
-        if not torch.is_tensor(beta):
-            beta = torch.tensor([float(beta)], device=value.device)
-        beta = beta.detach().float().reshape(-1)[:1].contiguous().to(value.device)
-        scale = softmax_scale(C) if scale is None else float(scale)
+        if value.shape != self.query.shape:
+            raise RuntimeError("value must have the query's (b, c, T, h, w) shape")
         st = _lib.stream_ptr()
         _lib.check(self.lib.ppm_pack_key(self.key.data_ptr(), _lib.dtype_code(self.key), *self.k_strides,
                                          self.pe.data_ptr(), self.picked.data_ptr(), self.score_norm.data_ptr(),
                                          b, T, self.top_k, hw, self.k_packed.data_ptr(), st), "ppm_pack_key")
         _lib.check(self.lib.ppm_pack_value(value.data_ptr(), _lib.dtype_code(value), *vs, b, T, hw,
                                            self.v_packed.data_ptr(), st), "ppm_pack_value")
-        out = torch.empty(b * T, C, self.h, self.w, dtype=torch.float32, device=value.device)
+
+    def aggregate(self, motion_features: torch.Tensor, beta: torch.Tensor,
+                  scale: Optional[float] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """ppm_memory_attend on the packed operands; returns (b*T, 128, h, w) fp32."""
+        b, T, hw = self.b, self.T, self.hw
+        mf, *ms = _bcthw(motion_features, "motion_features")
+        if mf.shape != self.query.shape:
+            raise RuntimeError("motion_features must have the query's (b, c, T, h, w) shape")
+        if not torch.is_tensor(beta):
+            beta = torch.tensor([float(beta)], device=mf.device)
+        beta = beta.detach().float().reshape(-1)[:1].contiguous().to(mf.device)
+        scale = softmax_scale(C) if scale is None else float(scale)
+        if out is None:
+            out = torch.empty(b * T, C, self.h, self.w, dtype=torch.float32, device=mf.device)
         _lib.check(self.lib.ppm_memory_attend(self.q_packed.data_ptr(), self.k_packed.data_ptr(),
                                               self.v_packed.data_ptr(), self.picked.data_ptr(), mf.data_ptr(),
                                               _lib.dtype_code(mf), *ms, beta.data_ptr(), scale, b, T,
-                                              self.top_k, hw, out.data_ptr(), st), "ppm_memory_attend")
+                                              self.top_k, hw, out.data_ptr(), _lib.stream_ptr()),
+                   "ppm_memory_attend")
         return out
+
+    def attend(self, value: torch.Tensor, motion_features: torch.Tensor, beta: torch.Tensor,
+               scale: Optional[float] = None) -> torch.Tensor:
+        """Modulate + aggregate with the current pick; returns (b*T, 128, h, w) fp32."""
+        self.pack_kv(value)
+        return self.aggregate(motion_features, beta, scale)
 
     def read(self, value, motion_features, sim, strive, uncertainty, beta, scale=None):
         mask = self.pick(sim, strive, uncertainty)
