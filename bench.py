@@ -1,0 +1,342 @@
+"""bench.py — frames/s of the PPMStereo hot path (correlation pyramid + lookup + PPM memory read)
+on synthetic 720p 40-frame clips, one process per GPU.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+A "step" is one pass of the hot path over one 40-frame 720x1280 clip exactly as
+PPMStereoModel.forward schedules it (reference models/core/ppmstereo.py:238-320, :601-810):
+4 temporal windows [20, 20, 20, 10 frames], per window 3 cascade levels (1/16, 1/8, 1/4 of the
+736x1280 padded image) with iters//2, iters//2, iters = 10, 10, 20 update iterations; per level one
+correlation-pyramid build + one query pack, per iteration one lookup + one QAM pick + K'/V pack
++ one memory read over all T query frames.  The PyTorch glue between the kernels (encoders,
+GRU) is not part of the path and is not run; its outputs are replaced by synthetic tensors of
+the shapes and dtypes the autocast model hands over (bf16 features/values, fp32 flow).
+At N > 1 every rank processes its own clip (weak scaling, no data-path collective).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "frames/s @720p 40-frame clips (hot path: corr pyramid + lookup + PPM memory read)"
+CLIP_FRAMES, KERNEL_SIZE, ITERS, TOP_K, D_FEAT, C_QKV = 40, 20, 20, 5, 256, 128
+PAD_H, PAD_W = 736, 1280                      # 720 -> 736 rows (InputPadder divis_by=32, utils.py:22-38)
+LEVELS = [(16, ITERS // 2), (8, ITERS // 2), (4, ITERS)]   # (downscale, iterations)
+
+
+def clip_windows():
+    w, stride = [], KERNEL_SIZE // 2
+    for i in range(0, CLIP_FRAMES, stride):
+        w.append(len(range(i, min(i + KERNEL_SIZE, CLIP_FRAMES))))
+    return w                                     # [20, 20, 20, 10]
+
+
+def attention_flops(T: int, hw: int, k: int = TOP_K) -> float:
+    """4*K*c*hw^2 per query frame (QK^T + PV, 2 FLOP/MAC), T query frames per launch."""
+    return 4.0 * min(k, T) * C_QKV * float(hw) ** 2 * T
+
+
+def clip_attention_flops() -> float:
+    tot = 0.0
+    for T in clip_windows():
+        for ds, it in LEVELS:
+            tot += it * attention_flops(T, (PAD_H // ds) * (PAD_W // ds))
+    return tot
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return d, "measured (MEASURED_PEAKS.json)"
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu, self.proc, self.lines = gpu_index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200", "-i", str(self.gpu)], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=lambda: self.lines.extend(self.proc.stdout), daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        load = [x for x in sm if x >= 0.5 * (mx[0] if mx else 1)] or sm
+        return {"sm_mhz": load[len(load) // 2] if load else None, "sm_max_mhz": mx[0] if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# --------------------------------------------------------------------------------------------
+# our arm: the CUDA path through the public Python API (which calls the C ABI)
+# --------------------------------------------------------------------------------------------
+class LevelInputs:
+    """Synthetic inputs of one (window length T, cascade level) in pinned host memory and in HBM."""
+    NAMES = ("fmap1", "fmap2", "query", "key", "value", "mf", "unc", "flow_a", "flow_b", "sim")
+
+    def __init__(self, T: int, ds: int, seed: int, device):
+        h, w = PAD_H // ds, PAD_W // ds
+        self.T, self.h, self.w, self.ds = T, h, w, ds
+        g = torch.Generator(device=device).manual_seed(seed)
+        rn = lambda *shape: torch.randn(*shape, generator=g, device=device)
+        dev = {
+            "fmap1": rn(T, D_FEAT, h, w).bfloat16(), "fmap2": rn(T, D_FEAT, h, w).bfloat16(),
+            "query": rn(1, C_QKV, T, h, w).bfloat16(), "key": rn(1, C_QKV, T, h, w).bfloat16(),
+            "value": rn(1, C_QKV, T, h, w).bfloat16(), "mf": rn(1, C_QKV, T, h, w).bfloat16(),
+            "unc": torch.rand(T, 1, h, w, generator=g, device=device).bfloat16(),
+            "sim": torch.rand(1, 1, T, T, generator=g, device=device) * 2 - 1,
+        }
+        for n in ("flow_a", "flow_b"):
+            f = torch.zeros(T, 2, h, w, device=device)
+            f[:, 0] = torch.rand(T, h, w, generator=g, device=device) * (-160.0 / ds)
+            dev[n] = f
+        self.dev = dev
+        self.host = {k: torch.empty(v.shape, dtype=v.dtype, pin_memory=True).copy_(v) for k, v in dev.items()}
+        self.in_bytes = sum(v.numel() * v.element_size() for v in dev.values())
+        self.out_bytes = T * C_QKV * h * w * 4 + T * 36 * h * w * 4
+
+
+class Counters:
+    launches = 0
+    attend_events = []          # (start, end) CUDA events of the 1/4-res memory-read launches
+
+
+def run_level(P, x, iters: int, beta, from_host: bool, time_attend: bool):
+    """One cascade level of one window.  Returns the tensors a caller would read back."""
+    src = x.host if from_host else x.dev
+    t = {k: (v.cuda(non_blocking=True) if from_host else v) for k, v in src.items()}
+    blk = P.CorrBlock1D(t["fmap1"], t["fmap2"])                       # K1
+    mem = P.PPMMemory(t["query"], t["key"], None, top_k=TOP_K)          # pack Q' once per level
+    strive = torch.ones_like(t["sim"])
+    Counters.launches += 2
+    out = corr = None
+    for it in range(iters):
+        corr = blk(t["flow_a"] if it % 2 == 0 else t["flow_b"])         # K2
+        mem.pick(t["sim"], strive, t["unc"])                            # K3a (2 launches)
+        mem.pack_kv(t["value"])                                         # K3b (2 launches)
+        if time_attend:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+        out = mem.aggregate(t["mf"], beta, out=out)                     # K3c
+        if time_attend:
+            e1.record()
+            Counters.attend_events.append((e0, e1))
+        Counters.launches += 6
+    if from_host:
+        return out.cpu(), corr.cpu()
+    return out, corr
+
+
+def run_clip(P, inputs, beta, from_host: bool, time_attend: bool = False):
+    for T in clip_windows():
+        for ds, iters in LEVELS:
+            run_level(P, inputs[(T, ds)], iters, beta, from_host, time_attend and ds == 4 and T == KERNEL_SIZE)
+
+
+# --------------------------------------------------------------------------------------------
+# CPU arm: the oracle port of the reference's path on the host cores (bounded sample)
+# --------------------------------------------------------------------------------------------
+SAMPLE_DS, SAMPLE_T = 16, KERNEL_SIZE
+SAMPLE_DESC = ("one update iteration of the 1/16-res level of a 20-frame 720p window (h x w = 46 x 80, hw = 3680, "
+               "T = 20, K = 5): corr pyramid build + lookup + full PPM read, oracle/ppm_oracle.py (port of the "
+               "reference's PyTorch CPU path) on all host threads; frames/s extrapolated to the 40-frame clip by "
+               "attention FLOPs")
+
+
+def make_cpu_sample(seed: int = 0):
+    h, w, T = PAD_H // SAMPLE_DS, PAD_W // SAMPLE_DS, SAMPLE_T
+    g = torch.Generator().manual_seed(seed)
+    rn = lambda *s: torch.randn(*s, generator=g)
+    flow = torch.zeros(T, 2, h, w)
+    flow[:, 0] = torch.rand(T, h, w, generator=g) * -10.0
+    return dict(f1=rn(T, D_FEAT, h, w), f2=rn(T, D_FEAT, h, w), q=rn(1, C_QKV, T, h, w), k=rn(1, C_QKV, T, h, w),
+                v=rn(1, C_QKV, T, h, w), mf=rn(1, C_QKV, T, h, w), unc=torch.rand(T, 1, h, w, generator=g),
+                sim=torch.rand(1, 1, T, T, generator=g) * 2 - 1, strive=torch.ones(1, 1, T, T), flow=flow)
+
+
+def cpu_sample_step(s) -> float:
+    from oracle import ppm_oracle as O          # the CPU baseline is the one place bench.py runs the oracle
+    t0 = time.perf_counter()
+    lv = O.corr_pyramid(s["f1"], s["f2"], mode="bf16")
+    O.corr_lookup(lv, s["flow"])
+    O.ppm_memory_read(s["q"], s["k"], O.temporal_pe(SAMPLE_T, C_QKV), s["v"], s["mf"], s["sim"], s["strive"],
+                      s["unc"], 0.5)
+    return time.perf_counter() - t0
+
+
+def cpu_frames_per_s(seconds_per_sample: float) -> float:
+    f_sample = attention_flops(SAMPLE_T, (PAD_H // SAMPLE_DS) * (PAD_W // SAMPLE_DS))
+    return CLIP_FRAMES / (seconds_per_sample * clip_attention_flops() / f_sample)
+
+
+def run_reference_arm(args, rank: int):
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    s = make_cpu_sample()
+    for _ in range(args.warmup):
+        cpu_sample_step(s)
+    ts = [cpu_sample_step(s) for _ in range(args.steps)]
+    sec = sum(ts) / len(ts)
+    v = cpu_frames_per_s(sec)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": "frames/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": workload_config(args.gpus),
+        "cpu_baseline": {"value": v, "unit": "frames/s", "cores": cores, "kind": "port", "sample": SAMPLE_DESC},
+        "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+def workload_config(n_gpus: int):
+    return {"workload": "hot path of PPMStereoModel.forward on one synthetic 40-frame 720x1280 clip per GPU "
+                        "(BASELINE configs[3]/[4]): 4 windows [20,20,20,10], levels 1/16,1/8,1/4 of 736x1280, "
+                        "iters 10/10/20, D=256 bf16 features, c=128, top-5 of T frames",
+            "clips_per_gpu": 1, "kernel_size": KERNEL_SIZE, "iters": ITERS, "top_k": TOP_K,
+            "parallelism": f"clip-sharded x{n_gpus} (no data-path collective)",
+            "l2_policy": "inputs larger than L2 (per-window working set > 3 GB vs 126 MB L2), no flush needed"}
+
+
+# --------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference_arm(args, rank)
+        return
+
+    import torch.distributed as dist
+    import ppmstereo_b200 as P          # fails loudly without libppm_sm100.so
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    inputs = {(T, ds): LevelInputs(T, ds, 1000 * rank + 10 * T + ds, dev)
+              for T in sorted(set(clip_windows())) for ds, _ in LEVELS}
+    beta = torch.tensor([0.5], device=dev)
+    h2d = sum(inputs[(T, ds)].in_bytes for T in clip_windows() for ds, _ in LEVELS)
+    d2h = sum(inputs[(T, ds)].out_bytes for T in clip_windows() for ds, _ in LEVELS)
+
+    def timed(from_host: bool, steps: int, time_attend: bool):
+        barrier()
+        sampler = ClockSampler(local)
+        if rank == 0 and not from_host:
+            sampler.start()
+        Counters.launches = 0
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            run_clip(P, inputs, beta, from_host, time_attend)
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        clocks = sampler.stop() if rank == 0 and not from_host else None
+        return float(ms) / steps, clocks
+
+    for _ in range(args.warmup):
+        run_clip(P, inputs, beta, False)
+    Counters.attend_events.clear()
+    ms_step, clocks = timed(False, args.steps, True)
+    launches = Counters.launches // args.steps
+    att_ms = [a.elapsed_time(b) for a, b in Counters.attend_events]
+    run_clip(P, inputs, beta, True)                      # warm the pinned-copy path once
+    ms_e2e, _ = timed(True, args.steps, False)
+
+    if rank == 0:
+        pk, pk_src = peaks()
+        hw4 = (PAD_H // 4) * (PAD_W // 4)
+        fl = attention_flops(KERNEL_SIZE, hw4)
+        avg = sum(att_ms) / max(1, len(att_ms))
+        ach = fl / (avg * 1e-3) / 1e12
+        peak = float(pk.get("bf16_tflops_sustained", pk.get("bf16_tflops", 1400.0)))
+        out = {
+            "metric": METRIC, "value": world * CLIP_FRAMES / (ms_step * 1e-3), "unit": "frames/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
+            "data": "synthetic", "config": workload_config(world),
+            "e2e": {"value": world * CLIP_FRAMES / (ms_e2e * 1e-3), "unit": "frames/s",
+                    "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "note": "per window and level: inputs copied from pinned host memory, the level's final "
+                            "motion_features_global and lookup read back; copies inside the timed region"},
+            "gpu_launches": launches,
+            "clocks": clocks,
+            "roofline": {"kernel": "ppm_attend_kernel (1/4-res level, T=20, hw=58880, K=5)", "bound": "tensor",
+                         "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
+                         "peak_source": "bf16_tflops_sustained, " + pk_src, "traffic": None,
+                         "flops_per_launch": fl, "avg_launch_ms": avg, "launches_timed": len(att_ms),
+                         "share_of_step": sum(att_ms) / args.steps / ms_step},
+            "attention_tflops_whole_step": clip_attention_flops() / (ms_step * 1e-3) / 1e12,
+        }
+        if not args.no_cpu_baseline:
+            cores = os.cpu_count() or 1
+            torch.set_num_threads(cores)
+            s = make_cpu_sample()
+            cpu_sample_step(s)
+            sec = min(cpu_sample_step(s) for _ in range(2))
+            out["cpu_baseline"] = {"value": cpu_frames_per_s(sec), "unit": "frames/s", "cores": cores,
+                                   "kind": "port", "sample": SAMPLE_DESC, "sample_seconds": sec}
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
