@@ -281,6 +281,12 @@ static int launch_attend(const CUtensorMap& mq, const CUtensorMap& mk, const CUt
   return PPM_OK;
 }
 
+int attend2_dispatch(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv, const int32_t* picked,
+                     const void* mf, int mf_dtype, long long mb, long long mc, long long mt, const float* beta,
+                     float scale_log2, float rescale_thr, int b, int T, int Kp, int hw, float* out,
+                     cudaStream_t st);
+
+static int g_attend_version = 2;   // 2 = two query tiles per CTA (ppm_attend2.cu), 1 = one tile (this file)
 static int g_p_in_tmem = 1;
 static float g_rescale_thr = kRescaleThreshold;
 
@@ -288,6 +294,8 @@ static float g_rescale_thr = kRescaleThreshold;
 
 // Test hook: choose how P reaches the P.V MMA (1 = TMEM operand, 0 = shared memory operand).
 extern "C" int ppm_debug_set_p_in_tmem(int v) { ppm::g_p_in_tmem = v ? 1 : 0; return PPM_OK; }
+// Test hook: kernel generation (2 = default two-tile kernel, 1 = one-tile kernel kept for cross-checks).
+extern "C" int ppm_debug_set_attend_version(int v) { ppm::g_attend_version = v == 1 ? 1 : 2; return PPM_OK; }
 // Test hook: lazy-rescale threshold in log2 units (0 = rescale whenever the running max grows).
 extern "C" int ppm_debug_set_rescale_threshold(float v) { ppm::g_rescale_thr = v; return PPM_OK; }
 
@@ -326,6 +334,9 @@ extern "C" int ppm_memory_attend(const void* Q, const void* K, const void* V, co
   p.T = T; p.Kp = Kp; p.hw = hw;
   const int n_qtiles = (hw + kAtTile - 1) / kAtTile;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (g_attend_version == 2 && g_p_in_tmem)
+    return attend2_dispatch(mq, mk, mv, picked, mf, mf_dtype, mb, mc, mt, beta, p.scale_log2, p.rescale_thr, b, T,
+                            Kp, hw, out, st);
   if (g_p_in_tmem) {
     if (mf_dtype == PPM_BF16) return launch_attend<true, __nv_bfloat16>(mq, mk, mv, p, n_qtiles, b * T, st);
     return launch_attend<true, float>(mq, mk, mv, p, n_qtiles, b * T, st);

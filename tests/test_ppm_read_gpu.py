@@ -36,6 +36,15 @@ def set_p_mode(in_tmem: bool):
     lib.ppm_debug_set_p_in_tmem(1 if in_tmem else 0)
 
 
+def set_attend_version(v: int):
+    from ppmstereo_b200 import _lib
+    import ctypes
+    lib = _lib.load()
+    lib.ppm_debug_set_attend_version.restype = ctypes.c_int
+    lib.ppm_debug_set_attend_version.argtypes = [ctypes.c_int]
+    lib.ppm_debug_set_attend_version(v)
+
+
 def run_read(P, t, top_k=5, scale=None, beta=0.5):
     mem = P.PPMMemory(t["query"].cuda(), t["key"].cuda(), None, top_k=top_k)
     strive = t["strive_before"].clone().cuda()
@@ -125,6 +134,22 @@ def test_ragged_tiles_batch2(P, p_in_tmem):
         check_vs_oracle(P, make_case(2, 8, 13, 23, seed=11))
     finally:
         set_p_mode(True)
+
+
+def test_one_tile_and_two_tile_kernels_agree(P):
+    """The two-query-tile kernel (default) and the one-tile kernel compute the same P and O; only the
+    order of the fp32 row-sum differs (1 ulp of 1/l before the bf16 rounding of the output)."""
+    t = make_case(1, 9, 20, 31, seed=15)                  # hw = 620: 5 key tiles, 3 two-tile CTAs per frame
+    outs = []
+    for v in (2, 1):
+        set_attend_version(v)
+        try:
+            outs.append(run_read(P, t)[1])
+        finally:
+            set_attend_version(2)
+    d = (outs[0] - outs[1]).abs()
+    assert float((d == 0).float().mean()) >= 0.99
+    assert float(d.max()) <= 2.0 ** -7 * float(outs[1].abs().max())
 
 
 def test_peaky_softmax_rescale_path(P):
