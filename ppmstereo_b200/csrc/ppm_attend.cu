@@ -286,7 +286,16 @@ int attend2_dispatch(const CUtensorMap& mq, const CUtensorMap& mk, const CUtenso
                      float scale_log2, float rescale_thr, int b, int T, int Kp, int hw, float* out,
                      cudaStream_t st);
 
-static int g_attend_version = 2;   // 2 = two query tiles per CTA (ppm_attend2.cu), 1 = one tile (this file)
+int attend3_dispatch(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv, const int32_t* picked,
+                     const void* mf, int mf_dtype, long long mb, long long mc, long long mt, const float* beta,
+                     float scale_log2, float rescale_thr, int emu, int b, int T, int Kp, int hw, float* out,
+                     cudaStream_t st);
+
+// 3 = two query tiles, chunked P hand-off (ppm_attend3.cu); 2 = two query tiles (ppm_attend2.cu);
+// 1 = one tile (this file).  2 and 1 are kept for cross-checks.
+static int g_attend_version = 3;
+static int g_exp_emulation = 0;    // v3: exponentials per 8 evaluated on the FMA pipe (0, 2, 3 or 4);
+                                   // measured on B200: 0 is fastest (the softmax warps are issue-bound, not MUFU-bound)
 static int g_p_in_tmem = 1;
 static float g_rescale_thr = kRescaleThreshold;
 
@@ -294,8 +303,10 @@ static float g_rescale_thr = kRescaleThreshold;
 
 // Test hook: choose how P reaches the P.V MMA (1 = TMEM operand, 0 = shared memory operand).
 extern "C" int ppm_debug_set_p_in_tmem(int v) { ppm::g_p_in_tmem = v ? 1 : 0; return PPM_OK; }
-// Test hook: kernel generation (2 = default two-tile kernel, 1 = one-tile kernel kept for cross-checks).
-extern "C" int ppm_debug_set_attend_version(int v) { ppm::g_attend_version = v == 1 ? 1 : 2; return PPM_OK; }
+// Test hook: kernel generation (3 = default; 2 and 1 = earlier kernels kept for cross-checks).
+extern "C" int ppm_debug_set_attend_version(int v) { ppm::g_attend_version = (v >= 1 && v <= 3) ? v : 3; return PPM_OK; }
+// Test hook: how many of every 8 exponentials the v3 kernel evaluates by polynomial (0, 2, 3, 4).
+extern "C" int ppm_debug_set_exp_emulation(int n) { ppm::g_exp_emulation = n; return PPM_OK; }
 // Test hook: lazy-rescale threshold in log2 units (0 = rescale whenever the running max grows).
 extern "C" int ppm_debug_set_rescale_threshold(float v) { ppm::g_rescale_thr = v; return PPM_OK; }
 
@@ -334,7 +345,10 @@ extern "C" int ppm_memory_attend(const void* Q, const void* K, const void* V, co
   p.T = T; p.Kp = Kp; p.hw = hw;
   const int n_qtiles = (hw + kAtTile - 1) / kAtTile;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (g_attend_version == 2 && g_p_in_tmem)
+  if (g_attend_version == 3 && g_p_in_tmem)
+    return attend3_dispatch(mq, mk, mv, picked, mf, mf_dtype, mb, mc, mt, beta, p.scale_log2, p.rescale_thr,
+                            g_exp_emulation, b, T, Kp, hw, out, st);
+  if (g_attend_version >= 2 && g_p_in_tmem)
     return attend2_dispatch(mq, mk, mv, picked, mf, mf_dtype, mb, mc, mt, beta, p.scale_log2, p.rescale_thr, b, T,
                             Kp, hw, out, st);
   if (g_p_in_tmem) {

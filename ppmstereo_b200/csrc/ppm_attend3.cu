@@ -1,0 +1,409 @@
+// K3c (v3): PPM memory read, two 128-query tiles per CTA, fine-grained P hand-off.
+// Replaces the flash_attn_func call and residual at reference models/core/ppmstereo.py:550-555.
+//
+// What changed against ppm_attend2.cu (same tiling, same TMEM map, same arithmetic contract):
+//  * P is handed to the tensor pipe in four 32-key chunks (one mbarrier each), so P.V of a
+//    query tile starts while its softmax warps are still exponentiating the rest of the row:
+//    the S-ready -> P-ready latency no longer sits between two MMAs.
+//  * K'/V tiles travel through ONE in-order ring of five 32 KB slots (K0 V0 K1 V1 ...), the
+//    order the MMA thread consumes and releases them in; 2.5 key tiles of prefetch.
+//  * softmax arithmetic in packed fp32x2 (FFMA2/FADD2); kEmu of every 8 exponentials are
+//    evaluated on the FMA pipe (Cody-Waite split + degree-3 minimax polynomial, rel. error
+//    9e-5, far below the bf16 rounding of P) because MUFU.EX2 (16/clk/SM) needs exactly as
+//    many cycles per tile as the two MMAs.
+//  * no integer division in the tile loop; no wait on the previous P.V before publishing P.
+//
+//   warps 0-3   control group (setmaxnreg 88): warp 0 = TMA producer, warp 1 = tcgen05.mma issuer
+//   warps 4-7   softmax / correction / epilogue for query tile A (TMEM lane = query row)
+//   warps 8-11  same for query tile B   (setmaxnreg 208: the register file is 16 K per SM
+//               sub-partition, three warps each -> 88 + 208 + 208)
+// Tensor-pipe order per key tile j:  PV_A(j)  QK_A(j+1)  PV_B(j)  QK_B(j+1)
+// TMEM columns: S_A 0-127, S_B 128-255, O_A 256-383, O_B 384-511; P (bf16) overwrites the first
+// 64 columns of its S (all of S is in registers before the first P chunk is stored).
+#include <math.h>
+
+#include "../../include/ppm_b200.h"
+#include "common.cuh"
+
+namespace ppm {
+
+constexpr int kA3Threads = 384;
+constexpr int kA3Tile = 128;
+constexpr int kA3TileBytes = kA3Tile * kA3Tile * 2;       // 32 KB
+constexpr int kA3HalfBytes = kA3TileBytes / 2;
+constexpr int kA3Slots = 5;
+constexpr uint32_t kA3TmemCols = 512;
+
+struct Attend3Params {
+  const int32_t* picked;
+  const void* mf;
+  long long mb, mc, mt;
+  const float* beta;
+  float* out;
+  float scale_log2, rescale_thr;
+  int T, Kp, hw;
+};
+
+__device__ __forceinline__ float a3_ld(const float* p) { return __ldg(p); }
+__device__ __forceinline__ float a3_ld(const __nv_bfloat16* p) { return __bfloat162float(__ldg(p)); }
+__device__ __forceinline__ float a3_max3(float a, float b, float c) {
+  float d;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+  return d;
+}
+
+// ---- packed fp32x2 helpers (sm_100 FFMA2 / FADD2)
+__device__ __forceinline__ uint64_t f2_pack(float lo, float hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void f2_unpack(uint64_t v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t f2_fma(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ uint64_t f2_add(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ uint64_t f2_add_rm(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("add.rm.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ uint64_t f2_sub(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+
+// 2^x for a pair, x <= 127, on the FMA pipe: n = floor(x) through the 1.5*2^23 magic add
+// (round-down), f = x - n in [0,1), 2^f by a degree-3 minimax polynomial, exponent += n.
+__device__ __forceinline__ void ex2_poly2(float x0, float x1, float& p0, float& p1) {
+  x0 = fmaxf(x0, -127.f);
+  x1 = fmaxf(x1, -127.f);
+  const uint64_t magic = f2_pack(12582912.f, 12582912.f);
+  const uint64_t x = f2_pack(x0, x1);
+  const uint64_t r = f2_add_rm(x, magic);
+  const uint64_t f = f2_sub(x, f2_sub(r, magic));
+  uint64_t q = f2_fma(f, f2_pack(0.077119089663028717f, 0.077119089663028717f),
+                      f2_pack(0.227564394474029541f, 0.227564394474029541f));
+  q = f2_fma(q, f, f2_pack(0.695146143436431885f, 0.695146143436431885f));
+  q = f2_fma(q, f, f2_pack(1.f, 1.f));
+  float q0, q1, r0, r1;
+  f2_unpack(q, q0, q1);
+  f2_unpack(r, r0, r1);
+  p0 = __int_as_float(__float_as_int(q0) + (__float_as_int(r0) << 23));
+  p1 = __int_as_float(__float_as_int(q1) + (__float_as_int(r1) << 23));
+}
+
+template <int kEmu, typename MfT>
+__global__ void __launch_bounds__(kA3Threads, 1)
+ppm_attend3_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_k,
+                   const __grid_constant__ CUtensorMap map_v, const Attend3Params p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem;                                     // 2 query tiles
+  uint8_t* sR = sQ + 2 * kA3TileBytes;                    // K'/V ring, kA3Slots tiles
+  __shared__ uint64_t bar_q, bar_full[kA3Slots], bar_empty[kA3Slots];
+  __shared__ uint64_t bar_sf[2], bar_pf[2][4], bar_o[2];
+  __shared__ uint32_t tmem_slot;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int frame = blockIdx.y;
+  const int bb = frame / p.T;
+  const int q0 = blockIdx.x * 2 * kA3Tile;
+  const int tiles_per_frame = (p.hw + kA3Tile - 1) / kA3Tile;
+  int n_frames = 0;
+  for (int n = 0; n < p.Kp; ++n) n_frames += (__ldg(p.picked + frame * p.Kp + n) >= 0);
+  const int n_tiles = n_frames * tiles_per_frame;
+
+  if (threadIdx.x == 0) {
+    mbar_init(&bar_q, 1);
+    for (int s = 0; s < kA3Slots; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 1); }
+    for (int x = 0; x < 2; ++x) {
+      mbar_init(&bar_sf[x], 1);
+      mbar_init(&bar_o[x], 1);
+      for (int c = 0; c < 4; ++c) mbar_init(&bar_pf[x][c], 4);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc<kA3TmemCols>(&tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = tmem_slot;
+
+  if (warp < 4) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 88;");
+    if (warp == 0) {
+      // -------------------------------------------------------------- TMA producer
+      if (elect_one() && n_tiles > 0) {
+        tma_prefetch_desc(&map_q); tma_prefetch_desc(&map_k); tma_prefetch_desc(&map_v);
+        mbar_expect_tx(&bar_q, 2 * kA3TileBytes);
+        #pragma unroll
+        for (int x = 0; x < 2; ++x) {
+          tma_load_3d(sQ + x * kA3TileBytes, &map_q, &bar_q, 0, q0 + x * kA3Tile, frame);
+          tma_load_3d(sQ + x * kA3TileBytes + kA3HalfBytes, &map_q, &bar_q, 64, q0 + x * kA3Tile, frame);
+        }
+        int slot = 0;
+        uint32_t ph = 1;                                   // parity to wait for on bar_empty[slot]
+        auto advance = [&]() { if (++slot == kA3Slots) { slot = 0; ph ^= 1; } };
+        for (int n = 0; n < p.Kp; ++n) {
+          const int src = __ldg(p.picked + frame * p.Kp + n);
+          if (src < 0) continue;
+          for (int t = 0; t < tiles_per_frame; ++t) {
+            mbar_wait(&bar_empty[slot], ph);
+            mbar_expect_tx(&bar_full[slot], kA3TileBytes);
+            uint8_t* dk = sR + slot * kA3TileBytes;
+            tma_load_3d(dk, &map_k, &bar_full[slot], 0, t * kA3Tile, frame * p.Kp + n);
+            tma_load_3d(dk + kA3HalfBytes, &map_k, &bar_full[slot], 64, t * kA3Tile, frame * p.Kp + n);
+            advance();
+            mbar_wait(&bar_empty[slot], ph);
+            mbar_expect_tx(&bar_full[slot], kA3TileBytes);
+            uint8_t* dv = sR + slot * kA3TileBytes;
+            tma_load_3d(dv, &map_v, &bar_full[slot], t * kA3Tile, 0, bb * p.T + src);
+            tma_load_3d(dv + kA3HalfBytes, &map_v, &bar_full[slot], t * kA3Tile + 64, 0, bb * p.T + src);
+            advance();
+          }
+        }
+      }
+    } else if (warp == 1) {
+      // -------------------------------------------------------------- MMA issuer
+      if (elect_one() && n_tiles > 0) {
+        const uint32_t idesc = umma_idesc(1, 0, 0, kA3Tile, kA3Tile);
+        int slot = 0;                                      // ring position of the next tile to consume
+        uint32_t ph = 0;
+        auto advance = [&]() { if (++slot == kA3Slots) { slot = 0; ph ^= 1; } };
+        auto issue_qk = [&](int x, int ks) {               // S_x = Q_x K'^T, K' in ring slot ks
+          const uint32_t q_addr = smem_u32(sQ + x * kA3TileBytes);
+          const uint32_t k_addr = smem_u32(sR + ks * kA3TileBytes);
+          #pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const uint32_t off = (k >> 2) * kA3HalfBytes + (k & 3) * 32;
+            umma_f16_ss(tmem + x * 128, umma_desc_sw128(q_addr + off, 16, 1024),
+                        umma_desc_sw128(k_addr + off, 16, 1024), idesc, k != 0);
+          }
+          umma_commit(&bar_sf[x]);
+        };
+        auto issue_pv = [&](int x, int vs, int j) {        // O_x += P_x V, chunk by chunk as P arrives
+          const uint32_t v_addr = smem_u32(sR + vs * kA3TileBytes);
+          #pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            mbar_wait(&bar_pf[x][c], j & 1);
+            tc_fence_after();
+            #pragma unroll
+            for (int kk = 0; kk < 2; ++kk) {
+              const int k = 2 * c + kk;
+              const uint32_t off = (k >> 2) * kA3HalfBytes + (k & 3) * 32;
+              umma_f16_ts(tmem + 256 + x * 128, tmem + x * 128 + k * 8, umma_desc_sw128(v_addr + off, 16, 1024),
+                          idesc, (j | k) != 0);
+            }
+          }
+          umma_commit(&bar_o[x]);
+        };
+        mbar_wait(&bar_q, 0);
+        mbar_wait(&bar_full[0], 0);
+        tc_fence_after();
+        issue_qk(0, 0);
+        issue_qk(1, 0);
+        umma_commit(&bar_empty[0]);
+        advance();
+        for (int j = 0; j < n_tiles; ++j) {
+          const bool more = j + 1 < n_tiles;
+          const int vs = slot;                             // V(j)
+          mbar_wait(&bar_full[vs], ph);
+          advance();
+          const int ks = slot;                             // K'(j+1)
+          const uint32_t kph = ph;
+          issue_pv(0, vs, j);
+          if (more) {
+            mbar_wait(&bar_full[ks], kph);
+            tc_fence_after();
+            issue_qk(0, ks);
+          }
+          issue_pv(1, vs, j);
+          umma_commit(&bar_empty[vs]);
+          if (more) {
+            issue_qk(1, ks);
+            umma_commit(&bar_empty[ks]);
+            advance();
+          }
+        }
+      }
+    }
+  } else {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 208;");
+    // ---------------------------------------------------------------- softmax / correction / epilogue
+    const int x = (warp - 4) >> 2;                          // query tile of this warpgroup
+    const int quarter = warp & 3;                           // TMEM lane quarter this warp may access
+    const int row = quarter * 32 + lane;
+    const uint32_t lane_base = static_cast<uint32_t>(quarter * 32) << 16;
+    const uint32_t s_addr = tmem + lane_base + x * 128;
+    const uint32_t o_addr = tmem + lane_base + 256 + x * 128;
+    const float c1 = p.scale_log2;
+    const float thr = p.rescale_thr / c1;
+    const uint64_t c1x2 = f2_pack(c1, c1);
+    const int tail_valid = p.hw - (tiles_per_frame - 1) * kA3Tile;   // keys in the last tile of a frame
+    float m_used = -INFINITY;
+    uint64_t acc0 = f2_pack(0.f, 0.f), acc1 = acc0;
+    int t = 0;                                               // tile index inside the current frame
+    for (int j = 0; j < n_tiles; ++j) {
+      const bool is_tail = (t == tiles_per_frame - 1) && tail_valid < kA3Tile;
+      if (++t == tiles_per_frame) t = 0;
+      mbar_wait(&bar_sf[x], j & 1);
+      tc_fence_after();
+      uint32_t s[4][32];
+      #pragma unroll
+      for (int c = 0; c < 4; ++c) tmem_ld_x32(s_addr + c * 32, s[c]);
+      tmem_ld_wait();
+      if (is_tail) {                                         // mask the keys past the frame end
+        #pragma unroll
+        for (int c = 0; c < 4; ++c)
+          #pragma unroll
+          for (int e = 0; e < 32; ++e)
+            if (c * 32 + e >= tail_valid) s[c][e] = 0xff800000u;
+      }
+      float mx[4];
+      #pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        mx[c] = __uint_as_float(s[c][0]);
+        #pragma unroll
+        for (int e = 1; e < 31; e += 2)
+          mx[c] = a3_max3(mx[c], __uint_as_float(s[c][e]), __uint_as_float(s[c][e + 1]));
+        mx[c] = fmaxf(mx[c], __uint_as_float(s[c][31]));
+      }
+      const float m_tile = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+      const bool grow = m_tile > m_used + thr;
+      if (__any_sync(0xffffffffu, grow)) {
+        float alpha = 1.f;
+        if (grow) {
+          alpha = (m_used == -INFINITY) ? 0.f : ex2_approx((m_used - m_tile) * c1);
+          m_used = m_tile;
+          const uint64_t a2 = f2_pack(alpha, alpha);
+          acc0 = f2_fma(acc0, a2, f2_pack(0.f, 0.f));
+          acc1 = f2_fma(acc1, a2, f2_pack(0.f, 0.f));
+        }
+        if (j > 0) {
+          mbar_wait(&bar_o[x], (j - 1) & 1);                 // P.V of tile j-1 has landed in O
+          tc_fence_after();
+          #pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            uint32_t o[32];
+            tmem_ld_x32(o_addr + c * 32, o);
+            tmem_ld_wait();
+            #pragma unroll
+            for (int e = 0; e < 32; ++e) o[e] = __float_as_uint(__uint_as_float(o[e]) * alpha);
+            tmem_st_x32(o_addr + c * 32, o);
+          }
+        }
+      }
+      const float mneg = -m_used * c1;
+      const uint64_t mneg2 = f2_pack(mneg, mneg);
+      #pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        uint32_t pk[16];
+        #pragma unroll
+        for (int pi = 0; pi < 16; ++pi) {
+          float x0, x1, p0, p1;
+          f2_unpack(f2_fma(f2_pack(__uint_as_float(s[c][2 * pi]), __uint_as_float(s[c][2 * pi + 1])), c1x2, mneg2),
+                    x0, x1);
+          if (((pi * kEmu) & 7) < kEmu) {
+            ex2_poly2(x0, x1, p0, p1);
+          } else {
+            p0 = ex2_approx(x0);
+            p1 = ex2_approx(x1);
+          }
+          if (pi & 1) acc1 = f2_add(acc1, f2_pack(p0, p1));
+          else acc0 = f2_add(acc0, f2_pack(p0, p1));
+          pk[pi] = pack_bf16x2(p0, p1);
+        }
+        tmem_st_x16(s_addr + c * 16, pk);                    // P columns [16c, 16c+16) of this S buffer
+        tmem_st_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bar_pf[x][c]);
+      }
+    }
+    if (n_tiles > 0) {
+      mbar_wait(&bar_o[x], (n_tiles - 1) & 1);
+      tc_fence_after();
+    }
+    float l0, l1, l2, l3;
+    f2_unpack(acc0, l0, l1);
+    f2_unpack(acc1, l2, l3);
+    const float l_sum = (l0 + l1) + (l2 + l3);
+    const float inv = n_tiles > 0 ? 1.f / l_sum : 0.f;
+    const float beta = __ldg(p.beta);
+    const int pix = q0 + x * kA3Tile + row;
+    const MfT* mf = static_cast<const MfT*>(p.mf) + bb * p.mb + (frame - bb * p.T) * p.mt + pix;
+    float* dst = p.out + static_cast<long long>(frame) * kA3Tile * p.hw + pix;
+    #pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      uint32_t o[32];
+      if (n_tiles > 0) {
+        tmem_ld_x32(o_addr + c * 32, o);
+        tmem_ld_wait();
+      } else {
+        #pragma unroll
+        for (int e = 0; e < 32; ++e) o[e] = 0u;
+      }
+      if (pix < p.hw) {
+        #pragma unroll
+        for (int e = 0; e < 32; ++e) {
+          const int ch = c * 32 + e;
+          const float hid = bf16_round_f(__uint_as_float(o[e]) * inv);
+          dst[static_cast<long long>(ch) * p.hw] = __fadd_rn(a3_ld(mf + ch * p.mc), __fmul_rn(beta, hid));
+        }
+      }
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<kA3TmemCols>(tmem);
+  }
+}
+
+template <int kEmu, typename MfT>
+static int launch_attend3(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv, const Attend3Params& p,
+                          int n_qtiles, int n_frames, cudaStream_t st) {
+  constexpr int kSmem = (2 + kA3Slots) * kA3TileBytes + 1024;
+  auto kern = ppm_attend3_kernel<kEmu, MfT>;
+  PPM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+  kern<<<dim3(n_qtiles, n_frames), kA3Threads, kSmem, st>>>(mq, mk, mv, p);
+  PPM_CUDA(cudaGetLastError());
+  return PPM_OK;
+}
+
+template <int kEmu>
+static int launch_attend3_mf(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv,
+                             const Attend3Params& p, int mf_dtype, int n_qtiles, int n_frames, cudaStream_t st) {
+  if (mf_dtype == PPM_BF16) return launch_attend3<kEmu, __nv_bfloat16>(mq, mk, mv, p, n_qtiles, n_frames, st);
+  return launch_attend3<kEmu, float>(mq, mk, mv, p, n_qtiles, n_frames, st);
+}
+
+// Entry used by ppm_memory_attend (ppm_attend.cu).  `emu` = exponentials per 8 evaluated on the FMA pipe.
+int attend3_dispatch(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv, const int32_t* picked,
+                     const void* mf, int mf_dtype, long long mb, long long mc, long long mt, const float* beta,
+                     float scale_log2, float rescale_thr, int emu, int b, int T, int Kp, int hw, float* out,
+                     cudaStream_t st) {
+  Attend3Params p{};
+  p.picked = picked; p.mf = mf; p.mb = mb; p.mc = mc; p.mt = mt; p.beta = beta; p.out = out;
+  p.scale_log2 = scale_log2; p.rescale_thr = rescale_thr; p.T = T; p.Kp = Kp; p.hw = hw;
+  const int n_qtiles = (hw + 2 * kA3Tile - 1) / (2 * kA3Tile);
+  switch (emu) {
+    default: return launch_attend3_mf<0>(mq, mk, mv, p, mf_dtype, n_qtiles, b * T, st);
+    case 2: return launch_attend3_mf<2>(mq, mk, mv, p, mf_dtype, n_qtiles, b * T, st);
+    case 4: return launch_attend3_mf<4>(mq, mk, mv, p, mf_dtype, n_qtiles, b * T, st);
+    case 3: return launch_attend3_mf<3>(mq, mk, mv, p, mf_dtype, n_qtiles, b * T, st);
+  }
+}
+
+}  // namespace ppm

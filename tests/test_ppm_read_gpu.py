@@ -136,20 +136,34 @@ def test_ragged_tiles_batch2(P, p_in_tmem):
         set_p_mode(True)
 
 
-def test_one_tile_and_two_tile_kernels_agree(P):
-    """The two-query-tile kernel (default) and the one-tile kernel compute the same P and O; only the
-    order of the fp32 row-sum differs (1 ulp of 1/l before the bf16 rounding of the output)."""
+def set_exp_emulation(n: int):
+    from ppmstereo_b200 import _lib
+    import ctypes
+    lib = _lib.load()
+    lib.ppm_debug_set_exp_emulation.restype = ctypes.c_int
+    lib.ppm_debug_set_exp_emulation.argtypes = [ctypes.c_int]
+    lib.ppm_debug_set_exp_emulation(n)
+
+
+def test_kernel_generations_agree(P):
+    """v3 (default: chunked P hand-off, MUFU exponentials), v3 with 2/3/4 of 8 exponentials by polynomial, the v2
+    two-tile kernel and the v1 one-tile kernel see the same operands; they differ only in summation
+    order and in the 9e-5 relative error of the polynomial, i.e. by at most one bf16 ulp of hidden."""
     t = make_case(1, 9, 20, 31, seed=15)                  # hw = 620: 5 key tiles, 3 two-tile CTAs per frame
-    outs = []
-    for v in (2, 1):
-        set_attend_version(v)
-        try:
-            outs.append(run_read(P, t)[1])
-        finally:
-            set_attend_version(2)
-    d = (outs[0] - outs[1]).abs()
-    assert float((d == 0).float().mean()) >= 0.99
-    assert float(d.max()) <= 2.0 ** -7 * float(outs[1].abs().max())
+    outs = {}
+    try:
+        for v, emu in ((3, 0), (3, 2), (3, 3), (3, 4), (2, 0), (1, 0)):
+            set_attend_version(v)
+            set_exp_emulation(emu)
+            outs[(v, emu)] = run_read(P, t)[1]
+    finally:
+        set_attend_version(3)
+        set_exp_emulation(0)
+    base = outs[(1, 0)]
+    for key, o in outs.items():
+        d = (o - base).abs()
+        assert float(d.max()) <= 2.0 ** -7 * float(base.abs().max()), key
+        assert float((d == 0).float().mean()) >= (0.99 if key[1] == 0 else 0.80), key
 
 
 def test_peaky_softmax_rescale_path(P):
