@@ -8,13 +8,17 @@
 // of W] land in shared memory as SWIZZLE_128B MN-major tiles that tcgen05.mma consumes
 // directly (no transpose pass, no repack).  bf16 inputs use kind::f16, fp32 inputs kind::tf32.
 //
-// One CTA computes a 128 x NT tile (NT <= 256) of one row problem:
-//   warp 0    TMA producer (3-stage mbarrier ring over the channel axis)
+// One work item is a 128 x NT tile (NT <= 256) of one row problem:
+//   warp 0    TMA producer (4-stage mbarrier ring over the channel axis)
 //   warp 1    TMEM allocation + single-thread tcgen05.mma issue, accumulator in TMEM
-//   warps 2-5 epilogue: tcgen05.ld (one output row per thread, 32 columns at a time), scale by
+//   warps 2-9 epilogue: tcgen05.ld (one output row per thread, 32 columns at a time), scale by
 //             1/sqrt(D), form levels 1..4 by pair-averaging IN REGISTERS (a thread owns whole
-//             row segments, so pooling along j needs no communication), transpose through a
-//             per-warp shared-memory slab and write every level with row-contiguous stores.
+//             row segments, so pooling along j needs no communication) and store every level
+//             straight from registers with 16-byte vector stores (a 32-column chunk of a bf16
+//             row is 64 contiguous bytes; L2 merges the sector halves before they reach HBM).
+// Persistent: one CTA per SM loops over (image row, M tile, N tile) work items; the smem ring
+// runs on across items and the accumulator is double-buffered in TMEM (2 x 256 columns), so
+// the TMA loads and MMAs of item i+1 overlap the epilogue stores of item i.
 // The volume is written exactly once and never re-read: 1.9375 x W1 x W2 elements per row.
 #include <math.h>
 
@@ -24,25 +28,21 @@
 namespace ppm {
 
 constexpr int kCbM = 128;            // pixels of W1 per CTA (UMMA M)
-constexpr int kCbStages = 3;
-constexpr int kCbThreads = 192;
+constexpr int kCbStages = 4;
+constexpr int kCbThreads = 320;      // TMA warp, MMA warp, 8 epilogue warps
 constexpr int kCbMaxN = 256;
-constexpr int kCbTmemCols = 256;
+constexpr int kCbTmemCols = 512;     // two 256-column accumulators: MMA of tile i+1 overlaps the epilogue of tile i
+constexpr int kCbEpiWarps = 8;
 constexpr int kCbLevels = 5;
-// per-warp epilogue slab: [32 rows][n_l + 1] floats for n_l = 32,16,8,4,2
-__host__ __device__ constexpr int slab_off(int l) {
-  int o = 0;
-  for (int i = 0; i < l; ++i) o += 32 * ((32 >> i) + 1);
-  return o;
-}
-constexpr int kSlabFloats = 32 * (33 + 17 + 9 + 5 + 3);
-
 struct CorrBuildParams {
   void* level[kCbLevels];
   int width[kCbLevels];
   int n_levels;                      // pooled levels to write (<= 4)
-  int D, W1, W2, NT, n_ntiles;
+  int D, H, W1, W2, NT, n_ntiles, n_mtiles;
+  long long n_tiles;
   float sqrt_d;
+  float inv_sqrt_d;                  // 1/sqrt(D) when that is exact (sqrt(D) a power of two), else 0
+  int vec_ok[kCbLevels];             // level rows allow the full-width vector store
 };
 
 template <typename ElemT> struct CbTraits;
@@ -70,8 +70,42 @@ template <> struct CbTraits<float> {
 __device__ __forceinline__ float cb_round(float v, float) { return v; }
 __device__ __forceinline__ float cb_round(float v, __nv_bfloat16) { return bf16_round_f(v); }
 
+// Store v[0..n) (n = 32, 16, 8, 4 or 2, compile-time at every call after unrolling) to dst[0..n),
+// only the first `valid` elements exist in the row.  vec: dst is aligned to min(16, n*sizeof) bytes.
+template <typename OutT>
+__device__ __forceinline__ void cb_store_row(OutT* dst, const float (&v)[32], int n, int valid, bool vec) {
+  if (vec && valid >= n) {
+    if constexpr (sizeof(OutT) == 2) {
+      uint32_t pk[16];
+      #pragma unroll
+      for (int j = 0; j < 16; ++j) pk[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
+      if (n >= 8) {
+        #pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if (8 * j < n) reinterpret_cast<uint4*>(dst)[j] = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+      } else if (n == 4) {
+        *reinterpret_cast<uint2*>(dst) = make_uint2(pk[0], pk[1]);
+      } else {
+        *reinterpret_cast<uint32_t*>(dst) = pk[0];
+      }
+    } else {
+      if (n >= 4) {
+        #pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (4 * j < n) reinterpret_cast<float4*>(dst)[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+      } else {
+        *reinterpret_cast<float2*>(dst) = make_float2(v[0], v[1]);
+      }
+    }
+  } else {
+    #pragma unroll
+    for (int j = 0; j < 32; ++j)
+      if (j < n && j < valid) dst[j] = OutT(v[j]);
+  }
+}
+
 template <typename ElemT, typename OutT>
-__global__ void __launch_bounds__(kCbThreads)
+__global__ void __launch_bounds__(kCbThreads, 1)
 corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constant__ CUtensorMap map2,
                   const CorrBuildParams p) {
   using Tr = CbTraits<ElemT>;
@@ -83,20 +117,19 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
 
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  float* slabs = reinterpret_cast<float*>(smem + kCbStages * kStageBytes);
-  __shared__ uint64_t bar_full[kCbStages], bar_empty[kCbStages], bar_acc;
+  __shared__ uint64_t bar_full[kCbStages], bar_empty[kCbStages], bar_acc_full[2], bar_acc_empty[2];
   __shared__ uint32_t tmem_slot;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int mt = blockIdx.x / p.n_ntiles, nt = blockIdx.x % p.n_ntiles;
-  const int h = blockIdx.y, b = blockIdx.z;
-  const int m0 = mt * kCbM, n0 = nt * p.NT;
   const int n_bchunks = (p.NT + Tr::kChunkW - 1) / Tr::kChunkW;
   const int n_k = (p.D + Tr::kKC - 1) / Tr::kKC;
+  // tile t -> (b*H + h, mt, nt), nt fastest: the CTAs working on one image row run side by side
+  // and find each other's feature tiles in L2.
+  const int tiles_per_row = p.n_mtiles * p.n_ntiles;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kCbStages; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 1); }
-    mbar_init(&bar_acc, 1);
+    for (int s = 0; s < 2; ++s) { mbar_init(&bar_acc_full[s], 1); mbar_init(&bar_acc_empty[s], kCbEpiWarps); }
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc<kCbTmemCols>(&tmem_slot);
@@ -111,102 +144,111 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
       tma_prefetch_desc(&map1);
       tma_prefetch_desc(&map2);
       const uint32_t bytes = (kAChunks + n_bchunks) * kChunkBytes;
-      for (int kc = 0; kc < n_k; ++kc) {
-        const int s = kc % kCbStages;
-        mbar_wait(&bar_empty[s], ((kc / kCbStages) & 1) ^ 1);
-        mbar_expect_tx(&bar_full[s], bytes);
-        uint8_t* st = smem + s * kStageBytes;
-        #pragma unroll
-        for (int c = 0; c < kAChunks; ++c)
-          tma_load_4d(st + c * kChunkBytes, &map1, &bar_full[s], m0 + c * Tr::kChunkW, h, kc * Tr::kKC, b);
-        for (int c = 0; c < n_bchunks; ++c)
-          tma_load_4d(st + kABytes + c * kChunkBytes, &map2, &bar_full[s], n0 + c * Tr::kChunkW, h,
-                      kc * Tr::kKC, b);
+      int s = 0;
+      uint32_t ph = 1;
+      for (long long t = blockIdx.x; t < p.n_tiles; t += gridDim.x) {
+        const int bh = static_cast<int>(t / tiles_per_row), r = static_cast<int>(t % tiles_per_row);
+        const int b = bh / p.H, h = bh % p.H;
+        const int m0 = (r / p.n_ntiles) * kCbM, n0 = (r % p.n_ntiles) * p.NT;
+        for (int kc = 0; kc < n_k; ++kc) {
+          mbar_wait(&bar_empty[s], ph);
+          mbar_expect_tx(&bar_full[s], bytes);
+          uint8_t* st = smem + s * kStageBytes;
+          #pragma unroll
+          for (int c = 0; c < kAChunks; ++c)
+            tma_load_4d(st + c * kChunkBytes, &map1, &bar_full[s], m0 + c * Tr::kChunkW, h, kc * Tr::kKC, b);
+          for (int c = 0; c < n_bchunks; ++c)
+            tma_load_4d(st + kABytes + c * kChunkBytes, &map2, &bar_full[s], n0 + c * Tr::kChunkW, h,
+                        kc * Tr::kKC, b);
+          if (++s == kCbStages) { s = 0; ph ^= 1; }
+        }
       }
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer
     if (elect_one()) {
       const uint32_t idesc = umma_idesc(Tr::kFmt, /*a MN-major*/ 1, /*b MN-major*/ 1, kCbM, p.NT);
-      for (int kc = 0; kc < n_k; ++kc) {
-        const int s = kc % kCbStages;
-        mbar_wait(&bar_full[s], (kc / kCbStages) & 1);
+      int s = 0;
+      uint32_t ph = 0;
+      int it = 0;
+      for (long long t = blockIdx.x; t < p.n_tiles; t += gridDim.x, ++it) {
+        const int buf = it & 1;
+        mbar_wait(&bar_acc_empty[buf], ((it >> 1) & 1) ^ 1);     // epilogue has drained this accumulator
         tc_fence_after();
-        const uint32_t a0 = smem_u32(smem + s * kStageBytes);
-        const uint32_t b0 = a0 + kABytes;
-        #pragma unroll
-        for (int k = 0; k < Tr::kKC / Tr::kUK; ++k) {
-          // MN-major: LBO = stride between 128-byte MN chunks, SBO = one swizzle group of channel rows
-          const uint64_t ad = umma_desc_sw128(a0 + k * Tr::kUK * 128, kChunkBytes, Tr::kSbo, Tr::kLayout);
-          const uint64_t bd = umma_desc_sw128(b0 + k * Tr::kUK * 128, kChunkBytes, Tr::kSbo, Tr::kLayout);
-          if constexpr (Tr::kFmt == 2) umma_tf32_ss(tmem_base, ad, bd, idesc, (kc | k) != 0);
-          else                         umma_f16_ss(tmem_base, ad, bd, idesc, (kc | k) != 0);
+        const uint32_t acc = tmem_base + buf * kCbMaxN;
+        for (int kc = 0; kc < n_k; ++kc) {
+          mbar_wait(&bar_full[s], ph);
+          tc_fence_after();
+          const uint32_t a0 = smem_u32(smem + s * kStageBytes);
+          const uint32_t b0 = a0 + kABytes;
+          #pragma unroll
+          for (int k = 0; k < Tr::kKC / Tr::kUK; ++k) {
+            // MN-major: LBO = stride between 128-byte MN chunks, SBO = one swizzle group of channel rows
+            const uint64_t ad = umma_desc_sw128(a0 + k * Tr::kUK * 128, kChunkBytes, Tr::kSbo, Tr::kLayout);
+            const uint64_t bd = umma_desc_sw128(b0 + k * Tr::kUK * 128, kChunkBytes, Tr::kSbo, Tr::kLayout);
+            if constexpr (Tr::kFmt == 2) umma_tf32_ss(acc, ad, bd, idesc, (kc | k) != 0);
+            else                         umma_f16_ss(acc, ad, bd, idesc, (kc | k) != 0);
+          }
+          umma_commit(&bar_empty[s]);
+          if (++s == kCbStages) { s = 0; ph ^= 1; }
         }
-        umma_commit(&bar_empty[s]);
+        umma_commit(&bar_acc_full[buf]);
       }
-      umma_commit(&bar_acc);
     }
   } else {
     // ------------------------------------------------------------ epilogue
+    // Thread = one output row (TMEM lane); two warps share a lane quarter and take alternate
+    // 32-column chunks.  A thread holds whole row segments, so the pooled levels come from
+    // pair-averaging in registers and every level is stored straight from registers with the
+    // widest aligned vector store (a 32-column chunk is 64 contiguous bytes of a bf16 row).
     const int q = warp & 3;                         // TMEM lane quarter this warp may access
-    float* slab = slabs + (warp - 2) * kSlabFloats;
-    const long long bh = static_cast<long long>(b) * gridDim.y + h;
-    const long long row_base = bh * p.W1 + m0 + q * 32;          // global row of slab row 0
-    const int rows_valid = min(32, p.W1 - (m0 + q * 32));        // may be <= 0
-    mbar_wait(&bar_acc, 0);
-    tc_fence_after();
+    const int half = (warp - 2) >> 2;               // which chunks this warp takes
     const int n_chunks = p.NT / 32;
-    for (int cc = 0; cc < n_chunks; ++cc) {
-      uint32_t raw[32];
-      tmem_ld_x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + cc * 32, raw);
-      tmem_ld_wait();
-      float v[32];
-      #pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        float a = cb_round(__uint_as_float(raw[j]), OutT());
-        v[j] = cb_round(__fdiv_rn(a, p.sqrt_d), OutT());
-      }
-      __syncwarp();                                  // previous chunk's write-out is done
-      #pragma unroll
-      for (int j = 0; j < 32; ++j) slab[slab_off(0) + lane * 33 + j] = v[j];
-      #pragma unroll
-      for (int l = 1; l < kCbLevels; ++l) {
-        const int n = 32 >> l;
-        #pragma unroll
-        for (int j = 0; j < n; ++j) {
-          v[j] = cb_round(__fmul_rn(__fadd_rn(v[2 * j], v[2 * j + 1]), 0.5f), OutT());
-          slab[slab_off(l) + lane * (n + 1) + j] = v[j];
-        }
-      }
-      __syncwarp();
-      // write-out: row-contiguous stores, level by level
-      #pragma unroll
-      for (int l = 0; l < kCbLevels; ++l) {
-        if (l > p.n_levels) break;
-        const int n = 32 >> l;
-        const int Wl = p.width[l];
-        const int col0 = (n0 + cc * 32) >> l;
-        OutT* dst = static_cast<OutT*>(p.level[l]);
-        const float* src = slab + slab_off(l);
-        if (sizeof(OutT) == 2 && (Wl & 1) == 0) {
-          const int u = n / 2;                       // 4-byte units per row
-          for (int idx = lane; idx < 32 * u; idx += 32) {
-            const int r = idx / u, c = 2 * (idx % u);
-            if (r < rows_valid && col0 + c < Wl) {
-              const uint32_t pk = pack_bf16x2(src[r * (n + 1) + c], src[r * (n + 1) + c + 1]);
-              *reinterpret_cast<uint32_t*>(reinterpret_cast<__nv_bfloat16*>(dst) +
-                                           (row_base + r) * Wl + col0 + c) = pk;
-            }
-          }
+    int it = 0;
+    for (long long t = blockIdx.x; t < p.n_tiles; t += gridDim.x, ++it) {
+      const int bh = static_cast<int>(t / tiles_per_row), r = static_cast<int>(t % tiles_per_row);
+      const int m0 = (r / p.n_ntiles) * kCbM, n0 = (r % p.n_ntiles) * p.NT;
+      const int m = m0 + q * 32 + lane;             // pixel of W1 owned by this thread
+      const long long row = static_cast<long long>(bh) * p.W1 + m;
+      const bool row_ok = m < p.W1;
+      const int buf = it & 1;
+      mbar_wait(&bar_acc_full[buf], (it >> 1) & 1);
+      tc_fence_after();
+      const uint32_t acc = tmem_base + buf * kCbMaxN + (static_cast<uint32_t>(q * 32) << 16);
+      for (int cc = half; cc < n_chunks; cc += 2) {
+        uint32_t raw[32];
+        tmem_ld_x32(acc + cc * 32, raw);
+        tmem_ld_wait();
+        float v[32];
+        if (p.inv_sqrt_d != 0.f) {                  // sqrt(D) is a power of two: multiplying is exact
+          #pragma unroll
+          for (int j = 0; j < 32; ++j)
+            v[j] = cb_round(__fmul_rn(cb_round(__uint_as_float(raw[j]), OutT()), p.inv_sqrt_d), OutT());
         } else {
-          for (int idx = lane; idx < 32 * n; idx += 32) {
-            const int r = idx / n, c = idx % n;
-            if (r < rows_valid && col0 + c < Wl) dst[(row_base + r) * Wl + col0 + c] = OutT(src[r * (n + 1) + c]);
+          #pragma unroll
+          for (int j = 0; j < 32; ++j)
+            v[j] = cb_round(__fdiv_rn(cb_round(__uint_as_float(raw[j]), OutT()), p.sqrt_d), OutT());
+        }
+        #pragma unroll
+        for (int l = 0; l < kCbLevels; ++l) {
+          const int n = 32 >> l;                     // compile-time after unrolling
+          if (l > 0) {
+            #pragma unroll
+            for (int j = 0; j < n; ++j)
+              v[j] = cb_round(__fmul_rn(__fadd_rn(v[2 * j], v[2 * j + 1]), 0.5f), OutT());
+          }
+          if (l <= p.n_levels && row_ok) {
+            const int Wl = p.width[l];
+            const int col0 = (n0 + cc * 32) >> l;
+            OutT* dst = static_cast<OutT*>(p.level[l]) + row * Wl + col0;
+            cb_store_row<OutT>(dst, v, n, Wl - col0, p.vec_ok[l]);
           }
         }
       }
+      tc_fence_before();                            // this warp's TMEM reads of the buffer are done
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&bar_acc_empty[buf]);
     }
-    tc_fence_before();
   }
   __syncthreads();
   if (warp == 1) {
@@ -220,14 +262,29 @@ static int launch_corr_build(const void* f1, const void* f2, int B, int D, int H
                              int ld1, int ld2, void* const* levels, int n_levels, cudaStream_t st) {
   using Tr = CbTraits<ElemT>;
   constexpr int kStageBytes = (kCbM / Tr::kChunkW + kCbMaxN / Tr::kChunkW) * Tr::kKC * 128;
-  constexpr int kSmem = kCbStages * kStageBytes + 4 * kSlabFloats * 4 + 1024;
+  constexpr int kSmem = kCbStages * kStageBytes + 1024;
   CorrBuildParams p{};
   p.n_levels = n_levels;
   for (int l = 0; l <= n_levels; ++l) { p.level[l] = levels[l]; p.width[l] = W2 >> l; }
   p.D = D; p.W1 = W1; p.W2 = W2;
   p.n_ntiles = (W2 + kCbMaxN - 1) / kCbMaxN;
+  p.n_mtiles = (W1 + kCbM - 1) / kCbM;
+  p.H = H;
+  p.n_tiles = static_cast<long long>(B) * H * p.n_mtiles * p.n_ntiles;
   p.NT = (((W2 + p.n_ntiles - 1) / p.n_ntiles) + 31) / 32 * 32;
   p.sqrt_d = sqrtf(static_cast<float>(D));
+  {
+    int e = 0;
+    const float mant = frexpf(p.sqrt_d, &e);
+    p.inv_sqrt_d = (mant == 0.5f && p.sqrt_d * p.sqrt_d == static_cast<float>(D)) ? 1.f / p.sqrt_d : 0.f;
+  }
+  for (int l = 0; l <= n_levels; ++l) {
+    const size_t esz = sizeof(OutT);
+    const size_t chunk = static_cast<size_t>(32 >> l) * esz;
+    const size_t need = chunk < 16 ? chunk : 16;
+    p.vec_ok[l] = ((static_cast<size_t>(W2 >> l) * esz) % need == 0) &&
+                  (reinterpret_cast<uintptr_t>(levels[l]) % 16 == 0);
+  }
   const CUtensorMapDataType dt = sizeof(ElemT) == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
                                                     : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
   CUtensorMap m1, m2;
@@ -248,7 +305,11 @@ static int launch_corr_build(const void* f1, const void* f2, int B, int D, int H
   }
   auto kern = corr_build_kernel<ElemT, OutT>;
   PPM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
-  dim3 grid(((W1 + kCbM - 1) / kCbM) * p.n_ntiles, H, B);
+  // persistent: one CTA per SM (it owns all 512 TMEM columns), static round-robin over the tiles
+  int dev = 0, n_sm = 148;
+  PPM_CUDA(cudaGetDevice(&dev));
+  PPM_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
+  const int grid = static_cast<int>(p.n_tiles < n_sm ? p.n_tiles : n_sm);
   kern<<<grid, kCbThreads, kSmem, st>>>(m1, m2, p);
   PPM_CUDA(cudaGetLastError());
   return PPM_OK;

@@ -400,6 +400,7 @@ int attend3_dispatch(const CUtensorMap& mq, const CUtensorMap& mk, const CUtenso
   const int n_qtiles = (hw + 2 * kA3Tile - 1) / (2 * kA3Tile);
   switch (emu) {
     default: return launch_attend3_mf<0>(mq, mk, mv, p, mf_dtype, n_qtiles, b * T, st);
+    case 1: return launch_attend3_mf<1>(mq, mk, mv, p, mf_dtype, n_qtiles, b * T, st);
     case 2: return launch_attend3_mf<2>(mq, mk, mv, p, mf_dtype, n_qtiles, b * T, st);
     case 4: return launch_attend3_mf<4>(mq, mk, mv, p, mf_dtype, n_qtiles, b * T, st);
     case 3: return launch_attend3_mf<3>(mq, mk, mv, p, mf_dtype, n_qtiles, b * T, st);
