@@ -70,6 +70,47 @@ template <> struct CbTraits<float> {
 __device__ __forceinline__ float cb_round(float v, float) { return v; }
 __device__ __forceinline__ float cb_round(float v, __nv_bfloat16) { return bf16_round_f(v); }
 
+// ---- fast epilogue for bf16 output with an exact power-of-two 1/sqrt(D)
+// Rounding goes through cvt.rn.bf16x2.f32 (F2FP, ALU pipe): the scalar cvt.rn.bf16.f32 is an XU-pipe
+// instruction (16 lanes/clk/SM) and made the first epilogue conversion-bound.  Scaling by a power of
+// two commutes with rounding, so bf16(bf16(acc) / sqrt(D)) == bf16(acc * 2^-k) and the packed word
+// is both the value stored and (unpacked) the input of the next pyramid level.
+__device__ __forceinline__ void cb_st256(void* p, const uint32_t* w) {
+  asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+               ::"l"(p), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]), "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7])
+               : "memory");
+}
+// words: n/2 packed bf16 pairs of one level chunk (n = 32 >> l elements); vec 2 = 32-byte aligned rows,
+// 1 = aligned to min(16, chunk) bytes, 0 = element stores.
+__device__ __forceinline__ void cb_store_words(__nv_bfloat16* dst, const uint32_t* w, int n, int valid, int vec) {
+  if (vec && valid >= n) {
+    if (n == 32) {
+      if (vec == 2) { cb_st256(dst, w); cb_st256(dst + 16, w + 8); }
+      else {
+        #pragma unroll
+        for (int j = 0; j < 4; ++j) reinterpret_cast<uint4*>(dst)[j] = make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
+      }
+    } else if (n == 16) {
+      if (vec == 2) cb_st256(dst, w);
+      else {
+        #pragma unroll
+        for (int j = 0; j < 2; ++j) reinterpret_cast<uint4*>(dst)[j] = make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
+      }
+    } else if (n == 8) {
+      *reinterpret_cast<uint4*>(dst) = make_uint4(w[0], w[1], w[2], w[3]);
+    } else if (n == 4) {
+      *reinterpret_cast<uint2*>(dst) = make_uint2(w[0], w[1]);
+    } else {
+      *reinterpret_cast<uint32_t*>(dst) = w[0];
+    }
+  } else {
+    #pragma unroll
+    for (int j = 0; j < 32; ++j)
+      if (j < n && j < valid)
+        reinterpret_cast<uint16_t*>(dst)[j] = static_cast<uint16_t>((j & 1) ? (w[j >> 1] >> 16) : (w[j >> 1] & 0xFFFFu));
+  }
+}
+
 // Store v[0..n) (n = 32, 16, 8, 4 or 2, compile-time at every call after unrolling) to dst[0..n),
 // only the first `valid` elements exist in the row.  vec: dst is aligned to min(16, n*sizeof) bytes.
 template <typename OutT>
@@ -219,6 +260,34 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
         uint32_t raw[32];
         tmem_ld_x32(acc + cc * 32, raw);
         tmem_ld_wait();
+        if constexpr (sizeof(OutT) == 2) {
+          if (p.inv_sqrt_d != 0.f) {
+            // fast path: bf16 pyramid, exact power-of-two scale
+            uint32_t w[16];
+            #pragma unroll
+            for (int j = 0; j < 16; ++j)
+              w[j] = pack_bf16x2(__fmul_rn(__uint_as_float(raw[2 * j]), p.inv_sqrt_d),
+                                 __fmul_rn(__uint_as_float(raw[2 * j + 1]), p.inv_sqrt_d));
+            #pragma unroll
+            for (int l = 0; l < kCbLevels; ++l) {
+              const int n = 32 >> l;
+              if (l > 0) {                              // pool pairs of the previous level's rounded values
+                #pragma unroll
+                for (int j = 0; j < n / 2; ++j) {
+                  const float a = __fadd_rn(__uint_as_float(w[2 * j] << 16), __uint_as_float(w[2 * j] & 0xFFFF0000u));
+                  const float c = __fadd_rn(__uint_as_float(w[2 * j + 1] << 16), __uint_as_float(w[2 * j + 1] & 0xFFFF0000u));
+                  w[j] = pack_bf16x2(__fmul_rn(a, 0.5f), __fmul_rn(c, 0.5f));
+                }
+              }
+              if (l <= p.n_levels && row_ok) {
+                const int Wl = p.width[l];
+                const int col0 = (n0 + cc * 32) >> l;
+                cb_store_words(reinterpret_cast<__nv_bfloat16*>(p.level[l]) + row * Wl + col0, w, n, Wl - col0, p.vec_ok[l]);
+              }
+            }
+            continue;
+          }
+        }
         float v[32];
         if (p.inv_sqrt_d != 0.f) {                  // sqrt(D) is a power of two: multiplying is exact
           #pragma unroll
@@ -241,7 +310,7 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
             const int Wl = p.width[l];
             const int col0 = (n0 + cc * 32) >> l;
             OutT* dst = static_cast<OutT*>(p.level[l]) + row * Wl + col0;
-            cb_store_row<OutT>(dst, v, n, Wl - col0, p.vec_ok[l]);
+            cb_store_row<OutT>(dst, v, n, Wl - col0, p.vec_ok[l] != 0);
           }
         }
       }
@@ -284,6 +353,9 @@ static int launch_corr_build(const void* f1, const void* f2, int B, int D, int H
     const size_t need = chunk < 16 ? chunk : 16;
     p.vec_ok[l] = ((static_cast<size_t>(W2 >> l) * esz) % need == 0) &&
                   (reinterpret_cast<uintptr_t>(levels[l]) % 16 == 0);
+    if (p.vec_ok[l] && chunk >= 32 && (static_cast<size_t>(W2 >> l) * esz) % 32 == 0 &&
+        reinterpret_cast<uintptr_t>(levels[l]) % 32 == 0)
+      p.vec_ok[l] = 2;                               // 256-bit stores (bf16 fast path)
   }
   const CUtensorMapDataType dt = sizeof(ElemT) == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
                                                     : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
