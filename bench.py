@@ -139,10 +139,8 @@ class Counters:
     attend_events = []          # (start, end) CUDA events of the 1/4-res memory-read launches
 
 
-def run_level(P, x, iters: int, beta, from_host: bool, time_attend: bool):
-    """One cascade level of one window.  Returns the tensors a caller would read back."""
-    src = x.host if from_host else x.dev
-    t = {k: (v.cuda(non_blocking=True) if from_host else v) for k, v in src.items()}
+def run_level(P, t, iters: int, beta, time_attend: bool):
+    """One cascade level of one window on device tensors `t`.  Returns the tensors a caller reads back."""
     blk = P.CorrBlock1D(t["fmap1"], t["fmap2"])                       # K1
     mem = P.PPMMemory(t["query"], t["key"], None, top_k=TOP_K)          # pack Q' once per level
     strive = torch.ones_like(t["sim"])
@@ -160,15 +158,23 @@ def run_level(P, x, iters: int, beta, from_host: bool, time_attend: bool):
             e1.record()
             Counters.attend_events.append((e0, e1))
         Counters.launches += 6
-    if from_host:
-        return out.cpu(), corr.cpu()
     return out, corr
 
 
-def run_clip(P, inputs, beta, from_host: bool, time_attend: bool = False):
-    for T in clip_windows():
-        for ds, iters in LEVELS:
-            run_level(P, inputs[(T, ds)], iters, beta, from_host, time_attend and ds == 4 and T == KERNEL_SIZE)
+def clip_jobs():
+    return [(T, ds, iters) for T in clip_windows() for ds, iters in LEVELS]
+
+
+def run_clip(P, inputs, beta, from_host: bool, time_attend: bool = False, runner=None):
+    jobs = clip_jobs()
+    if not from_host:
+        for T, ds, iters in jobs:
+            run_level(P, inputs[(T, ds)].dev, iters, beta, time_attend and ds == 4 and T == KERNEL_SIZE)
+        return None
+    # end to end: every window/level's inputs come from pinned host memory and its results go back to
+    # host memory (ppmstereo_b200.StagedRunner: copies on side streams, overlapped with the kernels)
+    return runner.run([inputs[(T, ds)].host for T, ds, _ in jobs],
+                      lambda dev, i: run_level(P, dev, jobs[i][2], beta, False))
 
 
 # --------------------------------------------------------------------------------------------
@@ -274,6 +280,8 @@ def main():
     h2d = sum(inputs[(T, ds)].in_bytes for T in clip_windows() for ds, _ in LEVELS)
     d2h = sum(inputs[(T, ds)].out_bytes for T in clip_windows() for ds, _ in LEVELS)
 
+    runner = P.StagedRunner(dev)
+
     def timed(from_host: bool, steps: int, time_attend: bool):
         barrier()
         sampler = ClockSampler(local)
@@ -283,7 +291,7 @@ def main():
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for _ in range(steps):
-            run_clip(P, inputs, beta, from_host, time_attend)
+            run_clip(P, inputs, beta, from_host, time_attend, runner)
         e1.record()
         barrier()
         ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
@@ -300,8 +308,39 @@ def main():
     att_ms = [a.elapsed_time(b) for a, b in Counters.attend_events]
     ms_e2e = float("nan")
     if not args.no_e2e:
-        run_clip(P, inputs, beta, True)                  # warm the pinned-copy path once
+        run_clip(P, inputs, beta, True, False, runner)   # warm the pinned-copy path once
         ms_e2e, _ = timed(True, args.steps, False)
+
+    def time_kernel(fn, reps=10):
+        fn()
+        torch.cuda.synchronize()
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(reps + 1)]
+        ev[0].record()
+        for i in range(reps):
+            fn()
+            ev[i + 1].record()
+        torch.cuda.synchronize()
+        return sorted(ev[i].elapsed_time(ev[i + 1]) for i in range(reps))[reps // 2]
+
+    other = []
+    if rank == 0:
+        # K1 / K2 at the 1/4-res level of a 20-frame window, timed alone (HBM-bound kernels; burst copy peak)
+        x = inputs[(KERNEL_SIZE, 4)].dev
+        T4, h4, w4 = KERNEL_SIZE, PAD_H // 4, PAD_W // 4
+        hbm = float(peaks()[0].get("hbm_gbs", 6650.0))
+        ms1 = time_kernel(lambda: P.CorrBlock1D(x["fmap1"], x["fmap2"]))
+        b1 = 2.0 * T4 * D_FEAT * h4 * w4 * 2 + 1.9375 * T4 * h4 * w4 * w4 * 2
+        blk = P.CorrBlock1D(x["fmap1"], x["fmap2"])
+        ms2 = time_kernel(lambda: blk(x["flow_a"]), reps=20)
+        b2 = 228.0 * T4 * h4 * w4
+        for name, ms, byts, traffic in (("corr_build_kernel (K1, 1/4-res, T=20, D=256, bf16 in/out)", ms1, b1, 2.74e9),
+                                        ("corr_lookup_kernel (K2, 1/4-res, T=20, 4 levels, r=4)", ms2, b2, 7.59e8)):
+            other.append({"kernel": name, "bound": "hbm", "achieved": byts / (ms * 1e-3) / 1e9, "peak": hbm,
+                          "unit": "GB/s", "frac": byts / (ms * 1e-3) / 1e9 / hbm, "algorithmic_bytes": byts,
+                          "traffic": traffic, "median_call_ms": ms,
+                          "note": "timed through the Python call (includes output allocation); traffic = "
+                                  "dram bytes of one ncu --set full capture (profiles/)"})
+        del blk
 
     if rank == 0:
         pk, pk_src = peaks()
@@ -318,15 +357,17 @@ def main():
             "e2e": None if args.no_e2e else {"value": world * CLIP_FRAMES / (ms_e2e * 1e-3), "unit": "frames/s",
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "note": "per window and level: inputs copied from pinned host memory, the level's final "
-                            "motion_features_global and lookup read back; copies inside the timed region"},
+                            "motion_features_global and lookup read back into pinned host memory; copies inside "
+                            "the timed region, overlapped with the kernels by ppmstereo_b200.StagedRunner"},
             "gpu_launches": launches,
             "clocks": clocks,
-            "roofline": {"kernel": "ppm_attend_kernel (1/4-res level, T=20, hw=58880, K=5)", "bound": "tensor",
+            "roofline": {"kernel": "ppm_attend3_kernel (1/4-res level, T=20, hw=58880, K=5)", "bound": "tensor",
                          "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
-                         "peak_source": "bf16_tflops_sustained, " + pk_src, "traffic": None,
+                         "peak_source": "bf16_tflops_sustained, " + pk_src, "traffic": 8.7e9,
                          "flops_per_launch": fl, "avg_launch_ms": avg, "launches_timed": len(att_ms),
                          "share_of_step": sum(att_ms) / args.steps / ms_step},
             "attention_tflops_whole_step": clip_attention_flops() / (ms_step * 1e-3) / 1e12,
+            "roofline_other_kernels": other,
         }
         if not args.no_cpu_baseline:
             cores = os.cpu_count() or 1

@@ -4,11 +4,13 @@ Public surface (mirrors the reference's call sites):
   CorrBlock1D            models/core/corr.py:55
   PPMMemory / ppm_memory_read   the block at models/core/ppmstereo.py:501-555
   install(ppmstereo_module)     rewires a loaded reference model onto the two above
+  StagedRunner                  overlapped host<->device staging of independent windows / levels
 There is no CPU or PyTorch fallback: every op fails loudly without libppm_sm100.so + CUDA.
 """
 from .corr import CorrBlock1D, build_pyramid, lookup
 from .memory import PPMMemory, ppm_memory_read, softmax_scale, temporal_pe_table
 from .install import install, forward_update_block
+from .pipeline import StagedRunner
 
 __all__ = ["CorrBlock1D", "build_pyramid", "lookup", "PPMMemory", "ppm_memory_read", "softmax_scale",
-           "temporal_pe_table", "install", "forward_update_block"]
+           "temporal_pe_table", "install", "forward_update_block", "StagedRunner"]

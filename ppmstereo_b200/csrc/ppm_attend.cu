@@ -294,8 +294,7 @@ int attend3_dispatch(const CUtensorMap& mq, const CUtensorMap& mk, const CUtenso
 // 3 = two query tiles, chunked P hand-off (ppm_attend3.cu); 2 = two query tiles (ppm_attend2.cu);
 // 1 = one tile (this file).  2 and 1 are kept for cross-checks.
 static int g_attend_version = 3;
-static int g_exp_emulation = 0;    // v3: exponentials per 8 evaluated on the FMA pipe (0, 2, 3 or 4);
-                                   // measured on B200: 0 is fastest (the softmax warps are issue-bound, not MUFU-bound)
+static int g_exp_emulation = 0;    // v3: 4 = every other exponential by polynomial on the FMA pipe (measured slower)
 static int g_p_in_tmem = 1;
 static float g_rescale_thr = kRescaleThreshold;
 
@@ -305,7 +304,7 @@ static float g_rescale_thr = kRescaleThreshold;
 extern "C" int ppm_debug_set_p_in_tmem(int v) { ppm::g_p_in_tmem = v ? 1 : 0; return PPM_OK; }
 // Test hook: kernel generation (3 = default; 2 and 1 = earlier kernels kept for cross-checks).
 extern "C" int ppm_debug_set_attend_version(int v) { ppm::g_attend_version = (v >= 1 && v <= 3) ? v : 3; return PPM_OK; }
-// Test hook: how many of every 8 exponentials the v3 kernel evaluates by polynomial (0, 2, 3, 4).
+// Test hook: how many of every 8 exponentials the v3 kernel evaluates by polynomial (0 or 4).
 extern "C" int ppm_debug_set_exp_emulation(int n) { ppm::g_exp_emulation = n; return PPM_OK; }
 // Test hook: lazy-rescale threshold in log2 units (0 = rescale whenever the running max grows).
 extern "C" int ppm_debug_set_rescale_threshold(float v) { ppm::g_rescale_thr = v; return PPM_OK; }

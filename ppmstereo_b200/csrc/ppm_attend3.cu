@@ -7,10 +7,16 @@
 //    the S-ready -> P-ready latency no longer sits between two MMAs.
 //  * K'/V tiles travel through ONE in-order ring of five 32 KB slots (K0 V0 K1 V1 ...), the
 //    order the MMA thread consumes and releases them in; 2.5 key tiles of prefetch.
-//  * softmax arithmetic in packed fp32x2 (FFMA2/FADD2); kEmu of every 8 exponentials are
+//  * softmax arithmetic in packed fp32x2 (FFMA2/FADD2).  kEmu of every 8 exponentials CAN be
 //    evaluated on the FMA pipe (Cody-Waite split + degree-3 minimax polynomial, rel. error
-//    9e-5, far below the bf16 rounding of P) because MUFU.EX2 (16/clk/SM) needs exactly as
-//    many cycles per tile as the two MMAs.
+//    9e-5, far below the bf16 rounding of P), the FlashAttention-4 remedy for MUFU.EX2
+//    (16/clk/SM) needing as many cycles per tile as the two MMAs.  Measured on this B200 it
+//    LOSES 5-13 %: the kernel runs at the 1000 W power cap (SM clock 1.55 GHz of 1.97), a run
+//    with the exponential removed altogether is only 1.3 % faster, and the polynomial costs
+//    more energy than the MUFU op it replaces.  Default kEmu = 0; kEmu = 4 is kept as a
+//    tested alternative for parts with more power headroom.
+//  * the MMA warp walks its loop convergently and forms each descriptor with one integer add
+//    (the first version rebuilt two 64-bit descriptors per MMA in one thread: +4 %).
 //  * no integer division in the tile loop; no wait on the previous P.V before publishing P.
 //
 //   warps 0-3   control group (setmaxnreg 88): warp 0 = TMA producer, warp 1 = tcgen05.mma issuer
@@ -175,44 +181,67 @@ ppm_attend3_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
       }
     } else if (warp == 1) {
       // -------------------------------------------------------------- MMA issuer
-      if (elect_one() && n_tiles > 0) {
+      // The whole warp walks the loop (uniform control flow, so ring indices and descriptor words
+      // stay in uniform registers); one elected lane issues the tcgen05 instructions.  A
+      // descriptor is (hi, lo) with hi constant and lo = 0x10000 | (smem address >> 4): stepping
+      // to another K slice or ring slot is one integer add.  (The first version rebuilt both
+      // 64-bit descriptors from scratch for each of the 32 MMAs per key tile in a single thread,
+      // and that thread -- not the tensor pipe, not MUFU -- set the pace of the kernel.)
+      if (n_tiles > 0) {
+        const bool leader = elect_one();
         const uint32_t idesc = umma_idesc(1, 0, 0, kA3Tile, kA3Tile);
-        int slot = 0;                                      // ring position of the next tile to consume
-        uint32_t ph = 0;
-        auto advance = [&]() { if (++slot == kA3Slots) { slot = 0; ph ^= 1; } };
+        const uint32_t desc_hi = static_cast<uint32_t>(umma_desc_sw128(0, 16, 1024) >> 32);
+        const uint32_t desc_lo0 = static_cast<uint32_t>(umma_desc_sw128(0, 16, 1024));
+        const uint32_t q_lo = desc_lo0 + (smem_u32(sQ) >> 4);
+        const uint32_t r_lo = desc_lo0 + (smem_u32(sR) >> 4);
+        constexpr uint32_t kTileLo = kA3TileBytes >> 4;
+        auto kstep_lo = [](int k) -> uint32_t { return ((k >> 2) * kA3HalfBytes + (k & 3) * 32) >> 4; };
+        auto mk = [&](uint32_t lo) -> uint64_t {
+          uint64_t d;
+          asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "r"(lo), "r"(desc_hi));
+          return d;
+        };
         auto issue_qk = [&](int x, int ks) {               // S_x = Q_x K'^T, K' in ring slot ks
-          const uint32_t q_addr = smem_u32(sQ + x * kA3TileBytes);
-          const uint32_t k_addr = smem_u32(sR + ks * kA3TileBytes);
-          #pragma unroll
-          for (int k = 0; k < 8; ++k) {
-            const uint32_t off = (k >> 2) * kA3HalfBytes + (k & 3) * 32;
-            umma_f16_ss(tmem + x * 128, umma_desc_sw128(q_addr + off, 16, 1024),
-                        umma_desc_sw128(k_addr + off, 16, 1024), idesc, k != 0);
+          const uint32_t ql = q_lo + x * kTileLo, kl = r_lo + ks * kTileLo;
+          if (leader) {
+            #pragma unroll
+            for (int k = 0; k < 8; ++k)
+              umma_f16_ss(tmem + x * 128, mk(ql + kstep_lo(k)), mk(kl + kstep_lo(k)), idesc, k != 0);
+            umma_commit(&bar_sf[x]);
           }
-          umma_commit(&bar_sf[x]);
+          __syncwarp();
         };
         auto issue_pv = [&](int x, int vs, int j) {        // O_x += P_x V, chunk by chunk as P arrives
-          const uint32_t v_addr = smem_u32(sR + vs * kA3TileBytes);
+          const uint32_t vl = r_lo + vs * kTileLo;
           #pragma unroll
           for (int c = 0; c < 4; ++c) {
             mbar_wait(&bar_pf[x][c], j & 1);
             tc_fence_after();
-            #pragma unroll
-            for (int kk = 0; kk < 2; ++kk) {
-              const int k = 2 * c + kk;
-              const uint32_t off = (k >> 2) * kA3HalfBytes + (k & 3) * 32;
-              umma_f16_ts(tmem + 256 + x * 128, tmem + x * 128 + k * 8, umma_desc_sw128(v_addr + off, 16, 1024),
-                          idesc, (j | k) != 0);
+            if (leader) {
+              #pragma unroll
+              for (int kk = 0; kk < 2; ++kk) {
+                const int k = 2 * c + kk;
+                umma_f16_ts(tmem + 256 + x * 128, tmem + x * 128 + k * 8, mk(vl + kstep_lo(k)), idesc, (j | k) != 0);
+              }
             }
+            __syncwarp();
           }
-          umma_commit(&bar_o[x]);
+          if (leader) umma_commit(&bar_o[x]);
+          __syncwarp();
         };
+        // Static order PV_A(j) QK_A(j+1) PV_B(j) QK_B(j+1).  (A readiness-polling, work-conserving
+        // order was measured 35 % SLOWER: the kernel runs at the board's power cap, and a warp
+        // that spins on mbarrier.test_wait burns power the tensor pipe needs; try_wait sleeps.)
+        int slot = 0;                                      // ring position of the next tile to consume
+        uint32_t ph = 0;
+        auto advance = [&]() { if (++slot == kA3Slots) { slot = 0; ph ^= 1; } };
         mbar_wait(&bar_q, 0);
         mbar_wait(&bar_full[0], 0);
         tc_fence_after();
         issue_qk(0, 0);
         issue_qk(1, 0);
-        umma_commit(&bar_empty[0]);
+        if (leader) umma_commit(&bar_empty[0]);
+        __syncwarp();
         advance();
         for (int j = 0; j < n_tiles; ++j) {
           const bool more = j + 1 < n_tiles;
@@ -228,10 +257,12 @@ ppm_attend3_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
             issue_qk(0, ks);
           }
           issue_pv(1, vs, j);
-          umma_commit(&bar_empty[vs]);
+          if (leader) umma_commit(&bar_empty[vs]);
+          __syncwarp();
           if (more) {
             issue_qk(1, ks);
-            umma_commit(&bar_empty[ks]);
+            if (leader) umma_commit(&bar_empty[ks]);
+            __syncwarp();
             advance();
           }
         }
@@ -398,13 +429,8 @@ int attend3_dispatch(const CUtensorMap& mq, const CUtensorMap& mk, const CUtenso
   p.picked = picked; p.mf = mf; p.mb = mb; p.mc = mc; p.mt = mt; p.beta = beta; p.out = out;
   p.scale_log2 = scale_log2; p.rescale_thr = rescale_thr; p.T = T; p.Kp = Kp; p.hw = hw;
   const int n_qtiles = (hw + 2 * kA3Tile - 1) / (2 * kA3Tile);
-  switch (emu) {
-    default: return launch_attend3_mf<0>(mq, mk, mv, p, mf_dtype, n_qtiles, b * T, st);
-    case 1: return launch_attend3_mf<1>(mq, mk, mv, p, mf_dtype, n_qtiles, b * T, st);
-    case 2: return launch_attend3_mf<2>(mq, mk, mv, p, mf_dtype, n_qtiles, b * T, st);
-    case 4: return launch_attend3_mf<4>(mq, mk, mv, p, mf_dtype, n_qtiles, b * T, st);
-    case 3: return launch_attend3_mf<3>(mq, mk, mv, p, mf_dtype, n_qtiles, b * T, st);
-  }
+  if (emu == 4) return launch_attend3_mf<4>(mq, mk, mv, p, mf_dtype, n_qtiles, b * T, st);
+  return launch_attend3_mf<0>(mq, mk, mv, p, mf_dtype, n_qtiles, b * T, st);
 }
 
 }  // namespace ppm

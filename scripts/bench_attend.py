@@ -1,7 +1,7 @@
 """GPU aid: time ppm_memory_attend at the 1/4-res 720p shape (T=20, hw=58880, K=5) for the kernel
 generations / exp-emulation settings, and report the deviation between them.
   python scripts/bench_attend.py [T] [h] [w] [reps]"""
-import ctypes, os, sys
+import ctypes, os, subprocess, sys, threading, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import ppmstereo_b200 as P
@@ -12,7 +12,7 @@ h = int(sys.argv[2]) if len(sys.argv) > 2 else 184
 w = int(sys.argv[3]) if len(sys.argv) > 3 else 320
 reps = int(sys.argv[4]) if len(sys.argv) > 4 else 3
 variants = [tuple(int(x) for x in v.split(":")) for v in
-            (sys.argv[5].split(",") if len(sys.argv) > 5 else ["2:0", "3:0", "3:2", "3:3", "3:4"])]
+            (sys.argv[5].split(",") if len(sys.argv) > 5 else ["3:0", "3:4", "2:0", "1:0"])]
 lib = _lib.load()
 lib.ppm_debug_set_attend_version.argtypes = [ctypes.c_int]
 lib.ppm_debug_set_exp_emulation.argtypes = [ctypes.c_int]
@@ -27,12 +27,26 @@ mem = P.PPMMemory(q, k, None, top_k=5)
 mem.pick(sim, torch.ones_like(sim), unc)
 mem.pack_kv(v)
 flops = 4.0 * min(5, T) * 128 * float(h * w) ** 2 * T
+def smi_sampler(stop, out):
+    try:
+        pr = subprocess.Popen(["nvidia-smi", "--query-gpu=clocks.sm,power.draw", "--format=csv,noheader,nounits", "-lms", "100", "-i", "0"],
+                              stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+    except OSError:
+        return
+    for ln in pr.stdout:
+        out.append(ln)
+        if stop.is_set():
+            break
+    pr.terminate()
+
 ref = None
 for ver, emu in variants:
     lib.ppm_debug_set_attend_version(ver)
     lib.ppm_debug_set_exp_emulation(emu)
     out = mem.aggregate(mf, beta)
     torch.cuda.synchronize()
+    stop, lines = threading.Event(), []
+    th = threading.Thread(target=smi_sampler, args=(stop, lines), daemon=True); th.start()
     e = [torch.cuda.Event(enable_timing=True) for _ in range(reps + 1)]
     e[0].record()
     for i in range(reps):
@@ -40,12 +54,16 @@ for ver, emu in variants:
         e[i + 1].record()
     torch.cuda.synchronize()
     ms = [e[i].elapsed_time(e[i + 1]) for i in range(reps)]
+    stop.set()
+    vals = [[float(x) for x in ln.split(',')] for ln in lines if ln.count(',') == 1]
+    clk = sorted(v[0] for v in vals)[len(vals) // 2] if vals else float('nan')
+    pw = max((v[1] for v in vals), default=float('nan'))
     hid = (out.float() - mf.float().permute(0, 2, 1, 3, 4).reshape(out.shape)) / 0.5
     if ref is None:
         ref = hid
     d = (hid - ref).abs()
     print(f"v{ver} emu{emu}: {min(ms):8.2f} ms best, {sum(ms)/len(ms):8.2f} avg  -> {flops/min(ms)/1e9:7.1f} TFLOP/s best, "
           f"{flops/(sum(ms)/len(ms))/1e9:7.1f} avg | vs first: max {float(d.max()):.3e} mean {float(d.mean()):.3e} "
-          f"(|hidden| max {float(ref.abs().max()):.3f})", flush=True)
+          f"(|hidden| max {float(ref.abs().max()):.3f}) | sm clock median {clk:.0f} MHz, power max {pw:.0f} W ({len(vals)} samples)", flush=True)
 lib.ppm_debug_set_attend_version(3)
 lib.ppm_debug_set_exp_emulation(0)

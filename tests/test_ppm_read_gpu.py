@@ -146,13 +146,13 @@ def set_exp_emulation(n: int):
 
 
 def test_kernel_generations_agree(P):
-    """v3 (default: chunked P hand-off, MUFU exponentials), v3 with 2/3/4 of 8 exponentials by polynomial, the v2
+    """v3 (default: chunked P hand-off, MUFU exponentials), v3 with every other exponential by polynomial, the v2
     two-tile kernel and the v1 one-tile kernel see the same operands; they differ only in summation
     order and in the 9e-5 relative error of the polynomial, i.e. by at most one bf16 ulp of hidden."""
     t = make_case(1, 9, 20, 31, seed=15)                  # hw = 620: 5 key tiles, 3 two-tile CTAs per frame
     outs = {}
     try:
-        for v, emu in ((3, 0), (3, 2), (3, 3), (3, 4), (2, 0), (1, 0)):
+        for v, emu in ((3, 0), (3, 4), (2, 0), (1, 0)):
             set_attend_version(v)
             set_exp_emulation(emu)
             outs[(v, emu)] = run_read(P, t)[1]
