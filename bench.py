@@ -37,10 +37,8 @@ LEVELS = [(16, ITERS // 2), (8, ITERS // 2), (4, ITERS)]   # (downscale, iterati
 
 
 def clip_windows():
-    w, stride = [], KERNEL_SIZE // 2
-    for i in range(0, CLIP_FRAMES, stride):
-        w.append(len(range(i, min(i + KERNEL_SIZE, CLIP_FRAMES))))
-    return w                                     # [20, 20, 20, 10]
+    from ppmstereo_b200 import shard       # host-side partitioning logic (no CUDA needed to import)
+    return [e - s for s, e in shard.clip_windows(CLIP_FRAMES, KERNEL_SIZE)]     # [20, 20, 20, 10]
 
 
 def attention_flops(T: int, hw: int, k: int = TOP_K) -> float:
@@ -294,11 +292,10 @@ def main():
             run_clip(P, inputs, beta, from_host, time_attend, runner)
         e1.record()
         barrier()
-        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
-        if world > 1:
-            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        # every rank ran `steps` clips of its own; time = max over ranks (device events)
+        _, ms = P.shard.reduce_throughput(CLIP_FRAMES * steps, e0.elapsed_time(e1), device=dev)
         clocks = sampler.stop() if rank == 0 and not from_host else None
-        return float(ms) / steps, clocks
+        return ms / steps, clocks
 
     for _ in range(args.warmup):
         run_clip(P, inputs, beta, False)

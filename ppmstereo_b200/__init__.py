@@ -11,6 +11,7 @@ from .corr import CorrBlock1D, build_pyramid, lookup
 from .memory import PPMMemory, ppm_memory_read, softmax_scale, temporal_pe_table
 from .install import install, forward_update_block
 from .pipeline import StagedRunner
+from . import shard
 
 __all__ = ["CorrBlock1D", "build_pyramid", "lookup", "PPMMemory", "ppm_memory_read", "softmax_scale",
-           "temporal_pe_table", "install", "forward_update_block", "StagedRunner"]
+           "temporal_pe_table", "install", "forward_update_block", "StagedRunner", "shard"]
