@@ -107,6 +107,16 @@ int ppm_memory_attend(const void* Q, const void* K, const void* V, const int32_t
                       const float* beta, float scale, int b, int T, int Kp, int hw, float* out,
                       void* stream);
 
+/* Row-band form of ppm_memory_attend (optional split of ONE clip over GPUs): only the
+ * query pixels [q_begin, q_begin + q_count) of every frame are computed and stored; Q, K, V, mf and
+ * out keep the full-frame layouts above, keys and values of ALL hw pixels take part.  A rank that
+ * owns a band of image rows calls this after gathering the value bands of the other ranks.
+ * ppm_memory_attend == ppm_memory_attend_band(..., 0, hw, ...). */
+int ppm_memory_attend_band(const void* Q, const void* K, const void* V, const int32_t* picked,
+                           const void* mf, int mf_dtype, int64_t mb, int64_t mc, int64_t mt,
+                           const float* beta, float scale, int b, int T, int Kp, int hw, int q_begin,
+                           int q_count, float* out, void* stream);
+
 /* Bytes of the packed operands for (b, T, Kp, hw): q, k, v in that order. */
 int ppm_pack_bytes(int b, int T, int Kp, int hw, size_t* q_bytes, size_t* k_bytes,
                    size_t* v_bytes);

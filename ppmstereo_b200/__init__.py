@@ -12,6 +12,7 @@ from .memory import PPMMemory, ppm_memory_read, softmax_scale, temporal_pe_table
 from .install import install, forward_update_block
 from .pipeline import StagedRunner
 from . import shard
+from .rowband import RowBandMemory, gather_bands, row_bands
 
 __all__ = ["CorrBlock1D", "build_pyramid", "lookup", "PPMMemory", "ppm_memory_read", "softmax_scale",
-           "temporal_pe_table", "install", "forward_update_block", "StagedRunner", "shard"]
+           "temporal_pe_table", "install", "forward_update_block", "StagedRunner", "shard", "RowBandMemory", "gather_bands", "row_bands"]

@@ -288,8 +288,8 @@ int attend2_dispatch(const CUtensorMap& mq, const CUtensorMap& mk, const CUtenso
 
 int attend3_dispatch(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv, const int32_t* picked,
                      const void* mf, int mf_dtype, long long mb, long long mc, long long mt, const float* beta,
-                     float scale_log2, float rescale_thr, int emu, int b, int T, int Kp, int hw, float* out,
-                     cudaStream_t st);
+                     float scale_log2, float rescale_thr, int emu, int b, int T, int Kp, int hw, int q_begin,
+                     int q_count, float* out, cudaStream_t st);
 
 // 3 = two query tiles, chunked P hand-off (ppm_attend3.cu); 2 = two query tiles (ppm_attend2.cu);
 // 1 = one tile (this file).  2 and 1 are kept for cross-checks.
@@ -312,7 +312,17 @@ extern "C" int ppm_debug_set_rescale_threshold(float v) { ppm::g_rescale_thr = v
 extern "C" int ppm_memory_attend(const void* Q, const void* K, const void* V, const int32_t* picked, const void* mf,
                                  int mf_dtype, int64_t mb, int64_t mc, int64_t mt, const float* beta, float scale,
                                  int b, int T, int Kp, int hw, float* out, void* stream) {
+  return ppm_memory_attend_band(Q, K, V, picked, mf, mf_dtype, mb, mc, mt, beta, scale, b, T, Kp, hw, 0, hw, out, stream);
+}
+
+extern "C" int ppm_memory_attend_band(const void* Q, const void* K, const void* V, const int32_t* picked,
+                                      const void* mf, int mf_dtype, int64_t mb, int64_t mc, int64_t mt,
+                                      const float* beta, float scale, int b, int T, int Kp, int hw, int q_begin,
+                                      int q_count, float* out, void* stream) {
   using namespace ppm;
+  PPM_CHECK(q_begin >= 0 && q_count >= 0 && q_begin + q_count <= hw, PPM_ERR_ARG,
+            "ppm_memory_attend_band: query band [%d, %d) outside [0, %d)", q_begin, q_begin + q_count, hw);
+  if (q_count == 0) return PPM_OK;
   PPM_CHECK(Q && K && V && picked && mf && beta && out, PPM_ERR_ARG, "ppm_memory_attend: null pointer");
   PPM_CHECK(b > 0 && T > 0 && Kp > 0 && hw > 0, PPM_ERR_ARG, "ppm_memory_attend: bad shape");
   PPM_CHECK(mf_dtype == PPM_F32 || mf_dtype == PPM_BF16, PPM_ERR_ARG, "ppm_memory_attend: bad dtype");
@@ -346,7 +356,9 @@ extern "C" int ppm_memory_attend(const void* Q, const void* K, const void* V, co
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (g_attend_version == 3 && g_p_in_tmem)
     return attend3_dispatch(mq, mk, mv, picked, mf, mf_dtype, mb, mc, mt, beta, p.scale_log2, p.rescale_thr,
-                            g_exp_emulation, b, T, Kp, hw, out, st);
+                            g_exp_emulation, b, T, Kp, hw, q_begin, q_count, out, st);
+  PPM_CHECK(q_begin == 0 && q_count == hw, PPM_ERR_UNSUPPORTED,
+            "ppm_memory_attend_band: only the default (v3) kernel supports a partial query band");
   if (g_attend_version >= 2 && g_p_in_tmem)
     return attend2_dispatch(mq, mk, mv, picked, mf, mf_dtype, mb, mc, mt, beta, p.scale_log2, p.rescale_thr, b, T,
                             Kp, hw, out, st);

@@ -48,6 +48,7 @@ struct Attend3Params {
   float* out;
   float scale_log2, rescale_thr;
   int T, Kp, hw;
+  int q_begin, q_end;        // query pixels [q_begin, q_end) are computed and stored (row-band split)
 };
 
 __device__ __forceinline__ float a3_ld(const float* p) { return __ldg(p); }
@@ -123,7 +124,7 @@ ppm_attend3_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int frame = blockIdx.y;
   const int bb = frame / p.T;
-  const int q0 = blockIdx.x * 2 * kA3Tile;
+  const int q0 = p.q_begin + blockIdx.x * 2 * kA3Tile;
   const int tiles_per_frame = (p.hw + kA3Tile - 1) / kA3Tile;
   int n_frames = 0;
   for (int n = 0; n < p.Kp; ++n) n_frames += (__ldg(p.picked + frame * p.Kp + n) >= 0);
@@ -384,7 +385,7 @@ ppm_attend3_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
         #pragma unroll
         for (int e = 0; e < 32; ++e) o[e] = 0u;
       }
-      if (pix < p.hw) {
+      if (pix < p.q_end) {
         #pragma unroll
         for (int e = 0; e < 32; ++e) {
           const int ch = c * 32 + e;
@@ -423,12 +424,13 @@ static int launch_attend3_mf(const CUtensorMap& mq, const CUtensorMap& mk, const
 // Entry used by ppm_memory_attend (ppm_attend.cu).  `emu` = exponentials per 8 evaluated on the FMA pipe.
 int attend3_dispatch(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv, const int32_t* picked,
                      const void* mf, int mf_dtype, long long mb, long long mc, long long mt, const float* beta,
-                     float scale_log2, float rescale_thr, int emu, int b, int T, int Kp, int hw, float* out,
-                     cudaStream_t st) {
+                     float scale_log2, float rescale_thr, int emu, int b, int T, int Kp, int hw, int q_begin,
+                     int q_count, float* out, cudaStream_t st) {
   Attend3Params p{};
   p.picked = picked; p.mf = mf; p.mb = mb; p.mc = mc; p.mt = mt; p.beta = beta; p.out = out;
   p.scale_log2 = scale_log2; p.rescale_thr = rescale_thr; p.T = T; p.Kp = Kp; p.hw = hw;
-  const int n_qtiles = (hw + 2 * kA3Tile - 1) / (2 * kA3Tile);
+  p.q_begin = q_begin; p.q_end = q_begin + q_count;
+  const int n_qtiles = (q_count + 2 * kA3Tile - 1) / (2 * kA3Tile);
   if (emu == 4) return launch_attend3_mf<4>(mq, mk, mv, p, mf_dtype, n_qtiles, b * T, st);
   return launch_attend3_mf<0>(mq, mk, mv, p, mf_dtype, n_qtiles, b * T, st);
 }

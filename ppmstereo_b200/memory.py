@@ -111,8 +111,11 @@ class PPMMemory:
                                            self.v_packed.data_ptr(), st), "ppm_pack_value")
 
     def aggregate(self, motion_features: torch.Tensor, beta: torch.Tensor,
-                  scale: Optional[float] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
-        """ppm_memory_attend on the packed operands; returns (b*T, 128, h, w) fp32."""
+                  scale: Optional[float] = None, out: Optional[torch.Tensor] = None,
+                  band: Optional[Tuple[int, int]] = None) -> torch.Tensor:
+        """ppm_memory_attend on the packed operands; returns (b*T, 128, h, w) fp32.
+        ``band = (first_pixel, n_pixels)`` restricts the computed/stored queries (row-band split); the
+        other pixels of ``out`` are left untouched."""
         b, T, hw = self.b, self.T, self.hw
         mf, *ms = _bcthw(motion_features, "motion_features")
         if mf.shape != self.query.shape:
@@ -123,11 +126,13 @@ class PPMMemory:
         scale = softmax_scale(C) if scale is None else float(scale)
         if out is None:
             out = torch.empty(b * T, C, self.h, self.w, dtype=torch.float32, device=mf.device)
-        _lib.check(self.lib.ppm_memory_attend(self.q_packed.data_ptr(), self.k_packed.data_ptr(),
-                                              self.v_packed.data_ptr(), self.picked.data_ptr(), mf.data_ptr(),
-                                              _lib.dtype_code(mf), *ms, beta.data_ptr(), scale, b, T,
-                                              self.top_k, hw, out.data_ptr(), _lib.stream_ptr()),
-                   "ppm_memory_attend")
+        q_begin, q_count = (0, hw) if band is None else (int(band[0]), int(band[1]))
+        _lib.check(self.lib.ppm_memory_attend_band(self.q_packed.data_ptr(), self.k_packed.data_ptr(),
+                                                   self.v_packed.data_ptr(), self.picked.data_ptr(), mf.data_ptr(),
+                                                   _lib.dtype_code(mf), *ms, beta.data_ptr(), scale, b, T,
+                                                   self.top_k, hw, q_begin, q_count, out.data_ptr(),
+                                                   _lib.stream_ptr()),
+                   "ppm_memory_attend_band")
         return out
 
     def attend(self, value: torch.Tensor, motion_features: torch.Tensor, beta: torch.Tensor,

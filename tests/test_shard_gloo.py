@@ -78,3 +78,45 @@ def test_world_size_2_gloo_reduction():
 
 def test_reduce_without_process_group_is_local():
     assert shard.reduce_throughput(40.0, 12.5) == (40.0, 12.5)
+
+
+# ---------------------------------------------------------------- row-band split (optional)
+from ppmstereo_b200 import rowband
+
+
+@pytest.mark.parametrize("h,world", [(184, 8), (46, 4), (5, 2), (3, 4), (0, 2)])
+def test_row_bands_cover_rows_once(h, world):
+    bands = rowband.row_bands(h, world)
+    assert len(bands) == world and bands[0][0] == 0 and bands[-1][1] == h
+    assert all(a[1] == b[0] for a, b in zip(bands, bands[1:]))
+    sizes = [b - a for a, b in bands]
+    assert max(sizes) - min(sizes) <= 1
+
+
+def _band_worker(rank, world, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        h = 5                                                       # uneven: bands of 3 and 2 rows
+        full = torch.arange(2 * 3 * 4 * h * 6, dtype=torch.float32).reshape(2, 3, 4, h, 6)
+        r0, r1 = rowband.row_bands(h, world)[rank]
+        got = rowband.gather_bands(full[:, :, :, r0:r1].contiguous(), h, 3)
+        unc = torch.arange(8 * h * 6, dtype=torch.float32).reshape(8, 1, h, 6)
+        got_u = rowband.gather_bands(unc[:, :, r0:r1].contiguous(), h, 2)
+        out.put((rank, bool(torch.equal(got, full)), bool(torch.equal(got_u, unc))))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_gather_bands_world_size_2_gloo():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_band_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in range(2))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert res == [(0, True, True), (1, True, True)]
