@@ -9,13 +9,15 @@
 // directly (no transpose pass, no repack).  bf16 inputs use kind::f16, fp32 inputs kind::tf32.
 //
 // One work item is a 128 x NT tile (NT <= 256) of one row problem:
-//   warp 0    TMA producer (4-stage mbarrier ring over the channel axis)
+//   warp 0    TMA producer (6-stage mbarrier ring over the channel axis: 144 KB in flight to cover the L2 latency)
 //   warp 1    TMEM allocation + single-thread tcgen05.mma issue, accumulator in TMEM
 //   warps 2-9 epilogue: tcgen05.ld (one output row per thread, 32 columns at a time), scale by
 //             1/sqrt(D), form levels 1..4 by pair-averaging IN REGISTERS (a thread owns whole
 //             row segments, so pooling along j needs no communication) and store every level
-//             straight from registers with 16-byte vector stores (a 32-column chunk of a bf16
-//             row is 64 contiguous bytes; L2 merges the sector halves before they reach HBM).
+//             through a dense smem tile and ONE TMA store per level and work item (levels 0-2;
+//             a thread's own 64-byte row segments written with LSU stores touch 32 different
+//             128-byte lines per instruction and made the LSU tag stage the bottleneck); the two
+//             small levels (8 and 4 bytes per thread and chunk) go straight from registers.
 // Persistent: one CTA per SM loops over (image row, M tile, N tile) work items; the smem ring
 // runs on across items and the accumulator is double-buffered in TMEM (2 x 256 columns), so
 // the TMA loads and MMAs of item i+1 overlap the epilogue stores of item i.
@@ -28,7 +30,7 @@
 namespace ppm {
 
 constexpr int kCbM = 128;            // pixels of W1 per CTA (UMMA M)
-constexpr int kCbStages = 4;
+constexpr int kCbStages = 6;
 constexpr int kCbThreads = 320;      // TMA warp, MMA warp, 8 epilogue warps
 constexpr int kCbMaxN = 256;
 constexpr int kCbTmemCols = 512;     // two 256-column accumulators: MMA of tile i+1 overlaps the epilogue of tile i
@@ -43,7 +45,12 @@ struct CorrBuildParams {
   float sqrt_d;
   float inv_sqrt_d;                  // 1/sqrt(D) when that is exact (sqrt(D) a power of two), else 0
   int vec_ok[kCbLevels];             // level rows allow the full-width vector store
+  int tma_out;                       // levels 0..2 leave through TMA stores from a staged smem tile
+  int stage_bufs;                    // staging buffers (1 or 2)
 };
+
+struct CbStoreMaps { CUtensorMap m[3]; };
+constexpr int kCbTmaLevels = 3;
 
 template <typename ElemT> struct CbTraits;
 template <> struct CbTraits<__nv_bfloat16> {
@@ -69,6 +76,22 @@ template <> struct CbTraits<float> {
 
 __device__ __forceinline__ float cb_round(float v, float) { return v; }
 __device__ __forceinline__ float cb_round(float v, __nv_bfloat16) { return bf16_round_f(v); }
+
+// ---- TMA store (shared -> global), bulk-group completion
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* m, const void* src, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
+               ::"l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int kPending>
+__device__ __forceinline__ void bulk_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(kPending) : "memory");
+}
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void epi_barrier(int id) {          // the 8 epilogue warps only
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "n"(kCbEpiWarps * 32) : "memory");
+}
 
 // ---- fast epilogue for bf16 output with an exact power-of-two 1/sqrt(D)
 // Rounding goes through cvt.rn.bf16x2.f32 (F2FP, ALU pipe): the scalar cvt.rn.bf16.f32 is an XU-pipe
@@ -148,7 +171,7 @@ __device__ __forceinline__ void cb_store_row(OutT* dst, const float (&v)[32], in
 template <typename ElemT, typename OutT>
 __global__ void __launch_bounds__(kCbThreads, 1)
 corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constant__ CUtensorMap map2,
-                  const CorrBuildParams p) {
+                  const __grid_constant__ CbStoreMaps omap, const CorrBuildParams p) {
   using Tr = CbTraits<ElemT>;
   constexpr int kChunkBytes = Tr::kKC * 128;                    // one [KC][128 B] box
   constexpr int kAChunks = kCbM / Tr::kChunkW;
@@ -158,6 +181,7 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
 
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* stage0 = smem + kCbStages * kStageBytes;             // output staging (TMA-store path)
   __shared__ uint64_t bar_full[kCbStages], bar_empty[kCbStages], bar_acc_full[2], bar_acc_empty[2];
   __shared__ uint32_t tmem_slot;
 
@@ -253,6 +277,16 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
       const long long row = static_cast<long long>(bh) * p.W1 + m;
       const bool row_ok = m < p.W1;
       const int buf = it & 1;
+      // staging layout of one buffer: L0 [128][NT] | L1 [128][NT/2] | L2 [128][NT/4] bf16, dense rows
+      const int sb = p.stage_bufs == 2 ? (it & 1) : 0;
+      uint8_t* stg = stage0 + sb * (kCbM * p.NT * 2 * 7 / 4);
+      const bool store_thread = (warp == 2 && lane == 0);
+      if (p.tma_out) {
+        if (store_thread) {                                   // the TMA stores that last read this buffer are done
+          if (p.stage_bufs == 2) bulk_wait_read<1>(); else bulk_wait_read<0>();
+        }
+        epi_barrier(1);
+      }
       mbar_wait(&bar_acc_full[buf], (it >> 1) & 1);
       tc_fence_after();
       const uint32_t acc = tmem_base + buf * kCbMaxN + (static_cast<uint32_t>(q * 32) << 16);
@@ -279,7 +313,15 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
                   w[j] = pack_bf16x2(__fmul_rn(a, 0.5f), __fmul_rn(c, 0.5f));
                 }
               }
-              if (l <= p.n_levels && row_ok) {
+              if (p.tma_out && l < kCbTmaLevels) {
+                if (l <= p.n_levels) {                   // stage this thread's row segment: n bf16 = n/2 words
+                  const int ntl = p.NT >> l;
+                  const int off_l = l == 0 ? 0 : (l == 1 ? kCbM * p.NT * 2 : kCbM * p.NT * 3);
+                  uint4* d4 = reinterpret_cast<uint4*>(stg + off_l + ((q * 32 + lane) * ntl + ((cc * 32) >> l)) * 2);
+                  #pragma unroll
+                  for (int j = 0; j < n / 8; ++j) d4[j] = make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
+                }
+              } else if (l <= p.n_levels && row_ok) {
                 const int Wl = p.width[l];
                 const int col0 = (n0 + cc * 32) >> l;
                 cb_store_words(reinterpret_cast<__nv_bfloat16*>(p.level[l]) + row * Wl + col0, w, n, Wl - col0, p.vec_ok[l]);
@@ -317,7 +359,20 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
       tc_fence_before();                            // this warp's TMEM reads of the buffer are done
       __syncwarp();
       if (lane == 0) mbar_arrive(&bar_acc_empty[buf]);
+      if (p.tma_out) {
+        fence_proxy_async_smem();                   // staged rows -> visible to the TMA engine
+        epi_barrier(2);
+        if (store_thread) {
+          const int nl = p.n_levels < kCbTmaLevels - 1 ? p.n_levels : kCbTmaLevels - 1;
+          for (int l = 0; l <= nl; ++l) {
+            const int off_l = l == 0 ? 0 : (l == 1 ? kCbM * p.NT * 2 : kCbM * p.NT * 3);
+            tma_store_3d(&omap.m[l], stg + off_l, n0 >> l, m0, bh);   // rows past W1, columns past W_l are clipped
+          }
+          bulk_commit();
+        }
+      }
     }
+    if (p.tma_out && warp == 2 && lane == 0) bulk_wait_all();
   }
   __syncthreads();
   if (warp == 1) {
@@ -331,7 +386,7 @@ static int launch_corr_build(const void* f1, const void* f2, int B, int D, int H
                              int ld1, int ld2, void* const* levels, int n_levels, cudaStream_t st) {
   using Tr = CbTraits<ElemT>;
   constexpr int kStageBytes = (kCbM / Tr::kChunkW + kCbMaxN / Tr::kChunkW) * Tr::kKC * 128;
-  constexpr int kSmem = kCbStages * kStageBytes + 1024;
+  constexpr int kRingBytes = kCbStages * kStageBytes;
   CorrBuildParams p{};
   p.n_levels = n_levels;
   for (int l = 0; l <= n_levels; ++l) { p.level[l] = levels[l]; p.width[l] = W2 >> l; }
@@ -375,14 +430,42 @@ static int launch_corr_build(const void* f1, const void* f2, int B, int D, int H
     int rc = make_tensor_map(&m2, dt, 4, f2, dims, str, box, Tr::kTmaSwizzle);
     if (rc) return rc;
   }
+  // Output path: levels 0..2 of a bf16 pyramid with an exact scale leave through TMA stores from a
+  // staged smem tile (dense [128][NT >> l] rows); needs 16-byte row pitches in global memory.
+  CbStoreMaps om{};
+  p.tma_out = 0;
+  p.stage_bufs = 1;
+  int smem_bytes = kRingBytes + 1024;
+  if (sizeof(OutT) == 2 && p.inv_sqrt_d != 0.f) {
+    bool ok = true;
+    const int nl = n_levels < kCbTmaLevels - 1 ? n_levels : kCbTmaLevels - 1;
+    for (int l = 0; l <= nl; ++l)
+      ok = ok && ((static_cast<size_t>(W2 >> l) * 2) % 16 == 0) && (reinterpret_cast<uintptr_t>(levels[l]) % 16 == 0);
+    if (ok) {
+      for (int l = 0; l <= nl && ok; ++l) {
+        const uint64_t Wl = static_cast<uint64_t>(W2 >> l);
+        const uint64_t dims[3] = {Wl, (uint64_t)W1, (uint64_t)B * H};
+        const uint64_t str[2] = {Wl * 2, (uint64_t)W1 * Wl * 2};
+        const uint32_t obox[3] = {static_cast<uint32_t>(p.NT >> l), static_cast<uint32_t>(kCbM), 1};
+        ok = make_tensor_map(&om.m[l], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, levels[l], dims, str, obox,
+                             CU_TENSOR_MAP_SWIZZLE_NONE) == PPM_OK;
+      }
+      if (ok) {
+        const int stage_bytes = kCbM * p.NT * 2 * 7 / 4;
+        p.tma_out = 1;
+        p.stage_bufs = (kRingBytes + 2 * stage_bytes + 1024 <= 227 * 1024) ? 2 : 1;
+        smem_bytes = kRingBytes + p.stage_bufs * stage_bytes + 1024;
+      }
+    }
+  }
   auto kern = corr_build_kernel<ElemT, OutT>;
-  PPM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+  PPM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
   // persistent: one CTA per SM (it owns all 512 TMEM columns), static round-robin over the tiles
   int dev = 0, n_sm = 148;
   PPM_CUDA(cudaGetDevice(&dev));
   PPM_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
   const int grid = static_cast<int>(p.n_tiles < n_sm ? p.n_tiles : n_sm);
-  kern<<<grid, kCbThreads, kSmem, st>>>(m1, m2, p);
+  kern<<<grid, kCbThreads, smem_bytes, st>>>(m1, m2, om, p);
   PPM_CUDA(cudaGetLastError());
   return PPM_OK;
 }
