@@ -117,6 +117,17 @@ int ppm_memory_attend_band(const void* Q, const void* K, const void* V, const in
                            const float* beta, float scale, int b, int T, int Kp, int hw, int q_begin,
                            int q_count, float* out, void* stream);
 
+/* ---------------------------------------------------------------------------------------
+ * K4  convex upsampling of the flow (models/core/ppmstereo.py:185-197, called
+ * per iteration at :577).
+ *   p[n,k,i,j,y,x]          = softmax_k mask[n, (k*rate + i)*rate + j, y, x]          k = 0..8
+ *   out[n,c,rate*y+i,rate*x+j] = sum_k p * rate * flow[n, c, y + k/3 - 1, x + k%3 - 1]   (zero outside)
+ * flow (N,2,H,W) fp32; mask (N, 9*rate*rate, H, W) dtype mask_dtype (for PPM_BF16 the softmax result is
+ * rounded to bf16 before the product, as torch.softmax does for a bf16 input); out (N,2,rate*H,rate*W)
+ * fp32, 16-byte aligned.  rate must be 4. */
+int ppm_convex_upsample(const float* flow, const void* mask, int mask_dtype, int N, int H, int W,
+                        int rate, float* out, void* stream);
+
 /* Bytes of the packed operands for (b, T, Kp, hw): q, k, v in that order. */
 int ppm_pack_bytes(int b, int T, int Kp, int hw, size_t* q_bytes, size_t* k_bytes,
                    size_t* v_bytes);

@@ -305,3 +305,21 @@ def ppm_memory_read(query, key, pe, value, motion_features, sim, strive, uncerta
         "score_norm": score_norm, "hidden": hidden,
         "motion_features_global": out.reshape(b * T, c, h, w),
     }
+
+
+# ---------------------------------------------------------------------------------------------
+# convex upsampling (models/core/ppmstereo.py:185-197)
+# ---------------------------------------------------------------------------------------------
+def convex_upsample(flow: torch.Tensor, mask: torch.Tensor, rate: int = 4) -> torch.Tensor:
+    """out[n,c,rate*y+i,rate*x+j] = sum_k softmax_k(mask[n,(k*rate+i)*rate+j,y,x]) * rate*flow[n,c,y+k//3-1,x+k%3-1],
+    zero outside the image.  flow (N,2,H,W); mask (N,9*rate^2,H,W) fp32 or bf16 -- torch.softmax returns the
+    input dtype, so for a bf16 mask the weights are bf16-rounded before the fp32 product (:188, :193)."""
+    N, _, H, W = flow.shape
+    w = torch.softmax(mask.reshape(N, 9, rate, rate, H, W), dim=1).float()        # rounded to mask.dtype first
+    fp = torch.nn.functional.pad(rate * flow.float(), (1, 1, 1, 1))              # zero padding (:190)
+    out = torch.zeros(N, 2, rate, rate, H, W)
+    for k in range(9):
+        ky, kx = divmod(k, 3)
+        nb = fp[:, :, ky:ky + H, kx:kx + W]                                       # (N,2,H,W) neighbour k
+        out += w[:, k][:, None] * nb[:, :, None, None]
+    return out.permute(0, 1, 4, 2, 5, 3).reshape(N, 2, rate * H, rate * W)

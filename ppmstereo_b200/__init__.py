@@ -4,6 +4,7 @@ Public surface (mirrors the reference's call sites):
   CorrBlock1D            models/core/corr.py:55
   PPMMemory / ppm_memory_read   the block at models/core/ppmstereo.py:501-555
   install(ppmstereo_module)     rewires a loaded reference model onto the two above
+  convex_upsample               PPMStereo.convex_upsample (models/core/ppmstereo.py:185-197) as one kernel
   StagedRunner                  overlapped host<->device staging of independent windows / levels
 There is no CPU or PyTorch fallback: every op fails loudly without libppm_sm100.so + CUDA.
 """
@@ -12,7 +13,8 @@ from .memory import PPMMemory, ppm_memory_read, softmax_scale, temporal_pe_table
 from .install import install, forward_update_block
 from .pipeline import StagedRunner
 from . import shard
+from .upsample import convex_upsample
 from .rowband import RowBandMemory, gather_bands, row_bands
 
 __all__ = ["CorrBlock1D", "build_pyramid", "lookup", "PPMMemory", "ppm_memory_read", "softmax_scale",
-           "temporal_pe_table", "install", "forward_update_block", "StagedRunner", "shard", "RowBandMemory", "gather_bands", "row_bands"]
+           "temporal_pe_table", "install", "forward_update_block", "StagedRunner", "shard", "convex_upsample", "RowBandMemory", "gather_bands", "row_bands"]

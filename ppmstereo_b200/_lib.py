@@ -35,6 +35,7 @@ SIGNATURES = {
     "ppm_memory_attend_band": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int64, c_int64,
                                        c_int64, c_void_p, c_float, c_int, c_int, c_int, c_int, c_int, c_int,
                                        c_void_p, c_void_p]),
+    "ppm_convex_upsample": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     "ppm_pack_bytes": (c_int, [c_int, c_int, c_int, c_int, POINTER(c_size_t), POINTER(c_size_t),
                                POINTER(c_size_t)]),
 }

@@ -1,0 +1,102 @@
+// K4: convex upsampling of the flow field (first glue op moved onto the GPU path).
+// Replaces PPMStereo.convex_upsample (reference models/core/ppmstereo.py:185-197), called once per update
+// iteration at :577:
+//   mask.view(N, 1, 9, r, r, H, W) -> softmax over the 9 taps -> sum_k p_k * (r * flow)[3x3 neighbour k]
+//   -> (N, 2, r*H, r*W), zero padding outside the image.
+// The reference spends ~7 passes over (N, 9*r*r, H, W) tensors (view/contiguous, softmax, unfold, mul, sum,
+// permute/contiguous); here every mask value is read once and every output written once.
+// HBM-bound: 9*r*r*e_mask + 2*r*r*4 (+ 8 for the flow) bytes per coarse pixel.
+//   thread = one coarse pixel (n, y, x); lanes = consecutive x, so each of the 9*r*r mask channels is read with
+//   a full-width coalesced request and every store instruction writes r*4 contiguous bytes per lane;
+//   per fine row i: softmax of the r columns' 9 taps in fp32 (rounded to bf16 when the mask is bf16 -- that is
+//   what torch.softmax returns for a bf16 input), then the two flow channels.
+#include <math.h>
+
+#include "../../include/ppm_b200.h"
+#include "common.cuh"
+
+namespace ppm {
+
+constexpr int kCuThreads = 128;
+constexpr int kCuRate = 4;
+
+__device__ __forceinline__ float cu_ld(const float* p) { return __ldg(p); }
+__device__ __forceinline__ float cu_ld(const __nv_bfloat16* p) { return __bfloat162float(__ldg(p)); }
+__device__ __forceinline__ float cu_round(float v, const float*) { return v; }
+__device__ __forceinline__ float cu_round(float v, const __nv_bfloat16*) { return bf16_round_f(v); }
+
+template <typename MaskT>
+__global__ void __launch_bounds__(kCuThreads)
+convex_upsample_kernel(const float* __restrict__ flow, const MaskT* __restrict__ mask, float* __restrict__ out,
+                       int H, int W) {
+  const int n = blockIdx.y;
+  const int HW = H * W;
+  const int q = blockIdx.x * kCuThreads + threadIdx.x;
+  if (q >= HW) return;
+  const int y = q / W, x = q - y * W;
+  // 3x3 neighbourhood of r * flow, zero padded (F.unfold(rate * flow, [3, 3], padding=1))
+  float f[2][9];
+  const float* fl = flow + static_cast<long long>(n) * 2 * HW;
+  #pragma unroll
+  for (int k = 0; k < 9; ++k) {
+    const int yy = y + k / 3 - 1, xx = x + k % 3 - 1;
+    const bool in = yy >= 0 && yy < H && xx >= 0 && xx < W;
+    #pragma unroll
+    for (int c = 0; c < 2; ++c)
+      f[c][k] = in ? __fmul_rn(static_cast<float>(kCuRate), __ldg(fl + c * HW + yy * W + xx)) : 0.f;
+  }
+  const MaskT* mk = mask + static_cast<long long>(n) * 9 * kCuRate * kCuRate * HW + q;
+  float* o = out + static_cast<long long>(n) * 2 * kCuRate * kCuRate * HW + static_cast<long long>(y) * kCuRate * kCuRate * W +
+             x * kCuRate;
+  #pragma unroll
+  for (int i = 0; i < kCuRate; ++i) {
+    float m[9][kCuRate];
+    #pragma unroll
+    for (int k = 0; k < 9; ++k)
+      #pragma unroll
+      for (int j = 0; j < kCuRate; ++j)
+        m[k][j] = cu_ld(mk + static_cast<long long>((k * kCuRate + i) * kCuRate + j) * HW);
+    float r0[kCuRate], r1[kCuRate];
+    #pragma unroll
+    for (int j = 0; j < kCuRate; ++j) {
+      float mx = m[0][j];
+      #pragma unroll
+      for (int k = 1; k < 9; ++k) mx = fmaxf(mx, m[k][j]);
+      float e[9], s = 0.f;
+      #pragma unroll
+      for (int k = 0; k < 9; ++k) { e[k] = expf(m[k][j] - mx); s += e[k]; }
+      float a0 = 0.f, a1 = 0.f;
+      #pragma unroll
+      for (int k = 0; k < 9; ++k) {
+        const float pk = cu_round(__fdiv_rn(e[k], s), mask);
+        a0 = __fadd_rn(a0, __fmul_rn(pk, f[0][k]));
+        a1 = __fadd_rn(a1, __fmul_rn(pk, f[1][k]));
+      }
+      r0[j] = a0; r1[j] = a1;
+    }
+    const long long row = static_cast<long long>(i) * kCuRate * W;
+    *reinterpret_cast<float4*>(o + row) = make_float4(r0[0], r0[1], r0[2], r0[3]);
+    *reinterpret_cast<float4*>(o + static_cast<long long>(kCuRate) * kCuRate * HW + row) = make_float4(r1[0], r1[1], r1[2], r1[3]);
+  }
+}
+
+}  // namespace ppm
+
+extern "C" int ppm_convex_upsample(const float* flow, const void* mask, int mask_dtype, int N, int H, int W,
+                                   int rate, float* out, void* stream) {
+  using namespace ppm;
+  PPM_CHECK(flow && mask && out, PPM_ERR_ARG, "ppm_convex_upsample: null pointer");
+  PPM_CHECK(N > 0 && H > 0 && W > 0, PPM_ERR_ARG, "ppm_convex_upsample: bad shape");
+  PPM_CHECK(rate == kCuRate, PPM_ERR_UNSUPPORTED, "ppm_convex_upsample: rate %d (only 4, the reference's call site)", rate);
+  PPM_CHECK(mask_dtype == PPM_F32 || mask_dtype == PPM_BF16, PPM_ERR_ARG, "ppm_convex_upsample: bad dtype");
+  PPM_CHECK(N <= 65535, PPM_ERR_UNSUPPORTED, "ppm_convex_upsample: N > 65535");
+  PPM_CHECK((reinterpret_cast<uintptr_t>(out) & 15) == 0, PPM_ERR_ARG, "ppm_convex_upsample: out must be 16-byte aligned");
+  dim3 grid((H * W + kCuThreads - 1) / kCuThreads, N);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (mask_dtype == PPM_BF16)
+    convex_upsample_kernel<__nv_bfloat16><<<grid, kCuThreads, 0, st>>>(flow, static_cast<const __nv_bfloat16*>(mask), out, H, W);
+  else
+    convex_upsample_kernel<float><<<grid, kCuThreads, 0, st>>>(flow, static_cast<const float*>(mask), out, H, W);
+  PPM_CUDA(cudaGetLastError());
+  return PPM_OK;
+}

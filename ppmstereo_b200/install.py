@@ -14,6 +14,7 @@ import torch.nn.functional as F
 
 from .corr import CorrBlock1D
 from .memory import C, PPMMemory, softmax_scale
+from .upsample import convex_upsample
 
 
 def forward_update_block(self, image1, update_block, corr_fn, flow, net, inp, motion_hidden_state,
@@ -48,7 +49,7 @@ def forward_update_block(self, image1, update_block, corr_fn, flow, net, inp, mo
         if self.use_convex_3d:
             flow_up = flow_out = self.convex_upsample_3d(flow, up_mask, rate=4, T=t)
         else:
-            flow_up = flow_out = self.convex_upsample(flow, up_mask, rate=4)
+            flow_up = flow_out = convex_upsample(flow, up_mask, rate=4)     # K4 (ppmstereo.py:185-197)
         uncertainty_up = F.interpolate(uncertainty_score, scale_factor=4 * interp_scale, mode="bilinear")
         if interp_scale > 1:
             size = (interp_scale * flow_out.shape[2], interp_scale * flow_out.shape[3])

@@ -14,7 +14,11 @@ KEYS = ["gpu__time_duration.sum", "gpc__cycles_elapsed.avg.per_second", "dram__b
         "launch__shared_mem_per_block_dynamic", "launch__occupancy_limit_shared_mem", "sm__cycles_elapsed.avg",
         "smsp__issue_active.avg.pct_of_peak_sustained_active", "l1tex__t_sectors_pipe_lsu_mem_global_op_ld.sum",
         "l1tex__t_requests_pipe_lsu_mem_global_op_ld.sum", "l1tex__t_sectors_pipe_lsu_mem_global_op_st.sum",
-        "l1tex__t_requests_pipe_lsu_mem_global_op_st.sum", "lts__t_bytes.sum"]
+        "l1tex__t_requests_pipe_lsu_mem_global_op_st.sum", "lts__t_bytes.sum",
+        "sm__mem_tensor_cycles_active.avg.pct_of_peak_sustained_elapsed",
+        "l1tex__data_pipe_tc_wavefronts_mem_shared.sum.pct_of_peak_sustained_elapsed",
+        "lts__t_sectors_srcunit_tex_op_read.sum", "lts__t_sectors_srcunit_tex_op_write.sum",
+        "lts__t_sectors_srcunit_ltcfabric.sum", "lts__t_sector_hit_rate.pct"]
 
 
 def launch_table(path):

@@ -147,7 +147,30 @@ def model_cases():
         f_off += n_it[lvl] * T
 
 
+def upsample_cases():
+    """PPMStereo.convex_upsample (models/core/ppmstereo.py:185-197) on fp32 and bf16 masks; the method uses no
+    module state, so it is called unbound."""
+    import importlib
+    ref_import.load_reference()
+    ppm = importlib.import_module("models.core.ppmstereo")
+    g = torch.Generator().manual_seed(21)
+    N, H, W = 2, 7, 13
+    flow = torch.randn(N, 2, H, W, generator=g) * 6.0
+    mask = torch.randn(N, 9 * 16, H, W, generator=g) * 2.0
+    out32 = ppm.PPMStereo.convex_upsample(None, flow, mask, 4)
+    mask16 = mask.bfloat16()
+    out16 = ppm.PPMStereo.convex_upsample(None, flow, mask16, 4)
+    np.savez_compressed(os.path.join(HERE, "convex_upsample.npz"), flow=flow.numpy(), mask=mask.numpy(),
+                        out_fp32_mask=out32.float().numpy(), mask_bf16=bf16_bits(mask16),
+                        out_bf16_mask=out16.float().numpy())
+    print("convex_upsample", tuple(out32.shape), out16.dtype)
+
+
 if __name__ == "__main__":
     torch.set_num_threads(os.cpu_count() or 1)
+    if "--upsample-only" in sys.argv:
+        upsample_cases()
+        sys.exit(0)
     corr_cases()
     model_cases()
+    upsample_cases()

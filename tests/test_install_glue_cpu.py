@@ -1,8 +1,8 @@
 """Drop-in glue check (CPU, build container only): the reference PPMStereo with
 ``ppmstereo_b200.install`` applied must reproduce the reference's own disparity.
 
-The CUDA kernels cannot run here, so the two kernel-backed classes the glue calls (CorrBlock1D,
-PPMMemory) are replaced IN THIS TEST by stand-ins built on the CPU oracle -- the oracle the GPU parity
+The CUDA kernels cannot run here, so the kernel-backed pieces the glue calls (CorrBlock1D,
+PPMMemory, convex_upsample) are replaced IN THIS TEST by stand-ins built on the CPU oracle -- the oracle the GPU parity
 tests hold the kernels to.  What is under test is the host-side mirror: the replacement
 ``forward_update_block`` (same signature, side effects and tensor plumbing as models/core/ppmstereo.py:
 426-594) and the ``CorrBlock1D`` rebinding.  Bar (north_star): final disparity within 0.01 px mean
@@ -53,6 +53,7 @@ def test_installed_model_reproduces_reference_disparity(golden_dir, monkeypatch)
     inst = importlib.import_module("ppmstereo_b200.install")
     monkeypatch.setattr(inst, "CorrBlock1D", OracleCorrBlock1D)
     monkeypatch.setattr(inst, "PPMMemory", OraclePPMMemory)
+    monkeypatch.setattr(inst, "convex_upsample", O.convex_upsample)
     try:
         inst.install(ppm)
         assert ppm.CorrBlock1D is OracleCorrBlock1D

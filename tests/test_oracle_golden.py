@@ -81,3 +81,17 @@ def test_temporal_pe_endpoints():
 def test_topk_no_op_when_T_le_k():
     s = torch.rand(2, 1, 4, 4)
     assert O.topk_pick(s, 5).all()
+
+
+@pytest.mark.parametrize("kind", ["fp32", "bf16"])
+def test_convex_upsample_matches_reference(golden_dir, kind):
+    g = _load(golden_dir, "convex_upsample")
+    flow = torch.from_numpy(g["flow"])
+    if kind == "fp32":
+        mask, ref = torch.from_numpy(g["mask"]), torch.from_numpy(g["out_fp32_mask"])
+    else:
+        mask = torch.from_numpy(g["mask_bf16"].astype(np.int16)).view(torch.bfloat16)
+        ref = torch.from_numpy(g["out_bf16_mask"])
+    out = O.convex_upsample(flow, mask, 4)
+    assert out.shape == ref.shape
+    assert (out - ref).abs().max() <= 1e-5 * ref.abs().max()       # fp32 summation order only

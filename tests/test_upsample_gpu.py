@@ -1,0 +1,70 @@
+"""K4 convex upsampling: CUDA kernel vs the reference fixture and vs the oracle."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import ppm_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def P():
+    if not torch.cuda.is_available():
+        pytest.skip("needs a GPU")
+    import ppmstereo_b200
+    return ppmstereo_b200
+
+
+@pytest.mark.parametrize("kind", ["fp32", "bf16"])
+def test_vs_reference_golden(P, golden_dir, kind):
+    g = np.load(os.path.join(golden_dir, "convex_upsample.npz"))
+    flow = torch.from_numpy(g["flow"])
+    if kind == "fp32":
+        mask, ref, tol = torch.from_numpy(g["mask"]), torch.from_numpy(g["out_fp32_mask"]), 1e-5
+    else:
+        mask = torch.from_numpy(g["mask_bf16"].astype(np.int16)).view(torch.bfloat16)
+        ref, tol = torch.from_numpy(g["out_bf16_mask"]), 2.0 ** -8      # a 1-ulp exp difference can flip a bf16 weight
+    got = P.convex_upsample(flow.cuda(), mask.cuda(), 4).cpu()
+    assert got.shape == ref.shape and got.dtype == torch.float32
+    d = (got - ref).abs()
+    assert float(d.max()) <= tol * float(ref.abs().max())
+    assert float(d.mean()) <= 1e-5 * float(ref.abs().mean()) + 1e-7
+
+
+@pytest.mark.parametrize("shape", [(1, 1, 1), (3, 5, 130), (2, 46, 80)])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_vs_oracle_shapes(P, shape, dtype):
+    N, H, W = shape
+    g = torch.Generator().manual_seed(N * 1000 + H * 10 + W)
+    flow = torch.randn(N, 2, H, W, generator=g) * 10
+    mask = (torch.randn(N, 144, H, W, generator=g) * 3).to(dtype)
+    want = O.convex_upsample(flow, mask, 4)
+    got = P.convex_upsample(flow.cuda(), mask.cuda(), 4).cpu()
+    d = (got - want).abs()
+    assert float(d.max()) <= (1e-5 if dtype == torch.float32 else 2.0 ** -8) * float(want.abs().max())
+    assert float(d.mean()) <= 1e-5 * float(want.abs().mean()) + 1e-7
+
+
+def test_partition_of_unity_full_size(P):
+    """Size-independent property at the 720p 1/4-res shape: the weights of every fine pixel sum to one, so a
+    constant flow c upsamples to 4c away from the border, and the op is linear in the flow."""
+    N, H, W = 20, 184, 320
+    g = torch.Generator(device="cuda").manual_seed(3)
+    mask = torch.randn(N, 144, H, W, generator=g, device="cuda")
+    const = torch.full((N, 2, H, W), 1.5, device="cuda")
+    up = P.convex_upsample(const, mask, 4)
+    assert float((up[:, :, 4:-4, 4:-4] - 6.0).abs().max()) <= 1e-5
+    a = torch.randn(N, 2, H, W, generator=g, device="cuda")
+    b = torch.randn(N, 2, H, W, generator=g, device="cuda")
+    lin = P.convex_upsample(a + 2 * b, mask, 4) - (P.convex_upsample(a, mask, 4) + 2 * P.convex_upsample(b, mask, 4))
+    assert float(lin.abs().max()) <= 1e-4
+
+
+def test_rejects_cpu_tensors_and_bad_shapes(P):
+    with pytest.raises(RuntimeError):
+        P.convex_upsample(torch.zeros(1, 2, 4, 4), torch.zeros(1, 144, 4, 4))
+    with pytest.raises(RuntimeError):
+        P.convex_upsample(torch.zeros(1, 2, 4, 4).cuda(), torch.zeros(1, 100, 4, 4).cuda())
