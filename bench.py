@@ -330,8 +330,15 @@ def main():
         blk = P.CorrBlock1D(x["fmap1"], x["fmap2"])
         ms2 = time_kernel(lambda: blk(x["flow_a"]), reps=20)
         b2 = 228.0 * T4 * h4 * w4
-        for name, ms, byts, traffic in (("corr_build_kernel (K1, 1/4-res, T=20, D=256, bf16 in/out)", ms1, b1, 2.74e9),
-                                        ("corr_lookup_kernel (K2, 1/4-res, T=20, 4 levels, r=4)", ms2, b2, 7.59e8)):
+        gk = torch.Generator(device=dev).manual_seed(5)
+        up_mask = torch.randn(T4, 144, h4, w4, generator=gk, device=dev).bfloat16()       # autocast dtype of mask_2d
+        ms4 = time_kernel(lambda: P.convex_upsample(x["flow_a"], up_mask))
+        b4 = T4 * h4 * w4 * (144.0 * 2 + 8 + 128)
+        del up_mask
+        for name, ms, byts, traffic in (("corr_build_kernel (K1, 1/4-res, T=20, D=256, bf16 in/out)", ms1, b1, 2.61e9),
+                                        ("corr_lookup_kernel (K2, 1/4-res, T=20, 4 levels, r=4)", ms2, b2, 7.59e8),
+                                        ("convex_upsample_kernel (K4, SURVEY 8f glue op, 1/4-res, T=20, bf16 mask; "
+                                         "not part of the timed step)", ms4, b4, None)):
             other.append({"kernel": name, "bound": "hbm", "achieved": byts / (ms * 1e-3) / 1e9, "peak": hbm,
                           "unit": "GB/s", "frac": byts / (ms * 1e-3) / 1e9 / hbm, "algorithmic_bytes": byts,
                           "traffic": traffic, "median_call_ms": ms,

@@ -313,9 +313,12 @@ def ppm_memory_read(query, key, pe, value, motion_features, sim, strive, uncerta
 def convex_upsample(flow: torch.Tensor, mask: torch.Tensor, rate: int = 4) -> torch.Tensor:
     """out[n,c,rate*y+i,rate*x+j] = sum_k softmax_k(mask[n,(k*rate+i)*rate+j,y,x]) * rate*flow[n,c,y+k//3-1,x+k%3-1],
     zero outside the image.  flow (N,2,H,W); mask (N,9*rate^2,H,W) fp32 or bf16 -- torch.softmax returns the
-    input dtype, so for a bf16 mask the weights are bf16-rounded before the fp32 product (:188, :193)."""
+    input dtype, so for a bf16 mask the weights are bf16-rounded before the fp32 product (:188, :193).
+    The rounding restated here is torch's CUDA softmax (fp32 math, ONE rounding of the result), which is what
+    the reference runs; torch's CPU softmax rounds a bf16 input twice (exp stored as bf16, then the
+    normalised value), so 0.7 % of its weights differ by one bf16 ulp from this function."""
     N, _, H, W = flow.shape
-    w = torch.softmax(mask.reshape(N, 9, rate, rate, H, W), dim=1).float()        # rounded to mask.dtype first
+    w = torch.softmax(mask.float().reshape(N, 9, rate, rate, H, W), dim=1).to(mask.dtype).float()
     fp = torch.nn.functional.pad(rate * flow.float(), (1, 1, 1, 1))              # zero padding (:190)
     out = torch.zeros(N, 2, rate, rate, H, W)
     for k in range(9):

@@ -26,12 +26,36 @@ def test_vs_reference_golden(P, golden_dir, kind):
         mask, ref, tol = torch.from_numpy(g["mask"]), torch.from_numpy(g["out_fp32_mask"]), 1e-5
     else:
         mask = torch.from_numpy(g["mask_bf16"].astype(np.int16)).view(torch.bfloat16)
-        ref, tol = torch.from_numpy(g["out_bf16_mask"]), 2.0 ** -8      # a 1-ulp exp difference can flip a bf16 weight
+        # CPU fixture: torch's CPU softmax rounds a bf16 input twice (0.7 % of the weights one ulp off)
+        ref, tol = torch.from_numpy(g["out_bf16_mask"]), 2.0 ** -8
     got = P.convex_upsample(flow.cuda(), mask.cuda(), 4).cpu()
     assert got.shape == ref.shape and got.dtype == torch.float32
     d = (got - ref).abs()
     assert float(d.max()) <= tol * float(ref.abs().max())
-    assert float(d.mean()) <= 1e-5 * float(ref.abs().mean()) + 1e-7
+    assert float(d.mean()) <= (1e-5 if kind == "fp32" else 1e-4) * float(ref.abs().mean()) + 1e-7
+
+
+def _torch_sequence(flow, mask, rate=4):
+    """The reference's op sequence (models/core/ppmstereo.py:185-197) restated with torch ops, run on the GPU."""
+    import torch.nn.functional as F
+    n, _, h, w = flow.shape
+    m = torch.softmax(mask.view(n, 1, 9, rate, rate, h, w).contiguous(), dim=2)
+    up = F.unfold(rate * flow, [3, 3], padding=1).view(n, 2, 9, 1, 1, h, w)
+    up = torch.sum(m * up, dim=2).permute(0, 1, 4, 2, 5, 3).contiguous()
+    return up.reshape(n, 2, rate * h, rate * w).float()
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_vs_torch_cuda_sequence(P, dtype):
+    """Pins the bf16 rounding to torch's CUDA softmax (one rounding), which the CPU fixture cannot."""
+    g = torch.Generator().manual_seed(77)
+    flow = (torch.randn(2, 2, 23, 37, generator=g) * 10).cuda()
+    mask = (torch.randn(2, 144, 23, 37, generator=g) * 3).to(dtype).cuda()
+    want = _torch_sequence(flow, mask)
+    got = P.convex_upsample(flow, mask, 4)
+    d = (got - want).abs()
+    assert float(d.max()) <= (1e-5 if dtype == torch.float32 else 2.0 ** -8) * float(want.abs().max())
+    assert float(d.mean()) <= 1e-5 * float(want.abs().mean())
 
 
 @pytest.mark.parametrize("shape", [(1, 1, 1), (3, 5, 130), (2, 46, 80)])
@@ -45,7 +69,8 @@ def test_vs_oracle_shapes(P, shape, dtype):
     got = P.convex_upsample(flow.cuda(), mask.cuda(), 4).cpu()
     d = (got - want).abs()
     assert float(d.max()) <= (1e-5 if dtype == torch.float32 else 2.0 ** -8) * float(want.abs().max())
-    assert float(d.mean()) <= 1e-5 * float(want.abs().mean()) + 1e-7
+    if H * W >= 64:        # (a single coarse pixel has too few values for a mean bound under bf16 weight flips)
+        assert float(d.mean()) <= 1e-5 * float(want.abs().mean()) + 1e-7
 
 
 def test_partition_of_unity_full_size(P):
