@@ -63,6 +63,16 @@ int ppm_corr_lookup(const void* const* levels, int vol_dtype, const float* flow,
                     int W1, int W2, int radius, int n_levels, float* out, void* stream);
 
 /* ---------------------------------------------------------------------------------------
+ * K3-pre  QAM query/key frame similarity, once per cascade level (SURVEY.md 8a row a6;
+ * PPMStereo.compute_qk_similarity, models/core/ppmstereo.py:397-423).
+ *   x_[b,t,:]  = mean over the 128 channels of AdaptiveMaxPool2d((h/4, w/4))(x[b,:,t])   x = query, key
+ *   sim[b,i,j] = cos(k_[b,i], q_[b,j]) with F.cosine_similarity's eps = 1e-8 clamp on each norm
+ * query, key indexed src[b*sb + c*sc + t*st + y*w + x], dtype `dtype`; pooled_ws: 2*b*T*(h/4)*(w/4) fp32
+ * scratch; sim (b,T,T) fp32.  fp32 arithmetic, deterministic reduction order. */
+int ppm_qk_similarity(const void* query, const void* key, int dtype, int64_t sb, int64_t sc, int64_t st,
+                      int b, int T, int h, int w, float* pooled_ws, float* sim, void* stream);
+
+/* ---------------------------------------------------------------------------------------
  * K3a  QAM frame scoring + top-k pick (models/core/ppmstereo.py:501-513, :532-533).
  *   conf[b,j]      = mean_{hw} uncertainty[b*T + j]
  *   score[b,i,j]   = exp(-S[b,i,j] / (sum_j S[b,i,j] + T)) * sim[b,i,j] + conf[b,j]

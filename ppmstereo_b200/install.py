@@ -27,9 +27,9 @@ def forward_update_block(self, image1, update_block, corr_fn, flow, net, inp, mo
     qk = attn_block.to_qk(inp)
     query = qk[:, :c].reshape(b, t, c, h, w).permute(0, 2, 1, 3, 4)
     key = qk[:, c:].reshape(b, t, c, h, w).permute(0, 2, 1, 3, 4)
-    sim_score = self.compute_qk_similarity(query, key, t=t).float().contiguous()
-    strive_time = torch.ones_like(sim_score)
     memory = PPMMemory(query, key, None, top_k=5)
+    sim_score = memory.similarity()                       # compute_qk_similarity (ppmstereo.py:397-423)
+    strive_time = torch.ones_like(sim_score)
     scale = softmax_scale(c)
     autocast = torch.autocast("cuda", dtype=torch.bfloat16, enabled=bool(self.mixed_precision))
     flow_out = flow

@@ -78,6 +78,19 @@ class PPMMemory:
                                            self.pe.data_ptr(), b, T, self.hw, self.q_packed.data_ptr(),
                                            _lib.stream_ptr()), "ppm_pack_query")
 
+    def similarity(self) -> torch.Tensor:
+        """QAM frame similarity of this level's raw query / key (PPMStereo.compute_qk_similarity,
+        models/core/ppmstereo.py:397-423): (b, 1, T, T) fp32, sim[b,0,i,j] = cos(k_i, q_j)."""
+        b, T, h, w = self.b, self.T, self.h, self.w
+        if self.query.dtype != self.key.dtype or self.q_strides != self.k_strides:
+            raise RuntimeError("query and key must share dtype and layout")
+        ws = torch.empty(2 * b * T * (h // 4) * (w // 4), dtype=torch.float32, device=self.query.device)
+        sim = torch.empty(b, 1, T, T, dtype=torch.float32, device=self.query.device)
+        _lib.check(self.lib.ppm_qk_similarity(self.query.data_ptr(), self.key.data_ptr(), _lib.dtype_code(self.query),
+                                              *self.q_strides, b, T, h, w, ws.data_ptr(), sim.data_ptr(),
+                                              _lib.stream_ptr()), "ppm_qk_similarity")
+        return sim
+
     def pick(self, sim: torch.Tensor, strive: torch.Tensor, uncertainty: torch.Tensor) -> torch.Tensor:
         """QAM score + top-k; updates ``strive`` in place; returns the bool mask (b,1,T,T)."""
         b, T = self.b, self.T

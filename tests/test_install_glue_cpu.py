@@ -37,6 +37,9 @@ class OraclePPMMemory:
         b, c, T, h, w = query.shape
         self.pe = O.temporal_pe(T, c) if pe is None else pe
 
+    def similarity(self):
+        return O.qk_similarity(self.query, self.key)
+
     def read(self, value, motion_features, sim, strive, uncertainty, beta, scale=None):
         r = O.ppm_memory_read(self.query, self.key, self.pe, value, motion_features, sim, strive, uncertainty,
                               float(beta), scale, self.top_k)

@@ -219,3 +219,29 @@ def test_linearity_in_value_full_size(P):
     scale = float(ab.abs().max())
     assert float((a + b2 - ab).abs().max()) <= 6e-2 * scale
     assert float((a + b2 - ab).abs().mean()) <= 3e-3 * scale
+
+
+# ---------------------------------------------------------------- row a6: QAM frame similarity
+@pytest.mark.parametrize("name", ["ppm_read_l16", "ppm_read_l08"])
+def test_similarity_vs_reference_golden(P, golden_dir, name):
+    g = np.load(os.path.join(golden_dir, name + ".npz"))
+    q, k = torch.from_numpy(g["query"]).cuda(), torch.from_numpy(g["key"]).cuda()
+    sim = P.PPMMemory(q, k, None).similarity().cpu()
+    ref = torch.from_numpy(g["sim"])                       # captured from the reference's compute_qk_similarity
+    assert sim.shape == ref.shape and sim.dtype == torch.float32
+    assert float((sim - ref).abs().max()) <= 1e-5
+
+
+@pytest.mark.parametrize("shape", [(1, 6, 46, 80), (2, 5, 9, 13), (1, 3, 4, 4)])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_similarity_vs_oracle_adaptive_windows(P, shape, dtype):
+    """h, w not divisible by 4: AdaptiveMaxPool2d windows of uneven size (46 -> 11 rows at the 1/16 level)."""
+    b, T, h, w = shape
+    g = torch.Generator().manual_seed(h * 100 + w)
+    q = torch.randn(b, 128, T, h, w, generator=g).to(dtype)
+    k = torch.randn(b, 128, T, h, w, generator=g).to(dtype)
+    want = O.qk_similarity(q.float(), k.float())
+    got = P.PPMMemory(q.cuda(), k.cuda(), None).similarity().cpu()
+    assert float((got - want).abs().max()) <= 1e-5
+    again = P.PPMMemory(q.cuda(), k.cuda(), None).similarity().cpu()
+    assert torch.equal(got, again)                        # deterministic: it feeds the top-k pick
