@@ -281,6 +281,7 @@ ppm_attend3_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
     const float c1 = p.scale_log2;
     const float thr = p.rescale_thr / c1;
     const uint64_t c1x2 = f2_pack(c1, c1);
+    const uint32_t a_sf = smem_u32(&bar_sf[x]), a_pf = smem_u32(&bar_pf[x][0]);
     const int tail_valid = p.hw - (tiles_per_frame - 1) * kA3Tile;   // keys in the last tile of a frame
     float m_used = -INFINITY;
     uint64_t acc0 = f2_pack(0.f, 0.f), acc1 = acc0;
@@ -288,28 +289,33 @@ ppm_attend3_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
     for (int j = 0; j < n_tiles; ++j) {
       const bool is_tail = (t == tiles_per_frame - 1) && tail_valid < kA3Tile;
       if (++t == tiles_per_frame) t = 0;
-      mbar_wait(&bar_sf[x], j & 1);
+      mbar_wait_addr(a_sf, j & 1);
       tc_fence_after();
       uint32_t s[4][32];
-      #pragma unroll
-      for (int c = 0; c < 4; ++c) tmem_ld_x32(s_addr + c * 32, s[c]);
-      tmem_ld_wait();
-      if (is_tail) {                                         // mask the keys past the frame end
-        #pragma unroll
-        for (int c = 0; c < 4; ++c)
+      float mx[4];
+      auto row_max = [&](int c) {
+        if (is_tail) {                                       // mask the keys past the frame end
           #pragma unroll
           for (int e = 0; e < 32; ++e)
             if (c * 32 + e >= tail_valid) s[c][e] = 0xff800000u;
-      }
-      float mx[4];
-      #pragma unroll
-      for (int c = 0; c < 4; ++c) {
+        }
         mx[c] = __uint_as_float(s[c][0]);
         #pragma unroll
         for (int e = 1; e < 31; e += 2)
           mx[c] = a3_max3(mx[c], __uint_as_float(s[c][e]), __uint_as_float(s[c][e + 1]));
         mx[c] = fmaxf(mx[c], __uint_as_float(s[c][31]));
-      }
+      };
+      // two loads in flight while the maxima of the first two column blocks are formed
+      tmem_ld_x32(s_addr, s[0]);
+      tmem_ld_x32(s_addr + 32, s[1]);
+      tmem_ld_wait();
+      tmem_ld_x32(s_addr + 64, s[2]);
+      tmem_ld_x32(s_addr + 96, s[3]);
+      row_max(0);
+      row_max(1);
+      tmem_ld_wait();
+      row_max(2);
+      row_max(3);
       const float m_tile = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
       const bool grow = m_tile > m_used + thr;
       if (__any_sync(0xffffffffu, grow)) {
@@ -359,7 +365,7 @@ ppm_attend3_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
         tmem_st_wait();
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&bar_pf[x][c]);
+        if (lane == 0) mbar_arrive_addr(a_pf + c * 8);
       }
     }
     if (n_tiles > 0) {
