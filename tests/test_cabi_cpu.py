@@ -42,6 +42,13 @@ def test_argument_errors_are_reported(lib):
     assert rc == 3 and b"radius" in lib.ppm_last_error()
     rc = lib.ppm_qam_pick(*[ctypes.addressof(buf)] * 3, 0, 1, 65, 4, 5, *[ctypes.addressof(buf)] * 5, None)
     assert rc == 3 and b"T = 65" in lib.ppm_last_error()
+    a = ctypes.addressof(buf)
+    rc = lib.ppm_memory_attend_band(a, a, a, a, a, 0, 1, 1, 1, a, 0.05, 1, 2, 2, 100, 90, 20, a, None)
+    assert rc == 1 and b"query band" in lib.ppm_last_error()      # [90, 110) outside [0, 100)
+    rc = lib.ppm_convex_upsample(a, a, 0, 1, 4, 4, 8, a, None)
+    assert rc == 3 and b"rate" in lib.ppm_last_error()            # only the reference's rate = 4
+    rc = lib.ppm_qk_similarity(a, a, 0, 1, 1, 1, 1, 2, 3, 8, a, a, None)
+    assert rc == 1 and b">= 4" in lib.ppm_last_error()            # h // 4 == 0: the reference's pool would be empty
     q, k, v = ctypes.c_size_t(), ctypes.c_size_t(), ctypes.c_size_t()
     assert lib.ppm_pack_bytes(1, 20, 5, 3680, ctypes.byref(q), ctypes.byref(k), ctypes.byref(v)) == 0
     assert (q.value, k.value, v.value) == (20 * 3680 * 256, 100 * 3680 * 256, 20 * 128 * 3680 * 2)
