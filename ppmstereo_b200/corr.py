@@ -33,8 +33,10 @@ def _pitched(t: torch.Tensor, mult: int) -> torch.Tensor:
 
 
 def build_pyramid(fmap1: torch.Tensor, fmap2: torch.Tensor, num_levels: int = 4,
-                  out_dtype: Optional[torch.dtype] = None) -> List[torch.Tensor]:
-    """ppm_corr_build: returns ``num_levels + 1`` tensors (B*H*W1, 1, 1, W2 >> l)."""
+                  out_dtype: Optional[torch.dtype] = None,
+                  levels: Optional[List[torch.Tensor]] = None) -> List[torch.Tensor]:
+    """ppm_corr_build: returns ``num_levels + 1`` tensors (B*H*W1, 1, 1, W2 >> l).  ``levels`` may pass
+    buffers of exactly those shapes to be overwritten (no allocation on the call path)."""
     _check_fmap(fmap1, "fmap1")
     _check_fmap(fmap2, "fmap2")
     if fmap1.dtype != fmap2.dtype or fmap1.shape[:3] != fmap2.shape[:3]:
@@ -46,8 +48,12 @@ def build_pyramid(fmap1: torch.Tensor, fmap2: torch.Tensor, num_levels: int = 4,
     out_dtype = out_dtype or fmap1.dtype
     mult = 8 if fmap1.dtype == torch.bfloat16 else 4
     f1, f2 = _pitched(fmap1, mult), _pitched(fmap2, mult)
-    levels = [torch.empty(B * H * W1, 1, 1, W2 >> l, dtype=out_dtype, device=fmap1.device)
-              for l in range(num_levels + 1)]
+    shapes = [(B * H * W1, 1, 1, W2 >> l) for l in range(num_levels + 1)]
+    if levels is None:
+        levels = [torch.empty(s, dtype=out_dtype, device=fmap1.device) for s in shapes]
+    elif [tuple(t.shape) for t in levels] != shapes or any(
+            t.dtype != out_dtype or not t.is_contiguous() or t.device != fmap1.device for t in levels):
+        raise RuntimeError("levels must be contiguous tensors of shapes %s and dtype %s" % (shapes, out_dtype))
     lib = _lib.load()
     code_out = _lib.PPM_BF16 if out_dtype == torch.bfloat16 else _lib.PPM_F32
     _lib.check(lib.ppm_corr_build(f1.data_ptr(), f2.data_ptr(), _lib.dtype_code(f1), B, D, H, W1, W2,
@@ -79,10 +85,19 @@ class CorrBlock1D:
         self.radius = radius
         B, _, H, W1 = fmap1.shape
         self._w2 = fmap2.shape[3]
-        ys, xs = torch.meshgrid(torch.arange(H, device=fmap1.device), torch.arange(W1, device=fmap1.device),
-                                indexing="ij")
-        self.coords = torch.stack([xs, ys], dim=0).float()[None].repeat(B, 1, 1, 1)   # corr.py:47-52
+        self._grid = (B, H, W1, fmap1.device)
+        self._coords = None
         self.corr_pyramid = build_pyramid(fmap1.detach(), fmap2.detach(), num_levels)
+
+    @property
+    def coords(self) -> torch.Tensor:
+        """(B, 2, H, W1) pixel (x, y) grid, as coords_grid at corr.py:47-52.  Nothing on the path reads it
+        (the lookup kernel derives x from the thread index), so it is built on first access only."""
+        if self._coords is None:
+            B, H, W1, dev = self._grid
+            ys, xs = torch.meshgrid(torch.arange(H, device=dev), torch.arange(W1, device=dev), indexing="ij")
+            self._coords = torch.stack([xs, ys], dim=0).float()[None].repeat(B, 1, 1, 1)
+        return self._coords
 
     def __call__(self, flow: torch.Tensor) -> torch.Tensor:
         return lookup(self.corr_pyramid, flow.detach(), self._w2, self.radius, self.num_levels)
