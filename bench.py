@@ -338,7 +338,7 @@ def main():
         b4 = T4 * h4 * w4 * (144.0 * 2 + 8 + 128)
         del up_mask
         for name, ms, byts, traffic in (("corr_build_kernel (K1, 1/4-res, T=20, D=256, bf16 in/out)", ms1, b1, 2.61e9),
-                                        ("corr_lookup_kernel (K2, 1/4-res, T=20, 4 levels, r=4)", ms2, b2, 7.59e8),
+                                        ("corr_lookup_l0_kernel (K2b, 1/4-res, T=20, 4 levels from one level-0 span, r=4)", ms2, b2, 4.69e8),
                                         ("convex_upsample_kernel (K4, SURVEY 8f glue op, 1/4-res, T=20, bf16 mask; "
                                          "not part of the timed step)", ms4, b4, None)):
             other.append({"kernel": name, "bound": "hbm", "achieved": byts / (ms * 1e-3) / 1e9, "peak": hbm,
@@ -348,6 +348,22 @@ def main():
                                   "allocation); traffic = "
                                   "dram bytes of one ncu --set full capture (profiles/)"})
         del blk
+        same_box = None
+        try:                                            # the library the reference calls at ppmstereo.py:550, same box
+            import flash_attn
+            g2 = torch.Generator(device=dev).manual_seed(6)
+            hw4_ = h4 * w4
+            qf = torch.randn(1, hw4_, 1, C_QKV, generator=g2, device=dev).bfloat16()
+            kf = torch.randn(1, TOP_K * hw4_, 1, C_QKV, generator=g2, device=dev).bfloat16()
+            vf = torch.randn(1, TOP_K * hw4_, 1, C_QKV, generator=g2, device=dev).bfloat16()
+            msf = time_kernel(lambda: flash_attn.flash_attn_func(qf, kf, vf, 0.0, softmax_scale=P.softmax_scale(C_QKV),
+                                                                 causal=False), reps=5)
+            same_box = {"library": "flash_attn " + flash_attn.__version__ + " flash_attn_func (the reference's call, "
+                                   "ppmstereo.py:550), one query frame, Lq=58880 Lk=294400 d=128",
+                        "ms_per_query_frame": msf, "tflops": attention_flops(KERNEL_SIZE, hw4_) / KERNEL_SIZE / (msf * 1e-3) / 1e12}
+            del qf, kf, vf
+        except ImportError:
+            pass
 
     if rank == 0:
         pk, pk_src = peaks()
@@ -375,6 +391,7 @@ def main():
                          "share_of_step": sum(att_ms) / args.steps / ms_step},
             "attention_tflops_whole_step": clip_attention_flops() / (ms_step * 1e-3) / 1e12,
             "roofline_other_kernels": other,
+            "same_box_reference_attention": same_box,
         }
         if not args.no_cpu_baseline:
             cores = os.cpu_count() or 1

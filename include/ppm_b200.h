@@ -62,6 +62,14 @@ int ppm_corr_build(const void* fmap1, const void* fmap2, int in_dtype, int B, in
 int ppm_corr_lookup(const void* const* levels, int vol_dtype, const float* flow, int B, int H,
                     int W1, int W2, int radius, int n_levels, float* out, void* stream);
 
+/* K2b  the same lookup (radius 4, 4 levels, bf16 volume) sampled from LEVEL 0 ONLY: the 80-element level-0 span
+ * under the level-3 window of a pixel contains the windows of all four levels; the pooled taps are rebuilt in
+ * registers with ppm_corr_build's arithmetic, so the result equals ppm_corr_lookup on a pyramid written by
+ * ppm_corr_build bit for bit while touching ~2.2 instead of ~4.6 128-byte lines per pixel (B200 fetches a
+ * whole line for every random sector).  level0 (B*H*W1, W2) bf16, 32-byte aligned, W2 % 8 == 0. */
+int ppm_corr_lookup_l0(const void* level0, const float* flow, int B, int H, int W1, int W2, float* out,
+                       void* stream);
+
 /* ---------------------------------------------------------------------------------------
  * K3-pre  QAM query/key frame similarity, once per cascade level (SURVEY.md 8a row a6;
  * PPMStereo.compute_qk_similarity, models/core/ppmstereo.py:397-423).

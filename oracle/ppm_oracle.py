@@ -17,8 +17,10 @@ in the un-vendored, un-pinned third-party ``flash_attn`` package
 (reference models/core/ppmstereo.py:38-41, call site :550); its published
 algorithm (softmax(scale * Q K^T) V with bf16 operands, fp32 softmax,
 P rounded to bf16 before P.V, bf16 output) is restated in
-``attention_bf16``; for that one function parity is "unpinned" by reference
-tests and is anchored on the reference's own call site instead.
+``attention_bf16``; no reference test pins that function, so it is anchored on
+the reference's own call site and, on the GPU box (where the CUDA-only library
+can run), checked against the installed flash_attn 2.8.3 by
+``tests/test_ppm_read_gpu.py::test_oracle_attention_vs_installed_flash_attn``.
 
 Every function cites the reference file:line it follows (paths relative to
 /root/reference).  All math is fp32 on CPU unless a bf16 rounding is stated.

@@ -8,7 +8,7 @@ Public surface (mirrors the reference's call sites):
   StagedRunner                  overlapped host<->device staging of independent windows / levels
 There is no CPU or PyTorch fallback: every op fails loudly without libppm_sm100.so + CUDA.
 """
-from .corr import CorrBlock1D, build_pyramid, lookup
+from .corr import CorrBlock1D, build_pyramid, lookup, lookup_l0
 from .memory import PPMMemory, ppm_memory_read, softmax_scale, temporal_pe_table
 from .install import install, forward_update_block
 from .pipeline import StagedRunner
@@ -16,5 +16,5 @@ from . import shard
 from .upsample import convex_upsample
 from .rowband import RowBandMemory, gather_bands, row_bands
 
-__all__ = ["CorrBlock1D", "build_pyramid", "lookup", "PPMMemory", "ppm_memory_read", "softmax_scale",
+__all__ = ["CorrBlock1D", "build_pyramid", "lookup", "lookup_l0", "PPMMemory", "ppm_memory_read", "softmax_scale",
            "temporal_pe_table", "install", "forward_update_block", "StagedRunner", "shard", "convex_upsample", "RowBandMemory", "gather_bands", "row_bands"]

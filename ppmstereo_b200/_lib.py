@@ -22,6 +22,7 @@ SIGNATURES = {
                                POINTER(c_void_p), c_int, c_int, c_void_p]),
     "ppm_corr_lookup": (c_int, [POINTER(c_void_p), c_int, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int,
                                 c_void_p, c_void_p]),
+    "ppm_corr_lookup_l0": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     "ppm_qk_similarity": (c_int, [c_void_p, c_void_p, c_int, c_int64, c_int64, c_int64, c_int, c_int, c_int, c_int,
                                   c_void_p, c_void_p, c_void_p]),
     "ppm_qam_pick": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p,

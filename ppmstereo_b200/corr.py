@@ -77,6 +77,22 @@ def lookup(levels: List[torch.Tensor], flow: torch.Tensor, W2: int, radius: int 
     return out
 
 
+def lookup_l0(level0: torch.Tensor, flow: torch.Tensor, W2: int) -> torch.Tensor:
+    """ppm_corr_lookup_l0: radius-4, 4-level lookup of a bf16 pyramid sampled from its level 0 only (the
+    pooled taps are rebuilt in registers; equal to ``lookup`` on a pyramid written by ``build_pyramid``)."""
+    if not flow.is_cuda or flow.dim() != 4 or flow.shape[1] != 2:
+        raise RuntimeError(f"flow must be a CUDA tensor (B, 2, H, W), got {tuple(flow.shape)}")
+    if level0.dtype != torch.bfloat16 or W2 % 8:
+        raise RuntimeError("lookup_l0 needs a bf16 level 0 and W2 % 8 == 0")
+    flow = flow.float().contiguous()
+    B, _, H, W1 = flow.shape
+    out = torch.empty(B, 36, H, W1, dtype=torch.float32, device=flow.device)
+    lib = _lib.load()
+    _lib.check(lib.ppm_corr_lookup_l0(level0.data_ptr(), flow.data_ptr(), B, H, W1, W2, out.data_ptr(),
+                                      _lib.stream_ptr()), "ppm_corr_lookup_l0")
+    return out
+
+
 class CorrBlock1D:
     """Same surface as the reference class (models/core/corr.py:55)."""
 
@@ -100,7 +116,11 @@ class CorrBlock1D:
         return self._coords
 
     def __call__(self, flow: torch.Tensor) -> torch.Tensor:
-        return lookup(self.corr_pyramid, flow.detach(), self._w2, self.radius, self.num_levels)
+        lv = self.corr_pyramid
+        if (self.num_levels == 4 and self.radius == 4 and lv[0].dtype == torch.bfloat16 and self._w2 % 8 == 0
+                and lv[0].data_ptr() % 32 == 0):
+            return lookup_l0(lv[0], flow.detach(), self._w2)           # K2b: all levels from one level-0 span
+        return lookup(lv, flow.detach(), self._w2, self.radius, self.num_levels)
 
     @staticmethod
     def corr(fmap1: torch.Tensor, fmap2: torch.Tensor) -> torch.Tensor:

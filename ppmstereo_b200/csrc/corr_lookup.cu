@@ -167,6 +167,137 @@ corr_lookup_kernel(const LookupParams p) {
 }
 
 
+// ------------------------------------------------------------------------------------------------
+// K2b: the same lookup for a bf16 pyramid, sampling ALL four levels from one span of level 0.
+// On B200 a random 32-byte read costs a whole 128-byte line of DRAM traffic (scripts/exp/gather_exp.cu), so
+// the four separate windows of the kernel above cost ~4.6 lines per pixel.  The level-3 window of a pixel
+// covers 80 consecutive level-0 elements (160 bytes, ~2.2 lines) that contain the windows of levels 0-2 as
+// well, so this kernel reads that span once and rebuilds the pooled taps in registers with exactly the
+// arithmetic ppm_corr_build uses (bf16(lo/2 + hi/2) per level: HMUL2/HFMA2.BF16).  With f = floor(x),
+// the span starts at level-0 index 8*((f>>3) - 4) and the windows start at fixed offsets plus a few low
+// bits of f:  level 0: 28 + (f&7), level 1: 12 + ((f>>1)&3), level 2: 4 + ((f>>2)&1), level 3: 0.
+// Valid for pyramids whose levels 1-3 ARE the cascaded poolings of level 0 (those built by ppm_corr_build),
+// radius 4, W2 % 8 == 0.
+__device__ __forceinline__ uint32_t lk_avg_bf16x2(uint32_t w0, uint32_t w1) {       // (avg(w0.lo,w0.hi), avg(w1.lo,w1.hi))
+  const uint32_t lo = __byte_perm(w0, w1, 0x5410), hi = __byte_perm(w0, w1, 0x7632);
+  const uint32_t half2 = 0x3F003F00u;
+  uint32_t hb, d;
+  asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(hb) : "r"(hi), "r"(half2));
+  asm("fma.rn.bf16x2 %0, %1, %2, %3;" : "=r"(d) : "r"(lo), "r"(half2), "r"(hb));
+  return d;
+}
+// ten taps starting `odd` elements into words u[0..5]
+__device__ __forceinline__ void lk_taps(const uint32_t (&u)[6], int odd, float (&v)[kMaxTaps + 1]) {
+  const int sh = odd * 16;
+  #pragma unroll
+  for (int i = 0; i < 5; ++i) {
+    const uint32_t x = __funnelshift_r(u[i], u[i + 1], sh);
+    v[2 * i] = __uint_as_float(x << 16);
+    v[2 * i + 1] = __uint_as_float(x & 0xFFFF0000u);
+  }
+}
+
+struct LookupL0Params {
+  const __nv_bfloat16* level0;
+  long long total;                   // elements in level 0
+  const float* flow;
+  float* out;
+  int HW, W1, W2;
+};
+
+__global__ void __launch_bounds__(kLookupThreads)
+corr_lookup_l0_kernel(const LookupL0Params p) {
+  const int b = blockIdx.y;
+  const int q = blockIdx.x * kLookupThreads + threadIdx.x;
+  if (q >= p.HW) return;
+  const float x = __fadd_rn(static_cast<float>(q % p.W1), __ldg(p.flow + static_cast<long long>(b) * 2 * p.HW + q));
+  float fl = fminf(fmaxf(floorf(x), -1048576.f), 1048576.f);
+  fl = (fl == fl) ? fl : 0.f;
+  const int f = static_cast<int>(fl);
+  const int s0 = 8 * ((f >> 3) - 4);                      // in-row level-0 index of span element 0
+  float* dst = p.out + static_cast<long long>(b) * 36 * p.HW + q;
+  if (s0 >= p.W2 || s0 + 80 <= 0) {                      // every tap of every level is outside the row
+    #pragma unroll
+    for (int c = 0; c < 36; ++c) dst[static_cast<long long>(c) * p.HW] = 0.f;
+    return;
+  }
+  const long long g0 = (static_cast<long long>(b) * p.HW + q) * p.W2 + s0;      // multiple of 8
+  const long long gs = g0 & ~15LL;
+  uint32_t w0[40];                                        // the 80-element span, two bf16 per word
+  if (gs >= 0 && gs + 96 <= p.total) {
+    uint32_t w[48];
+    #pragma unroll
+    for (int i = 0; i < 6; ++i) {
+      const LkSector sct = lk_ldg256(p.level0 + gs + 16 * i);
+      #pragma unroll
+      for (int j = 0; j < 8; ++j) w[8 * i + j] = sct.w[j];
+    }
+    const bool hi = g0 != gs;                            // span starts 8 elements into the first sector
+    #pragma unroll
+    for (int i = 0; i < 40; ++i) w0[i] = hi ? w[i + 4] : w[i];
+  } else {                                                // first / last rows of the whole volume
+    const uint16_t* h16 = reinterpret_cast<const uint16_t*>(p.level0);
+    #pragma unroll
+    for (int i = 0; i < 40; ++i) {
+      const long long e = g0 + 2 * i;
+      const uint32_t lo = (e >= 0 && e < p.total) ? __ldg(h16 + e) : 0u;
+      const uint32_t hi = (e + 1 >= 0 && e + 1 < p.total) ? __ldg(h16 + e + 1) : 0u;
+      w0[i] = lo | (hi << 16);
+    }
+  }
+  uint32_t w1[20], w2[10], w3[5];
+  #pragma unroll
+  for (int i = 0; i < 20; ++i) w1[i] = lk_avg_bf16x2(w0[2 * i], w0[2 * i + 1]);
+  #pragma unroll
+  for (int i = 0; i < 10; ++i) w2[i] = lk_avg_bf16x2(w1[2 * i], w1[2 * i + 1]);
+  #pragma unroll
+  for (int i = 0; i < 5; ++i) w3[i] = lk_avg_bf16x2(w2[2 * i], w2[2 * i + 1]);
+
+  float v[kMaxLevels][kMaxTaps + 1];
+  {                                                       // level 0: element offset 28 + (f & 7)
+    const int r = f & 7;
+    uint32_t t[8], u[6];
+    #pragma unroll
+    for (int i = 0; i < 8; ++i) t[i] = (r & 4) ? w0[16 + i] : w0[14 + i];
+    #pragma unroll
+    for (int i = 0; i < 6; ++i) u[i] = (r & 2) ? t[i + 1] : t[i];
+    lk_taps(u, r & 1, v[0]);
+  }
+  {                                                       // level 1: element offset 12 + ((f >> 1) & 3)
+    const int r = (f >> 1) & 3;
+    uint32_t u[6];
+    #pragma unroll
+    for (int i = 0; i < 6; ++i) u[i] = (r & 2) ? w1[7 + i] : w1[6 + i];
+    lk_taps(u, r & 1, v[1]);
+  }
+  {                                                       // level 2: element offset 4 + ((f >> 2) & 1)
+    uint32_t u[6];
+    #pragma unroll
+    for (int i = 0; i < 6; ++i) u[i] = w2[2 + i];
+    lk_taps(u, (f >> 2) & 1, v[2]);
+  }
+  {                                                       // level 3: element offset 0
+    const uint32_t u[6] = {w3[0], w3[1], w3[2], w3[3], w3[4], 0u};
+    lk_taps(u, 0, v[3]);
+  }
+  #pragma unroll
+  for (int l = 0; l < kMaxLevels; ++l) {
+    const int Wl = p.W2 >> l;
+    const int first = (f >> l) - 4;
+    if (first < 0 || first + 9 >= Wl) {
+      #pragma unroll
+      for (int i = 0; i < kMaxTaps + 1; ++i)
+        if (static_cast<unsigned>(first + i) >= static_cast<unsigned>(Wl)) v[l][i] = 0.f;
+    }
+    const float xl = x * (1.f / static_cast<float>(1 << l));
+    const float w1f = __fsub_rn(xl, floorf(xl)), w0f = __fsub_rn(1.f, w1f);
+    float* d = dst + static_cast<long long>(l) * 9 * p.HW;
+    #pragma unroll
+    for (int k = 0; k < kMaxTaps; ++k)
+      d[static_cast<long long>(k) * p.HW] = __fmaf_rn(v[l][k + 1], w1f, __fmul_rn(v[l][k], w0f));
+  }
+}
+
 }  // namespace ppm
 
 extern "C" int ppm_corr_lookup(const void* const* levels, int vol_dtype, const float* flow, int B,
@@ -197,6 +328,25 @@ extern "C" int ppm_corr_lookup(const void* const* levels, int vol_dtype, const f
     corr_lookup_kernel<__nv_bfloat16><<<grid, kLookupThreads, 0, st>>>(p);
   else
     corr_lookup_kernel<float><<<grid, kLookupThreads, 0, st>>>(p);
+  PPM_CUDA(cudaGetLastError());
+  return PPM_OK;
+}
+
+extern "C" int ppm_corr_lookup_l0(const void* level0, const float* flow, int B, int H, int W1, int W2, float* out,
+                                  void* stream) {
+  using namespace ppm;
+  PPM_CHECK(level0 && flow && out, PPM_ERR_ARG, "ppm_corr_lookup_l0: null pointer");
+  PPM_CHECK(B > 0 && H > 0 && W1 > 0 && W2 > 0, PPM_ERR_ARG, "ppm_corr_lookup_l0: bad shape");
+  PPM_CHECK(W2 % 8 == 0 && (W2 >> 3) >= 1, PPM_ERR_UNSUPPORTED, "ppm_corr_lookup_l0: W2 = %d must be a multiple of 8", W2);
+  PPM_CHECK((reinterpret_cast<uintptr_t>(level0) & 31) == 0, PPM_ERR_ARG, "ppm_corr_lookup_l0: level 0 must be 32-byte aligned");
+  PPM_CHECK(B <= 65535, PPM_ERR_UNSUPPORTED, "ppm_corr_lookup_l0: B %d > 65535", B);
+  LookupL0Params p{};
+  p.level0 = static_cast<const __nv_bfloat16*>(level0);
+  p.HW = H * W1; p.W1 = W1; p.W2 = W2;
+  p.total = static_cast<long long>(B) * H * W1 * W2;
+  p.flow = flow; p.out = out;
+  dim3 grid((p.HW + kLookupThreads - 1) / kLookupThreads, B);
+  corr_lookup_l0_kernel<<<grid, kLookupThreads, 0, static_cast<cudaStream_t>(stream)>>>(p);
   PPM_CUDA(cudaGetLastError());
   return PPM_OK;
 }

@@ -41,6 +41,9 @@ best, med = timeit(lambda: P.CorrBlock1D(f1, f2))
 print(f"K1 build  B={B} D={D} H={H} W={W}: best {best*1e3:.1f} us median {med*1e3:.1f} us -> "
       f"{k1_bytes/med/1e6:.0f} GB/s algorithmic ({k1_bytes/med/1e6/peak:.2f} of {peak:.0f})")
 k2_bytes = B * H * W * 228.0
+best, med = timeit(lambda: P.lookup(blk.corr_pyramid, flow, W2=W), reps=20)
+print(f"K2  per-level lookup {B*H*W} px: best {best*1e3:.1f} us median {med*1e3:.1f} us -> "
+      f"{k2_bytes/med/1e6:.0f} GB/s algorithmic ({k2_bytes/med/1e6/peak:.2f} of {peak:.0f})")
 best, med = timeit(lambda: blk(flow), reps=20)
-print(f"K2 lookup {B*H*W} px: best {best*1e3:.1f} us median {med*1e3:.1f} us -> "
+print(f"K2b lookup from level 0 {B*H*W} px: best {best*1e3:.1f} us median {med*1e3:.1f} us -> "
       f"{k2_bytes/med/1e6:.0f} GB/s algorithmic ({k2_bytes/med/1e6/peak:.2f} of {peak:.0f})")

@@ -155,3 +155,25 @@ def test_errors(P):
         P.CorrBlock1D(f, f)                                                 # reference: W/16 >= 1
     with pytest.raises(RuntimeError, match="dtype"):
         P.CorrBlock1D(f.half(), f.half())
+
+
+@pytest.mark.parametrize("shape", [(2, 128, 3, 64, 64), (1, 256, 2, 40, 88), (3, 256, 5, 320, 320), (1, 128, 1, 8, 16), (1, 128, 2, 24, 40)])
+def test_lookup_from_level0_equals_generic_lookup(P, shape):
+    """K2b (all four levels rebuilt from one level-0 span) must equal the per-level lookup bit for bit on a
+    pyramid written by the build kernel -- including taps left / right of the row, the first and last rows of
+    the volume (guarded loads) and far out-of-range flows."""
+    B, D, H, W1, W2 = shape
+    g = torch.Generator().manual_seed(W1 * 7 + W2)
+    f1 = torch.randn(B, D, H, W1, generator=g).bfloat16().cuda()
+    f2 = torch.randn(B, D, H, W2, generator=g).bfloat16().cuda()
+    lv = P.build_pyramid(f1, f2, 4)
+    for lo, hi in ((-W2 - 24.0, 24.0), (-3.0, 3.0), (-1e6, 1e6)):
+        flow = torch.zeros(B, 2, H, W1)
+        flow[:, 0] = torch.rand(B, H, W1, generator=g) * (hi - lo) + lo
+        flow[0, 0, 0, 0] = -5.5                                  # first pixel of the volume, taps left of it
+        flow[-1, 0, -1, -1] = 6.25 + (W2 - W1)                   # last pixel, taps right of the row end
+        want = P.lookup(lv, flow.cuda(), W2=W2)
+        got = P.lookup_l0(lv[0], flow.cuda(), W2=W2)
+        assert torch.equal(got, want), (shape, lo, hi, float((got - want).abs().max()))
+    blk = P.CorrBlock1D(f1, f2)
+    assert torch.equal(blk(flow.cuda()), P.lookup(blk.corr_pyramid, flow.cuda(), W2=W2))

@@ -245,3 +245,61 @@ def test_similarity_vs_oracle_adaptive_windows(P, shape, dtype):
     assert float((got - want).abs().max()) <= 1e-5
     again = P.PPMMemory(q.cuda(), k.cuda(), None).similarity().cpu()
     assert torch.equal(got, again)                        # deterministic: it feeds the top-k pick
+
+
+@pytest.mark.parametrize("shape,peaky", [((1, 8, 24, 40), False), ((1, 20, 46, 80), False), ((2, 7, 13, 23), True)])
+def test_aggregation_vs_installed_flash_attn(P, shape, peaky):
+    """The reference's attention IS flash_attn.flash_attn_func (models/core/ppmstereo.py:550).  The image carries
+    flash_attn 2.8.3 with sm_100 code, so on the GPU box the real library is the checker: same bf16 q / K' / V
+    (the (b, K*hw, 1, c) layout of :547-548), same scale, compare `hidden`.  Skipped where flash_attn is absent."""
+    fa = pytest.importorskip("flash_attn")
+    b, T, h, w = shape
+    hw, c, K = h * w, 128, 5
+    t = make_case(b, T, h, w, seed=77 + T, peaky=peaky)
+    mem, out, mask, strive = run_read(P, t, beta=1.0)
+    scale = P.softmax_scale(c)
+    mf = t["motion_features"].permute(0, 2, 1, 3, 4).reshape(b, T, c, hw)
+    mine = out.reshape(b, T, c, hw) - mf                                   # beta = 1 -> hidden (fp32 of bf16 + fp32 add)
+    q_p = mem.q_packed.reshape(b, T, hw, c)
+    k_p = mem.k_packed.reshape(b, T, K, hw, c)
+    hw_pad = (hw + 7) // 8 * 8
+    v_p = mem.v_packed.reshape(b, T, c, hw_pad)[..., :hw]
+    picked = mem.picked.long()
+    worst, hmax, tot, n = 0.0, 0.0, 0.0, 0
+    for bb in range(b):
+        for i in range(T):
+            q = q_p[bb, i].reshape(1, hw, 1, c)
+            k = k_p[bb, i].reshape(1, K * hw, 1, c)
+            v = v_p[bb, picked[bb, i]].permute(0, 2, 1).reshape(1, K * hw, 1, c).contiguous()
+            ref = fa.flash_attn_func(q, k, v, 0.0, softmax_scale=scale, causal=False)   # (1, hw, 1, c) bf16
+            ref = ref.float().reshape(hw, c).t().cpu()
+            d = (mine[bb, i] - ref).abs()
+            worst, hmax = max(worst, float(d.max())), max(hmax, float(ref.abs().max()))
+            tot, n = tot + float(d.sum()), n + d.numel()
+    # both sides round P and the output to bf16 (2^-9 relative each); the residual add is fp32
+    assert worst <= 2e-2 * hmax + 1e-6, (worst, hmax)
+    assert tot / n <= 2e-3 * hmax, (tot / n, hmax)
+
+
+def test_oracle_attention_vs_installed_flash_attn():
+    """Pins the oracle's restatement of flash_attn (oracle.attention_bf16) against the real library where it can
+    run: the GPU box.  Same bf16 operands, soft and peaky score distributions."""
+    fa = pytest.importorskip("flash_attn")
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    g = torch.Generator().manual_seed(5)
+    for peaky in (False, True):
+        q = torch.randn(300, 128, generator=g)
+        k = torch.cat([q, q, q, q, q])[torch.randperm(1500, generator=g)] + 0.1 * torch.randn(1500, 128, generator=g) \
+            if peaky else torch.randn(1500, 128, generator=g)
+        v = torch.randn(1500, 128, generator=g)
+        scale = O.ppm_softmax_scale(128) * (4.0 if peaky else 1.0)
+        want = O.attention_bf16(q, k, v, scale)
+        got = fa.flash_attn_func(q.bfloat16().cuda()[None, :, None], k.bfloat16().cuda()[None, :, None],
+                                 v.bfloat16().cuda()[None, :, None], 0.0, softmax_scale=scale, causal=False)
+        got = got.float().cpu().reshape(300, 128)
+        d = (got - want).abs()
+        assert float(d.max()) <= 2.0 ** -7 * float(want.abs().max()), (peaky, float(d.max()))
+        # P is rounded to bf16 against a different running maximum on each side, so about half of the outputs of a
+        # diffuse softmax land on the neighbouring bf16 value: bound the mean at a quarter ulp of the largest output
+        assert float(d.mean()) <= 2.0 ** -10 * float(want.abs().max()), (peaky, float(d.mean()))
