@@ -386,7 +386,7 @@ def main():
             "clocks": clocks,
             "roofline": {"kernel": "ppm_attend3_kernel (1/4-res level, T=20, hw=58880, K=5)", "bound": "tensor",
                          "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
-                         "peak_source": "bf16_tflops_sustained, " + pk_src, "traffic": 8.7e9,
+                         "peak_source": "bf16_tflops_sustained, " + pk_src, "traffic": 1.033e10,
                          "flops_per_launch": fl, "avg_launch_ms": avg, "launches_timed": len(att_ms),
                          "share_of_step": sum(att_ms) / args.steps / ms_step},
             "attention_tflops_whole_step": clip_attention_flops() / (ms_step * 1e-3) / 1e12,
