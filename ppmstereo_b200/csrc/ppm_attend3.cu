@@ -202,6 +202,23 @@ ppm_attend3_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
           asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "r"(lo), "r"(desc_hi));
           return d;
         };
+        // Non-blocking barrier probe whose answer stays in a predicate register until `probed` reads it.
+        asm volatile(".reg .pred ppm_pr0, ppm_pr1, ppm_pr2, ppm_pr3;");
+        auto probe = [&](uint64_t* b, uint32_t parity, int reg) {
+          const uint32_t a = smem_u32(b);
+          if (reg == 0) asm volatile("mbarrier.test_wait.parity.shared::cta.b64 ppm_pr0, [%0], %1;" ::"r"(a), "r"(parity) : "memory");
+          else if (reg == 1) asm volatile("mbarrier.test_wait.parity.shared::cta.b64 ppm_pr1, [%0], %1;" ::"r"(a), "r"(parity) : "memory");
+          else if (reg == 2) asm volatile("mbarrier.test_wait.parity.shared::cta.b64 ppm_pr2, [%0], %1;" ::"r"(a), "r"(parity) : "memory");
+          else asm volatile("mbarrier.test_wait.parity.shared::cta.b64 ppm_pr3, [%0], %1;" ::"r"(a), "r"(parity) : "memory");
+        };
+        auto probed = [&](int reg) -> bool {
+          uint32_t ok;
+          if (reg == 0) asm volatile("selp.b32 %0, 1, 0, ppm_pr0;" : "=r"(ok)::"memory");
+          else if (reg == 1) asm volatile("selp.b32 %0, 1, 0, ppm_pr1;" : "=r"(ok)::"memory");
+          else if (reg == 2) asm volatile("selp.b32 %0, 1, 0, ppm_pr2;" : "=r"(ok)::"memory");
+          else asm volatile("selp.b32 %0, 1, 0, ppm_pr3;" : "=r"(ok)::"memory");
+          return ok != 0;
+        };
         auto issue_qk = [&](int x, int ks) {               // S_x = Q_x K'^T, K' in ring slot ks
           const uint32_t ql = q_lo + x * kTileLo, kl = r_lo + ks * kTileLo;
           if (leader) {
@@ -214,10 +231,17 @@ ppm_attend3_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
         };
         auto issue_pv = [&](int x, int vs, int j) {        // O_x += P_x V, chunk by chunk as P arrives
           const uint32_t vl = r_lo + vs * kTileLo;
+          // The answer of an mbarrier probe takes ~100 cycles to come back even when the phase has long
+          // completed, and tcgen05.mma issue runs only a couple of instructions ahead of execution: a
+          // wait per chunk in front of its MMAs left the tensor pipe idle for that long, eight times per
+          // key tile.  So chunk c+1's barrier is probed (non-blocking) BEFORE chunk c's MMAs are issued;
+          // the blocking wait is only the fallback (scripts/exp/mma_rate.cu: 2864 -> 2312 clk per tile).
+          probe(&bar_pf[x][0], j & 1, 0);
           #pragma unroll
           for (int c = 0; c < 4; ++c) {
-            mbar_wait(&bar_pf[x][c], j & 1);
+            if (!probed(c & 1)) mbar_wait(&bar_pf[x][c], j & 1);
             tc_fence_after();
+            if (c < 3) probe(&bar_pf[x][c + 1], j & 1, (c + 1) & 1);
             if (leader) {
               #pragma unroll
               for (int kk = 0; kk < 2; ++kk) {
@@ -244,16 +268,18 @@ ppm_attend3_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
         if (leader) umma_commit(&bar_empty[0]);
         __syncwarp();
         advance();
+        probe(&bar_full[slot], ph, 2);                     // V(0)
         for (int j = 0; j < n_tiles; ++j) {
           const bool more = j + 1 < n_tiles;
-          const int vs = slot;                             // V(j)
-          mbar_wait(&bar_full[vs], ph);
+          const int vs = slot;                             // V(j), probed during the previous step
+          if (!probed(2)) mbar_wait(&bar_full[vs], ph);
           advance();
           const int ks = slot;                             // K'(j+1)
           const uint32_t kph = ph;
+          if (more) probe(&bar_full[ks], kph, 3);
           issue_pv(0, vs, j);
           if (more) {
-            mbar_wait(&bar_full[ks], kph);
+            if (!probed(3)) mbar_wait(&bar_full[ks], kph);
             tc_fence_after();
             issue_qk(0, ks);
           }
@@ -261,10 +287,11 @@ ppm_attend3_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
           if (leader) umma_commit(&bar_empty[vs]);
           __syncwarp();
           if (more) {
+            advance();
+            probe(&bar_full[slot], ph, 2);                 // V(j+1)
             issue_qk(1, ks);
             if (leader) umma_commit(&bar_empty[ks]);
             __syncwarp();
-            advance();
           }
         }
       }
