@@ -2,7 +2,7 @@
 # ncu evidence for bench.py (run under gpurun).  Plain run first, then the launch list, then one
 # --set full capture per hot kernel.  Numbers printed under ncu are never bench values.
 mkdir -p gpurun_out
-CMD="python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e"
+CMD="python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e --no-same-box"
 $CMD > gpurun_out/prof_plain.json 2> gpurun_out/prof_plain.err || { echo "plain run failed"; tail gpurun_out/prof_plain.err; exit 1; }
 tail -c 400 gpurun_out/prof_plain.json; echo
 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_list.log 2>&1

@@ -1,7 +1,7 @@
 #!/bin/bash
 # ncu evidence for the memory-read kernel only (run under gpurun): plain run, launch list, one --set full capture.
 mkdir -p gpurun_out
-CMD="python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e"
+CMD="python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e --no-same-box"
 $CMD > gpurun_out/prof_plain.json 2> gpurun_out/prof_plain.err || { echo "plain run failed"; tail gpurun_out/prof_plain.err; exit 1; }
 tail -c 600 gpurun_out/prof_plain.json; echo
 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_list.log 2>&1
