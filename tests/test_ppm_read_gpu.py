@@ -303,3 +303,44 @@ def test_oracle_attention_vs_installed_flash_attn():
         # P is rounded to bf16 against a different running maximum on each side, so about half of the outputs of a
         # diffuse softmax land on the neighbouring bf16 value: bound the mean at a quarter ulp of the largest output
         assert float(d.mean()) <= 2.0 ** -10 * float(want.abs().max()), (peaky, float(d.mean()))
+
+
+def test_beta_zero_returns_motion_features_exactly(P):
+    """beta is initialised to 0 in the reference (ppmtereo_update.py:647): the read must then be the identity
+    on motion_features, bit for bit (mf + 0 * hidden)."""
+    t = make_case(1, 6, 12, 20, seed=31)
+    mem, out, mask, strive = run_read(P, t, beta=0.0)
+    assert torch.equal(out.reshape(1, 6, 128, 12, 20), t["motion_features"].permute(0, 2, 1, 3, 4))
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_frame_major_views_as_the_model_passes_them(P, dtype):
+    """forward_update_block hands over (b*T, c, h, w) tensors viewed as (b, c, T, h, w) (permute, no copy) and,
+    under autocast, bf16 value / motion features: the strided path must equal the contiguous one."""
+    b, T, h, w = 2, 6, 9, 14
+    t = make_case(b, T, h, w, seed=32)
+    cont = {k: t[k].to(dtype).cuda() for k in ("query", "key", "value", "motion_features")}
+    view = {k: v.permute(0, 2, 1, 3, 4).reshape(b * T, 128, h, w).clone()
+            .reshape(b, T, 128, h, w).permute(0, 2, 1, 3, 4) for k, v in cont.items()}
+    assert not view["query"].is_contiguous()
+    outs = []
+    for src in (cont, view):
+        mem = P.PPMMemory(src["query"], src["key"], None, top_k=5)
+        strive = t["strive_before"].clone().cuda()
+        out, _ = mem.read(src["value"], src["motion_features"], t["sim"].cuda(), strive,
+                          t["uncertainty"].to(dtype).cuda(), torch.tensor([0.5], device="cuda"))
+        outs.append(out)
+    assert torch.equal(outs[0], outs[1])
+    if dtype == torch.float32:
+        want = O.ppm_memory_read(t["query"], t["key"], O.temporal_pe(T, 128), t["value"], t["motion_features"],
+                                 t["sim"], t["strive_before"], t["uncertainty"], 0.5)
+        d = (outs[0].cpu() - want["motion_features_global"]).abs()
+        assert float(d.max()) <= 3e-2 * float(want["hidden"].abs().max())
+
+
+@pytest.mark.parametrize("shape", [(1, 6, 1, 1), (1, 6, 2, 3), (2, 7, 5, 5), (1, 2, 3, 43)])
+def test_tiny_and_odd_pixel_counts(P, shape):
+    """hw below one tile, below one 32-key chunk, not a multiple of 8 (the packed V pitch) and hw = 129 (one
+    key past a tile): every masking path of the aggregation."""
+    b, T, h, w = shape
+    check_vs_oracle(P, make_case(b, T, h, w, seed=40 + h * w))
