@@ -6,6 +6,8 @@ Public surface (mirrors the reference's call sites):
   install(ppmstereo_module)     rewires a loaded reference model onto the two above
   convex_upsample               PPMStereo.convex_upsample (models/core/ppmstereo.py:185-197) as one kernel
   StagedRunner                  overlapped host<->device staging of independent windows / levels
+  forward_batch_test            PPMStereo.forward_batch_test (models/core/ppmstereo.py:238-320): same windows and
+                                stitching, per-frame encoder cache, staged copies (window.py)
 There is no CPU or PyTorch fallback: every op fails loudly without libppm_sm100.so + CUDA.
 """
 from .corr import CorrBlock1D, build_pyramid, lookup, lookup_l0
@@ -15,6 +17,9 @@ from .pipeline import StagedRunner
 from . import shard
 from .upsample import convex_upsample
 from .rowband import RowBandMemory, gather_bands, row_bands
+from .window import FrameFeatureCache, forward_batch_test
+from . import window
 
 __all__ = ["CorrBlock1D", "build_pyramid", "lookup", "lookup_l0", "PPMMemory", "ppm_memory_read", "softmax_scale",
-           "temporal_pe_table", "install", "forward_update_block", "StagedRunner", "shard", "convex_upsample", "RowBandMemory", "gather_bands", "row_bands"]
+           "temporal_pe_table", "install", "forward_update_block", "StagedRunner", "shard", "convex_upsample", "RowBandMemory", "gather_bands", "row_bands",
+           "FrameFeatureCache", "forward_batch_test", "window"]

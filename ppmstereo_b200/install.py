@@ -4,7 +4,9 @@
   * rebinds the name ``CorrBlock1D`` used at models/core/ppmstereo.py:707, :743, :776, and
   * replaces ``PPMStereo.forward_update_block`` (models/core/ppmstereo.py:426-594) by the
     function below: same arguments, same return value, same side effects on ``predictions`` /
-    ``uncertainties``; the block :501-555 becomes one PPMMemory.read call.
+    ``uncertainties``; the block :501-555 becomes one PPMMemory.read call, and
+  * replaces ``PPMStereo.forward_batch_test`` (:238-320) by ``window.forward_batch_test``: same windows,
+    stitching and return value, each frame encoded once per clip, copies overlapped with the kernels.
 ``PPMStereoModel.forward`` / ``PPMStereo.forward`` and all state-dict keys are unchanged.
 """
 from __future__ import annotations
@@ -15,6 +17,7 @@ import torch.nn.functional as F
 from .corr import CorrBlock1D
 from .memory import C, PPMMemory, softmax_scale
 from .upsample import convex_upsample
+from .window import forward_batch_test
 
 
 def forward_update_block(self, image1, update_block, corr_fn, flow, net, inp, motion_hidden_state,
@@ -63,4 +66,5 @@ def install(ppmstereo_module):
     """Patch the reference module in place; returns it."""
     ppmstereo_module.CorrBlock1D = CorrBlock1D
     ppmstereo_module.PPMStereo.forward_update_block = forward_update_block
+    ppmstereo_module.PPMStereo.forward_batch_test = forward_batch_test      # window scheduler (ppmstereo.py:238-320)
     return ppmstereo_module

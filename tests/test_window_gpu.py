@@ -1,0 +1,64 @@
+"""Window scheduler on the GPU: staged uploads / downloads and the encoder cache must not change the result.
+The reference model cannot travel to the GPU box, so a small stand-in with the same surface (fnet([l, r]),
+cnet(l), mixed_precision, forward(left, right, iters, test_mode) -> (disp, unc) of shape (1, T, 1, H, W)) is
+driven through ``forward_batch_test`` on CUDA and compared with the same code path run synchronously on CPU."""
+import pytest
+import torch
+import torch.nn as nn
+
+pytestmark = pytest.mark.gpu
+
+
+class TinyStereo(nn.Module):
+    def __init__(self):
+        super().__init__()
+        torch.manual_seed(0)
+        self.fnet_conv = nn.Conv2d(3, 8, 3, padding=1)
+        self.cnet_conv = nn.Conv2d(3, 4, 3, padding=1)
+        self.mixed_precision = False
+        self.calls = {"fnet": 0, "cnet": 0}
+        outer = self
+
+        class F(nn.Module):
+            def forward(self, x):
+                outer.calls["fnet"] += x[0].shape[0]
+                return tuple(outer.fnet_conv(t) for t in x)
+
+        class Cn(nn.Module):
+            def forward(self, x):
+                outer.calls["cnet"] += x.shape[0]
+                y = outer.cnet_conv(x)
+                return y, y[..., ::2, ::2], y[..., ::4, ::4]
+
+        self.fnet, self.cnet = F(), Cn()
+
+    def forward(self, left, right, iters=2, test_mode=True):
+        b, T, c, h, w = left.shape
+        f1, f2 = self.fnet([left.reshape(b * T, c, h, w) / 255.0, right.reshape(b * T, c, h, w) / 255.0])
+        ctx, _, _ = self.cnet(left.reshape(b * T, c, h, w) / 255.0)
+        d = (f1 * f2).sum(1, keepdim=True) + ctx.mean(1, keepdim=True)
+        d = d + 0.1 * iters * d.mean(dim=0, keepdim=True)                # couples the frames of a window
+        return d.reshape(b, T, 1, h, w), torch.sigmoid(d).reshape(b, T, 1, h, w)
+
+
+@pytest.mark.parametrize("T,ks,hw", [(40, 20, (48, 80)), (13, 6, (33, 70)), (5, 20, (32, 64))])
+def test_staged_cached_windows_equal_the_synchronous_path(T, ks, hw):
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from ppmstereo_b200 import window
+    video = torch.rand(T, 2, 3, *hw, generator=torch.Generator().manual_seed(T)) * 255.0
+    cpu_model, gpu_model = TinyStereo(), TinyStereo().cuda()
+    tf32 = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False                             # compare fp32 with fp32
+    try:
+        with torch.no_grad():
+            want = window.forward_batch_test(cpu_model, {"stereo_video": video}, kernel_size=ks, iters=4, device="cpu")
+            got = window.forward_batch_test(gpu_model, {"stereo_video": video.pin_memory()}, kernel_size=ks, iters=4)
+    finally:
+        torch.backends.cudnn.allow_tf32 = tf32
+    assert gpu_model.calls == {"fnet": T, "cnet": T}                     # every frame encoded exactly once
+    assert not isinstance(gpu_model.fnet, window.FrameFeatureCache)
+    for k in ("disparity", "uncertainties"):
+        assert got[k].shape == want[k].shape == (T, 1, *hw)
+        assert not got[k].is_cuda
+        assert float((got[k] - want[k]).abs().max()) <= 1e-4 * float(want[k].abs().max())
