@@ -59,8 +59,17 @@ struct CorrBuildParams {
   int stage_bufs;                    // staging buffers (1 or 2)
 };
 
-struct CbStoreMaps { CUtensorMap m[3]; };
+// Store maps of levels 0..2: [l][0] = box of two 32-column chunks (128 >> l bytes wide), [l][1] = box of
+// one chunk (64 >> l bytes; the tail when a tile has an odd number of chunks).  The boxes are swizzled
+// (128B / 64B / 32B / none) so that the epilogue's row-per-thread 16-byte writes spread over all banks.
+struct CbStoreMaps { CUtensorMap m[3][2]; };
 constexpr int kCbTmaLevels = 3;
+// Byte offset of 16-byte piece `u` of row `row` inside a staged [128][bp] box (bp = 128, 64, 32 or 16), following
+// the TMA swizzle of that width: the piece index is XORed with the address bits [7, 7 + log2(bp/16)).
+__device__ __forceinline__ int cb_stage_off(int row, int u, int bp) {
+  const int sw = ((row * bp) >> 7) & ((bp >> 4) - 1);
+  return row * bp + ((u ^ sw) << 4);
+}
 
 template <typename ElemT> struct CbTraits;
 template <> struct CbTraits<__nv_bfloat16> {
@@ -336,7 +345,7 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
       const long long row = static_cast<long long>(bh) * p.W1 + m;
       const bool row_ok = m < p.W1;
       const int buf = static_cast<int>(it & 1);
-      // staging layout of one buffer: L0 [128][NT] | L1 [128][NT/2] | L2 [128][NT/4] bf16, dense rows
+      // staging layout of one buffer: L0 | L1 | L2, each level a run of swizzled [128 rows][2 chunks] boxes (+ a 1-chunk tail box)
       const int sb = p.stage_bufs == 2 ? static_cast<int>(it & 1) : 0;
       uint8_t* stg = stage0 + sb * (kCbM * p.NT * 2 * 7 / 4);
       const bool store_thread = (warp == 2 && lane == 0);
@@ -375,12 +384,16 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
                 }
               }
               if (p.tma_out && l < kCbTmaLevels) {
-                if (l <= p.n_levels) {                   // stage this thread's row segment: n bf16 = n/2 words
-                  const int ntl = p.NT >> l;
+                if (l <= p.n_levels) {                   // stage this thread's row segment: n bf16 = n/8 pieces of 16 B
                   const int off_l = l == 0 ? 0 : (l == 1 ? kCbM * p.NT * 2 : kCbM * p.NT * 3);
-                  uint4* d4 = reinterpret_cast<uint4*>(stg + off_l + ((q * 32 + lane) * ntl + ((cc * 32) >> l)) * 2);
+                  const bool tail = (n_chunks & 1) && cc == n_chunks - 1;
+                  const int bp = (tail ? 64 : 128) >> l;                      // bytes per box row
+                  const int u0 = tail ? 0 : (cc & 1) * (n / 8);
+                  uint8_t* box = stg + off_l + (cc >> 1) * ((kCbM * 128) >> l);
                   #pragma unroll
-                  for (int j = 0; j < n / 8; ++j) d4[j] = make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
+                  for (int j = 0; j < n / 8; ++j)
+                    *reinterpret_cast<uint4*>(box + cb_stage_off(q * 32 + lane, u0 + j, bp)) =
+                        make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
                 }
               } else if (l <= p.n_levels && row_ok) {
                 const int Wl = p.width[l];
@@ -427,7 +440,12 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
           const int nl = p.n_levels < kCbTmaLevels - 1 ? p.n_levels : kCbTmaLevels - 1;
           for (int l = 0; l <= nl; ++l) {
             const int off_l = l == 0 ? 0 : (l == 1 ? kCbM * p.NT * 2 : kCbM * p.NT * 3);
-            tma_store_3d(&omap.m[l], stg + off_l, n0 >> l, m0, bh);   // rows past W1, columns past W_l are clipped
+            const int n_pair = n_chunks >> 1;
+            // rows past W1 and columns past W_l are clipped by the TMA unit
+            for (int pi = 0; pi < n_pair; ++pi)
+              tma_store_3d(&omap.m[l][0], stg + off_l + pi * ((kCbM * 128) >> l), (n0 >> l) + pi * (64 >> l), m0, bh);
+            if (n_chunks & 1)
+              tma_store_3d(&omap.m[l][1], stg + off_l + n_pair * ((kCbM * 128) >> l), (n0 >> l) + n_pair * (64 >> l), m0, bh);
           }
           bulk_commit();
         }
@@ -505,13 +523,17 @@ static int launch_corr_build(const void* f1, const void* f2, int B, int D, int H
     const int nl = n_levels < kCbTmaLevels - 1 ? n_levels : kCbTmaLevels - 1;
     for (int l = 0; l <= nl; ++l)
       ok = ok && ((static_cast<size_t>(W2 >> l) * 2) % 16 == 0) && (reinterpret_cast<uintptr_t>(levels[l]) % 16 == 0);
+    static const CUtensorMapSwizzle kSw[4] = {CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_SWIZZLE_64B,
+                                              CU_TENSOR_MAP_SWIZZLE_32B, CU_TENSOR_MAP_SWIZZLE_NONE};
     for (int l = 0; l <= nl && ok; ++l) {
       const uint64_t Wl = static_cast<uint64_t>(W2 >> l);
       const uint64_t dims[3] = {Wl, (uint64_t)W1, (uint64_t)B * H};
       const uint64_t str[2] = {Wl * 2, (uint64_t)W1 * Wl * 2};
-      const uint32_t obox[3] = {static_cast<uint32_t>(p.NT >> l), static_cast<uint32_t>(kCbM), 1};
-      ok = make_tensor_map(&om.m[l], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, levels[l], dims, str, obox,
-                           CU_TENSOR_MAP_SWIZZLE_NONE) == PPM_OK;
+      for (int t = 0; t < 2 && ok; ++t) {            // t = 0: two chunks per box, t = 1: one chunk
+        const uint32_t obox[3] = {static_cast<uint32_t>((64 >> t) >> l), static_cast<uint32_t>(kCbM), 1};
+        ok = make_tensor_map(&om.m[l][t], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, levels[l], dims, str, obox,
+                             kSw[l + t]) == PPM_OK;
+      }
     }
     if (ok) {
       p.tma_out = 1;
