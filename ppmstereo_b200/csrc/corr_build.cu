@@ -28,6 +28,8 @@
 // the remaining gap is operand traffic competing with the output stream, not arithmetic.
 // The volume is written exactly once and never re-read: 1.9375 x W1 x W2 elements per row.
 #include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "../../include/ppm_b200.h"
@@ -57,12 +59,20 @@ struct CorrBuildParams {
   int a_stages;                      // res_b: stages of the F1 ring
   int tma_out;                       // levels 0..2 leave through TMA stores from a staged smem tile
   int stage_bufs;                    // staging buffers (1 or 2)
+  int l2_prefetch;                   // resident mode: the producer pulls the next work item's feature rows into L2
+  int pf_channels;                   // channels per prefetch box
+  int row_order;                     // resident mode: a CTA runs the N tiles of one image row back to back
+  int noprobe;                       // experiments: blocking waits only in the MMA issuer
+  int spin;                          // experiments: poll barriers with test_wait instead of try_wait
+  int ablate;                        // experiments only (PPM_CB_ABLATE bit mask): 1 no stores, 2 no TMA-store issue, 4 no loads, 8 no epilogue body, 16 tmem_ld only
+  int pair;                          // resident mode, 2 N tiles: a 2-CTA cluster owns an image row (CTA rank = N tile)
+                                     // and every F1 tile is fetched once and multicast to both CTAs
 };
 
 // Store maps of levels 0..2: [l][0] = box of two 32-column chunks (128 >> l bytes wide), [l][1] = box of
 // one chunk (64 >> l bytes; the tail when a tile has an odd number of chunks).  The boxes are swizzled
 // (128B / 64B / 32B / none) so that the epilogue's row-per-thread 16-byte writes spread over all banks.
-struct CbStoreMaps { CUtensorMap m[3][2]; };
+struct CbStoreMaps { CUtensorMap m[3][2]; CUtensorMap pf[2]; };   // pf: L2 prefetch boxes [pf_channels][64 columns] of F1 / F2
 constexpr int kCbTmaLevels = 3;
 // Byte offset of 16-byte piece `u` of row `row` inside a staged [128][bp] box (bp = 128, 64, 32 or 16), following
 // the TMA swizzle of that width: the piece index is XORed with the address bits [7, 7 + log2(bp/16)).
@@ -115,6 +125,35 @@ __device__ __forceinline__ void tma_store_3d(const CUtensorMap* m, const void* s
   asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
                ::"l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2)
                : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_l2_4d(const CUtensorMap* m, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.async.bulk.prefetch.tensor.4d.L2.global.tile [%0, {%1, %2, %3, %4}];"
+               ::"l"(reinterpret_cast<uint64_t>(m)), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+}
+__device__ __forceinline__ void tma_load_4d_mc(void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2,
+                                               int c3, uint16_t cta_mask) {   // lands at the same offset in every CTA of the mask
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
+      " [%0], [%1, {%3, %4, %5, %6}], [%2], %7;"
+      ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3),
+      "h"(cta_mask)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit_mc(uint64_t* bar, uint16_t cta_mask) {   // arrive on `bar` of every CTA in the mask
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               ::"r"(smem_u32(bar)), "h"(cta_mask) : "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void cb_wait(int spin, uint64_t* bar, uint32_t parity) {
+  if (spin) { while (!mbar_test_wait(bar, parity)) {} }
+  else mbar_wait(bar, parity);
 }
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 template <int kPending>
@@ -229,12 +268,22 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
   uint8_t* stage0 = smem + (p.res_b ? p.a_stages * kABytes + n_k * b_chunk_bytes : kCbStages * kStageBytes);
   // Work order.  Streaming: tile t = blockIdx.x + i*grid -> (bh, mt, nt).  Resident: item = blockIdx.x +
   // (i / n_mtiles)*grid -> (bh, nt), and the item's M tiles follow each other on the same CTA.
-  const long long my_tiles = p.res_b
-      ? ((p.n_items - blockIdx.x + gridDim.x - 1) / gridDim.x) * p.n_mtiles
+  // p.row_order: a CTA takes whole image rows (blockIdx.x + k*grid) and runs the row's N tiles back to back.
+  const long long n_rows_bh = p.n_items / p.n_ntiles;
+  const uint32_t crank = p.pair ? cluster_ctarank() : 0;
+  const long long my_tiles = p.pair ? ((n_rows_bh - (blockIdx.x >> 1) + (gridDim.x >> 1) - 1) / (gridDim.x >> 1)) * p.n_mtiles
+      : p.res_b
+      ? (p.row_order ? ((n_rows_bh - blockIdx.x + gridDim.x - 1) / gridDim.x) * p.n_ntiles
+                     : ((p.n_items - blockIdx.x + gridDim.x - 1) / gridDim.x)) * p.n_mtiles
       : (p.n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x;
+  auto item_of = [&](long long j) -> long long {          // j-th work item of this CTA -> global item (bh * n_ntiles + nt)
+    if (p.pair) return ((blockIdx.x >> 1) + j * (gridDim.x >> 1)) * 2 + crank;
+    if (!p.row_order) return blockIdx.x + j * gridDim.x;
+    return (blockIdx.x + (j / p.n_ntiles) * gridDim.x) * p.n_ntiles + (j % p.n_ntiles);
+  };
   auto decode = [&](long long i, int& bh, int& m0, int& n0, int& mt) {
     if (p.res_b) {
-      const long long item = blockIdx.x + (i / p.n_mtiles) * gridDim.x;
+      const long long item = item_of(i / p.n_mtiles);
       mt = static_cast<int>(i % p.n_mtiles);
       bh = static_cast<int>(item / p.n_ntiles);
       n0 = static_cast<int>(item % p.n_ntiles) * p.NT;
@@ -250,7 +299,7 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kCbMaxRing; ++s) {
-      mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 1); mbar_init(&bar_bfull[s], 1); mbar_init(&bar_bempty[s], 1);
+      mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], p.pair ? 2 : 1); mbar_init(&bar_bfull[s], 1); mbar_init(&bar_bempty[s], 1);
     }
     for (int s = 0; s < 2; ++s) { mbar_init(&bar_acc_full[s], 1); mbar_init(&bar_acc_empty[s], kCbEpiWarps); }
     fence_mbar_init();
@@ -258,6 +307,7 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
   if (warp == 1) tmem_alloc<kCbTmemCols>(&tmem_slot);
   tc_fence_before();
   __syncthreads();
+  if (p.pair) cluster_sync_all();          // the peer's barriers exist before anything is multicast into them
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
 
@@ -273,20 +323,41 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
         decode(i, bh, m0, n0, mt);
         const int b = bh / p.H, h = bh % p.H;
         const uint32_t bph = static_cast<uint32_t>((i / p.n_mtiles) & 1) ^ 1;     // resident: item parity
+        if (p.l2_prefetch && mt == 0) {
+          // Pull the NEXT item's feature rows into L2 while this item computes: the ring (56 KB) then only
+          // has to cover the L2 latency, not the DRAM latency under load.
+          const long long nxt = (i + p.n_mtiles < my_tiles) ? item_of(i / p.n_mtiles + 1) : p.n_items;
+          if (nxt < p.n_items) {
+            const int nbh = static_cast<int>(nxt / p.n_ntiles), nn0 = static_cast<int>(nxt % p.n_ntiles) * p.NT;
+            const int nb = nbh / p.H, nh = nbh % p.H;
+            for (int d0 = 0; d0 < p.D; d0 += p.pf_channels) {
+              for (int c = 0; c < n_bchunks; ++c)
+                if (nn0 + c * Tr::kChunkW < p.W2) tma_prefetch_l2_4d(&omap.pf[1], nn0 + c * Tr::kChunkW, nh, d0, nb);
+              if (p.l2_prefetch > 1)
+                for (int x = 0; x < p.W1; x += Tr::kChunkW) tma_prefetch_l2_4d(&omap.pf[0], x, nh, d0, nb);
+            }
+          }
+        }
         for (int kc = 0; kc < n_k; ++kc) {
           if (p.res_b && mt == 0) {                      // the item's F2 tile, once, chunk by chunk
-            mbar_wait(&bar_bempty[kc], bph);
+            cb_wait(p.spin, &bar_bempty[kc], bph);
+            if ((p.ablate & 4)) mbar_arrive(&bar_bfull[kc]); else
             mbar_expect_tx(&bar_bfull[kc], b_chunk_bytes);
-            for (int c = 0; c < n_bchunks; ++c)
+            for (int c = 0; c < n_bchunks && !(p.ablate & 4); ++c)
               tma_load_4d(b_res + kc * b_chunk_bytes + c * kChunkBytes, &map2, &bar_bfull[kc], n0 + c * Tr::kChunkW, h,
                           kc * Tr::kKC, b);
           }
-          mbar_wait(&bar_empty[s], ph);
+          cb_wait(p.spin, &bar_empty[s], ph);
+          if ((p.ablate & 4)) { mbar_arrive(&bar_full[s]); if (++s == n_ring) { s = 0; ph ^= 1; } continue; }
           mbar_expect_tx(&bar_full[s], p.res_b ? kABytes : kABytes + b_chunk_bytes);
           uint8_t* st = smem + s * (p.res_b ? kABytes : kStageBytes);
           #pragma unroll
-          for (int c = 0; c < kAChunks; ++c)
-            tma_load_4d(st + c * kChunkBytes, &map1, &bar_full[s], m0 + c * Tr::kChunkW, h, kc * Tr::kKC, b);
+          for (int c = 0; c < kAChunks; ++c) {
+            if (!p.pair)
+              tma_load_4d(st + c * kChunkBytes, &map1, &bar_full[s], m0 + c * Tr::kChunkW, h, kc * Tr::kKC, b);
+            else if ((c & 1) == static_cast<int>(crank))          // each CTA fetches half of the tile for both
+              tma_load_4d_mc(st + c * kChunkBytes, &map1, &bar_full[s], m0 + c * Tr::kChunkW, h, kc * Tr::kKC, b, 3);
+          }
           if (!p.res_b)
             for (int c = 0; c < n_bchunks; ++c)
               tma_load_4d(st + kABytes + c * kChunkBytes, &map2, &bar_full[s], n0 + c * Tr::kChunkW, h,
@@ -297,36 +368,74 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer
-    if (elect_one()) {
+    // The whole warp walks the loop (uniform control flow: ring indices and descriptor words stay in
+    // uniform registers, no per-MMA R2UR traffic); one elected lane issues the tcgen05 instructions.  A
+    // descriptor is (hi, lo) with hi constant and lo = base | (smem address >> 4): another K slice, ring
+    // stage or resident chunk is one integer add.  The next stage's barrier is probed (non-blocking) BEFORE
+    // this stage's MMAs are issued: a probe's answer takes ~100 cycles even on a completed phase and MMA
+    // issue runs only a couple of instructions ahead of execution, so a blocking wait in front of every
+    // pair of MMAs left the tensor pipe idle most of the time (measured: the MMA + barrier skeleton alone
+    // took 0.39 ms of the 0.41 ms HBM budget at the 720p 1/4-res shape).
+    {
+      const bool leader = elect_one();
       const uint32_t idesc = umma_idesc(Tr::kFmt, /*a MN-major*/ 1, /*b MN-major*/ 1, kCbM, p.NT);
+      // MN-major: LBO = stride between 128-byte MN chunks, SBO = one swizzle group of channel rows
+      const uint64_t d0 = umma_desc_sw128(0, kChunkBytes, Tr::kSbo, Tr::kLayout);
+      const uint32_t desc_hi = static_cast<uint32_t>(d0 >> 32);
+      // (& 0x3FFF: inside a cluster the shared-window address of rank 1 carries the CTA rank above bit 18)
+      const uint32_t a_lo0 = static_cast<uint32_t>(d0) + ((smem_u32(smem) >> 4) & 0x3FFF);
+      const uint32_t b_lo0 = static_cast<uint32_t>(d0) + (((p.res_b ? smem_u32(b_res) : smem_u32(smem) + kABytes) >> 4) & 0x3FFF);
+      const uint32_t a_step = static_cast<uint32_t>(p.res_b ? kABytes : kStageBytes) >> 4;
+      const uint32_t b_step = p.res_b ? static_cast<uint32_t>(b_chunk_bytes) >> 4 : a_step;
+      constexpr uint32_t kKStep = (Tr::kUK * 128) >> 4;
+      auto mk = [&](uint32_t lo) -> uint64_t {
+        uint64_t d;
+        asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "r"(lo), "r"(desc_hi));
+        return d;
+      };
+      asm volatile(".reg .pred ppm_cb_pr0, ppm_cb_pr1;");
+      auto probe0 = [&](uint64_t* bar, uint32_t parity) {
+        asm volatile("mbarrier.test_wait.parity.shared::cta.b64 ppm_cb_pr0, [%0], %1;" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+      };
+      auto probe1 = [&](uint64_t* bar, uint32_t parity) {
+        asm volatile("mbarrier.test_wait.parity.shared::cta.b64 ppm_cb_pr1, [%0], %1;" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+      };
+      auto probed0 = [&]() -> bool { uint32_t ok; asm volatile("selp.b32 %0, 1, 0, ppm_cb_pr0;" : "=r"(ok)::"memory"); return ok != 0; };
+      auto probed1 = [&]() -> bool { uint32_t ok; asm volatile("selp.b32 %0, 1, 0, ppm_cb_pr1;" : "=r"(ok)::"memory"); return ok != 0; };
       int s = 0;
       uint32_t ph = 0;
+      if (my_tiles > 0) probe0(&bar_full[0], 0);
       for (long long it = 0; it < my_tiles; ++it) {
         const int buf = static_cast<int>(it & 1);
         const int mt = p.res_b ? static_cast<int>(it % p.n_mtiles) : 0;
+        const bool first_m = p.res_b && mt == 0, last_m = p.res_b && mt == p.n_mtiles - 1;
         const uint32_t bph = static_cast<uint32_t>((it / p.n_mtiles) & 1);
-        mbar_wait(&bar_acc_empty[buf], static_cast<uint32_t>((it >> 1) & 1) ^ 1);   // epilogue has drained this accumulator
-        tc_fence_after();
+        if (first_m) probe1(&bar_bfull[0], bph);
+        cb_wait(p.spin, &bar_acc_empty[buf], static_cast<uint32_t>((it >> 1) & 1) ^ 1);   // epilogue has drained this accumulator
         const uint32_t acc = tmem_base + buf * kCbMaxN;
         for (int kc = 0; kc < n_k; ++kc) {
-          mbar_wait(&bar_full[s], ph);
-          if (p.res_b && mt == 0) mbar_wait(&bar_bfull[kc], bph);
+          if (p.noprobe || !probed0()) cb_wait(p.spin, &bar_full[s], ph);
+          if (first_m && (p.noprobe || !probed1())) cb_wait(p.spin, &bar_bfull[kc], bph);
           tc_fence_after();
-          const uint32_t a0 = smem_u32(smem + s * (p.res_b ? kABytes : kStageBytes));
-          const uint32_t b0 = p.res_b ? smem_u32(b_res + kc * b_chunk_bytes) : a0 + kABytes;
-          #pragma unroll
-          for (int k = 0; k < Tr::kKC / Tr::kUK; ++k) {
-            // MN-major: LBO = stride between 128-byte MN chunks, SBO = one swizzle group of channel rows
-            const uint64_t ad = umma_desc_sw128(a0 + k * Tr::kUK * 128, kChunkBytes, Tr::kSbo, Tr::kLayout);
-            const uint64_t bd = umma_desc_sw128(b0 + k * Tr::kUK * 128, kChunkBytes, Tr::kSbo, Tr::kLayout);
-            if constexpr (Tr::kFmt == 2) umma_tf32_ss(acc, ad, bd, idesc, (kc | k) != 0);
-            else                         umma_f16_ss(acc, ad, bd, idesc, (kc | k) != 0);
-          }
-          umma_commit(&bar_empty[s]);
-          if (p.res_b && mt == p.n_mtiles - 1) umma_commit(&bar_bempty[kc]);   // last M tile of the item: chunk is free
+          const uint32_t a_lo = a_lo0 + s * a_step;
+          const uint32_t b_lo = b_lo0 + (p.res_b ? kc : s) * b_step;
+          const int s_cur = s;
           if (++s == n_ring) { s = 0; ph ^= 1; }
+          probe0(&bar_full[s], ph);                                   // next stage (of this or the next tile)
+          if (first_m && kc + 1 < n_k) probe1(&bar_bfull[kc + 1], bph);
+          if (leader) {
+            #pragma unroll
+            for (int k = 0; k < Tr::kKC / Tr::kUK; ++k) {
+              if constexpr (Tr::kFmt == 2) umma_tf32_ss(acc, mk(a_lo + k * kKStep), mk(b_lo + k * kKStep), idesc, (kc | k) != 0);
+              else                         umma_f16_ss(acc, mk(a_lo + k * kKStep), mk(b_lo + k * kKStep), idesc, (kc | k) != 0);
+            }
+            if (p.pair) umma_commit_mc(&bar_empty[s_cur], 3); else umma_commit(&bar_empty[s_cur]);
+            if (last_m) umma_commit(&bar_bempty[kc]);                 // last M tile of the item: chunk is free
+          }
+          __syncwarp();
         }
-        umma_commit(&bar_acc_full[buf]);
+        if (leader) umma_commit(&bar_acc_full[buf]);
+        __syncwarp();
       }
     }
   } else {
@@ -355,13 +464,21 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
         }
         epi_barrier(1);
       }
-      mbar_wait(&bar_acc_full[buf], static_cast<uint32_t>((it >> 1) & 1));
+      cb_wait(p.spin, &bar_acc_full[buf], static_cast<uint32_t>((it >> 1) & 1));
       tc_fence_after();
       const uint32_t acc = tmem_base + buf * kCbMaxN + (static_cast<uint32_t>(q * 32) << 16);
       for (int cc = half; cc < n_chunks; cc += 2) {
+        if (p.ablate & 8) break;
         uint32_t raw[32];
         tmem_ld_x32(acc + cc * 32, raw);
         tmem_ld_wait();
+        if (p.ablate & 16) {
+          uint32_t x = 0;
+          #pragma unroll
+          for (int j = 0; j < 32; ++j) x ^= raw[j];
+          if (x == 0x12345678u) *reinterpret_cast<uint32_t*>(p.level[0]) = x;
+          continue;
+        }
         if constexpr (sizeof(OutT) == 2) {
           if (p.inv_sqrt_d != 0.f) {
             // fast path: bf16 pyramid, exact power-of-two scale, packed bf16x2 arithmetic:
@@ -383,6 +500,7 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
                   w[j] = cb_avg_bf16x2(lo, hi);
                 }
               }
+              if (p.ablate & 1) { if (w[0] == 0x12345678u && l == 4) *reinterpret_cast<uint32_t*>(p.level[0]) = w[0]; continue; }
               if (p.tma_out && l < kCbTmaLevels) {
                 if (l <= p.n_levels) {                   // stage this thread's row segment: n bf16 = n/8 pieces of 16 B
                   const int off_l = l == 0 ? 0 : (l == 1 ? kCbM * p.NT * 2 : kCbM * p.NT * 3);
@@ -436,7 +554,7 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
       if (p.tma_out) {
         fence_proxy_async_smem();                   // staged rows -> visible to the TMA engine
         epi_barrier(2);
-        if (store_thread) {
+        if (store_thread && !(p.ablate & 3)) {
           const int nl = p.n_levels < kCbTmaLevels - 1 ? p.n_levels : kCbTmaLevels - 1;
           for (int l = 0; l <= nl; ++l) {
             const int off_l = l == 0 ? 0 : (l == 1 ? kCbM * p.NT * 2 : kCbM * p.NT * 3);
@@ -454,6 +572,7 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
     if (p.tma_out && warp == 2 && lane == 0) bulk_wait_all();
   }
   __syncthreads();
+  if (p.pair) cluster_sync_all();          // no exit while the peer may still signal this CTA's barriers
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc<kCbTmemCols>(tmem_base);
@@ -558,6 +677,19 @@ static int launch_corr_build(const void* f1, const void* f2, int B, int D, int H
     ring_bytes = p.a_stages * kABytes + b_bytes;
   }
   if (p.tma_out && ring_bytes + 2 * stage_bytes <= kSmemMax) p.stage_bufs = 2;
+  p.l2_prefetch = 0;
+  p.pf_channels = D < 256 ? D : 256;
+  p.row_order = getenv("PPM_CB_ROW_ORDER") ? atoi(getenv("PPM_CB_ROW_ORDER")) : 0;
+  if (p.res_b && getenv("PPM_CB_PREFETCH")) {
+    const uint32_t pbox[4] = {static_cast<uint32_t>(Tr::kChunkW), 1, static_cast<uint32_t>(p.pf_channels), 1};
+    const uint64_t d1[4] = {(uint64_t)W1, (uint64_t)H, (uint64_t)D, (uint64_t)B};
+    const uint64_t s1[3] = {(uint64_t)ld1 * sizeof(ElemT), (uint64_t)ld1 * H * sizeof(ElemT), (uint64_t)ld1 * H * D * sizeof(ElemT)};
+    const uint64_t d2[4] = {(uint64_t)W2, (uint64_t)H, (uint64_t)D, (uint64_t)B};
+    const uint64_t s2[3] = {(uint64_t)ld2 * sizeof(ElemT), (uint64_t)ld2 * H * sizeof(ElemT), (uint64_t)ld2 * H * D * sizeof(ElemT)};
+    if (make_tensor_map(&om.pf[0], dt, 4, f1, d1, s1, pbox, Tr::kTmaSwizzle) == PPM_OK &&
+        make_tensor_map(&om.pf[1], dt, 4, f2, d2, s2, pbox, Tr::kTmaSwizzle) == PPM_OK)
+      p.l2_prefetch = atoi(getenv("PPM_CB_PREFETCH"));
+  }
   const int smem_bytes = ring_bytes + p.stage_bufs * stage_bytes + 1024;
   auto kern = corr_build_kernel<ElemT, OutT>;
   PPM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
@@ -565,7 +697,31 @@ static int launch_corr_build(const void* f1, const void* f2, int B, int D, int H
   int dev = 0, n_sm = 148;
   PPM_CUDA(cudaGetDevice(&dev));
   PPM_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
-  const long long units = p.res_b ? p.n_items : p.n_tiles;
+  p.spin = getenv("PPM_CB_SPIN") ? 1 : 0;
+  p.noprobe = getenv("PPM_CB_NOPROBE") ? 1 : 0;
+  p.ablate = getenv("PPM_CB_ABLATE") ? atoi(getenv("PPM_CB_ABLATE")) : 0;
+  p.pair = (p.res_b && p.n_ntiles == 2 && !p.row_order && !getenv("PPM_CB_NO_PAIR")) ? 1 : 0;
+  if (p.pair) {
+    cudaLaunchConfig_t cfg{};
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.gridDim = dim3(static_cast<unsigned>(n_sm & ~1)); cfg.blockDim = dim3(kCbThreads);
+    cfg.dynamicSmemBytes = smem_bytes; cfg.stream = st; cfg.attrs = at; cfg.numAttrs = 1;
+    int n_cl = 0;
+    PPM_CUDA(cudaOccupancyMaxActiveClusters(&n_cl, kern, &cfg));     // clusters that can be co-resident (persistent kernel)
+    const long long rows = p.n_items / 2;
+    if (n_cl > rows) n_cl = static_cast<int>(rows);
+    if (getenv("PPM_CB_VERBOSE")) fprintf(stderr, "corr_build: %d co-resident 2-CTA clusters\n", n_cl);
+    if (n_cl >= 1) {
+      cfg.gridDim = dim3(static_cast<unsigned>(2 * n_cl));
+      PPM_CUDA(cudaLaunchKernelEx(&cfg, kern, m1, m2, om, p));
+      PPM_CUDA(cudaGetLastError());
+      return PPM_OK;
+    }
+    p.pair = 0;
+  }
+  const long long units = p.res_b ? (p.row_order ? p.n_items / p.n_ntiles : p.n_items) : p.n_tiles;
   const int grid = static_cast<int>(units < n_sm ? units : n_sm);
   kern<<<grid, kCbThreads, smem_bytes, st>>>(m1, m2, om, p);
   PPM_CUDA(cudaGetLastError());

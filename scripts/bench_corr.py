@@ -35,11 +35,39 @@ def timeit(fn, reps=10):
     t = sorted(ev[i].elapsed_time(ev[i + 1]) for i in range(reps))
     return t[0], t[len(t) // 2]
 
+def graph_time(fn, reps=10, rounds=5):
+    """Kernel time free of the host launch path: `reps` launches captured in one CUDA graph, replayed."""
+    fn(); torch.cuda.synchronize()
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        fn()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=s):
+            for _ in range(reps):
+                fn()
+    torch.cuda.synchronize()
+    g.replay(); torch.cuda.synchronize()
+    ts = []
+    for _ in range(rounds):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(); g.replay(); b.record(); torch.cuda.synchronize()
+        ts.append(a.elapsed_time(b) / reps)
+    return min(ts), sorted(ts)[len(ts) // 2]
+
 blk = P.CorrBlock1D(f1, f2)
 k1_bytes = 2 * B * D * H * W * 2 + 1.9375 * B * H * W * W * 2
 best, med = timeit(lambda: P.CorrBlock1D(f1, f2))
 print(f"K1 build  B={B} D={D} H={H} W={W}: best {best*1e3:.1f} us median {med*1e3:.1f} us -> "
       f"{k1_bytes/med/1e6:.0f} GB/s algorithmic ({k1_bytes/med/1e6/peak:.2f} of {peak:.0f})")
+lv = P.build_pyramid(f1, f2)
+import time
+t0 = time.perf_counter()
+for _ in range(20): P.build_pyramid(f1, f2, levels=lv)
+host_us = (time.perf_counter() - t0) / 20 * 1e6
+torch.cuda.synchronize()
+best, med = graph_time(lambda: P.build_pyramid(f1, f2, levels=lv))
+print(f"K1 graph replay: best {best*1e3:.1f} us median {med*1e3:.1f} us -> {k1_bytes/med/1e6:.0f} GB/s algorithmic "
+      f"({k1_bytes/med/1e6/peak:.2f} of {peak:.0f}); host launch path {host_us:.0f} us per call")
 k2_bytes = B * H * W * 228.0
 best, med = timeit(lambda: P.lookup(blk.corr_pyramid, flow, W2=W), reps=20)
 print(f"K2  per-level lookup {B*H*W} px: best {best*1e3:.1f} us median {med*1e3:.1f} us -> "
