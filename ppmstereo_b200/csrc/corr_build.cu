@@ -38,7 +38,7 @@
 namespace ppm {
 
 constexpr int kCbM = 128;            // pixels of W1 per CTA (UMMA M)
-constexpr int kCbStages = 6;         // streaming mode: [F1 | F2] stages
+constexpr int kCbStages = 6;         // streaming mode: at most this many [F1 | F2] stages
 constexpr int kCbMaxRing = 16;       // barriers: ring stages (either mode) and resident F2 channel chunks
 constexpr int kCbThreads = 320;      // TMA warp, MMA warp, 8 epilogue warps
 constexpr int kCbMaxN = 256;
@@ -58,21 +58,15 @@ struct CorrBuildParams {
   int res_b;                         // 1: the F2 tile of a work item stays in smem for all its M tiles
   int a_stages;                      // res_b: stages of the F1 ring
   int tma_out;                       // levels 0..2 leave through TMA stores from a staged smem tile
-  int stage_bufs;                    // staging buffers (1 or 2)
-  int l2_prefetch;                   // resident mode: the producer pulls the next work item's feature rows into L2
-  int pf_channels;                   // channels per prefetch box
-  int row_order;                     // resident mode: a CTA runs the N tiles of one image row back to back
-  int noprobe;                       // experiments: blocking waits only in the MMA issuer
-  int spin;                          // experiments: poll barriers with test_wait instead of try_wait
   int ablate;                        // experiments only (PPM_CB_ABLATE bit mask): 1 no stores, 2 no TMA-store issue, 4 no loads, 8 no epilogue body, 16 tmem_ld only
   int pair;                          // resident mode, 2 N tiles: a 2-CTA cluster owns an image row (CTA rank = N tile)
                                      // and every F1 tile is fetched once and multicast to both CTAs
 };
 
-// Store maps of levels 0..2: [l][0] = box of two 32-column chunks (128 >> l bytes wide), [l][1] = box of
-// one chunk (64 >> l bytes; the tail when a tile has an odd number of chunks).  The boxes are swizzled
-// (128B / 64B / 32B / none) so that the epilogue's row-per-thread 16-byte writes spread over all banks.
-struct CbStoreMaps { CUtensorMap m[3][2]; CUtensorMap pf[2]; };   // pf: L2 prefetch boxes [pf_channels][64 columns] of F1 / F2
+// Store maps of levels 0..2: box = [32 rows (one epilogue warp)][one 32-column chunk >> l] = 64 / 32 / 16 bytes wide,
+// swizzled 64B / 32B / none so that the warp's row-per-thread 16-byte writes spread over all banks.
+struct CbStoreMaps { CUtensorMap m[3]; };
+constexpr int kCbWarpStage = 2048 + 1024 + 512;   // per-warp staging: L0 | L1 | L2 boxes of one chunk
 constexpr int kCbTmaLevels = 3;
 // Byte offset of 16-byte piece `u` of row `row` inside a staged [128][bp] box (bp = 128, 64, 32 or 16), following
 // the TMA swizzle of that width: the piece index is XORed with the address bits [7, 7 + log2(bp/16)).
@@ -84,7 +78,7 @@ __device__ __forceinline__ int cb_stage_off(int row, int u, int bp) {
 template <typename ElemT> struct CbTraits;
 template <> struct CbTraits<__nv_bfloat16> {
   static constexpr int kChunkW = 64;    // elements in 128 bytes
-  static constexpr int kKC = 32;        // channels per stage
+  static constexpr int kKC = 64;        // channels per stage
   static constexpr int kUK = 16;        // channels per MMA
   static constexpr uint32_t kFmt = 1;   // BF16
   static constexpr uint32_t kLayout = 2;     // SWIZZLE_128B (16-byte atoms), 8 channel rows per swizzle group
@@ -126,10 +120,6 @@ __device__ __forceinline__ void tma_store_3d(const CUtensorMap* m, const void* s
                ::"l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2)
                : "memory");
 }
-__device__ __forceinline__ void tma_prefetch_l2_4d(const CUtensorMap* m, int c0, int c1, int c2, int c3) {
-  asm volatile("cp.async.bulk.prefetch.tensor.4d.L2.global.tile [%0, {%1, %2, %3, %4}];"
-               ::"l"(reinterpret_cast<uint64_t>(m)), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
-}
 __device__ __forceinline__ void tma_load_4d_mc(void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2,
                                                int c3, uint16_t cta_mask) {   // lands at the same offset in every CTA of the mask
   asm volatile(
@@ -151,19 +141,12 @@ __device__ __forceinline__ uint32_t cluster_ctarank() {
 __device__ __forceinline__ void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
-__device__ __forceinline__ void cb_wait(int spin, uint64_t* bar, uint32_t parity) {
-  if (spin) { while (!mbar_test_wait(bar, parity)) {} }
-  else mbar_wait(bar, parity);
-}
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 template <int kPending>
 __device__ __forceinline__ void bulk_wait_read() {
   asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(kPending) : "memory");
 }
 __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
-__device__ __forceinline__ void epi_barrier(int id) {          // the 8 epilogue warps only
-  asm volatile("bar.sync %0, %1;" ::"r"(id), "n"(kCbEpiWarps * 32) : "memory");
-}
 
 // ---- fast epilogue for bf16 output with an exact power-of-two 1/sqrt(D)
 // Rounding goes through cvt.rn.bf16x2.f32 (F2FP, ALU pipe): the scalar cvt.rn.bf16.f32 is an XU-pipe
@@ -260,26 +243,23 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n_bchunks = (p.NT + Tr::kChunkW - 1) / Tr::kChunkW;
   const int n_k = (p.D + Tr::kKC - 1) / Tr::kKC;
-  // smem: streaming mode  [kCbStages x (F1 8 KB | F2 16 KB)] [staging]
+  // smem: streaming mode  [a_stages x (F1 | F2)] [staging]
   //       resident mode   [a_stages x F1 8 KB] [n_k x F2 channel chunk] [staging]
   const int b_chunk_bytes = n_bchunks * kChunkBytes;
-  const int n_ring = p.res_b ? p.a_stages : kCbStages;
+  const int n_ring = p.a_stages;
   uint8_t* b_res = smem + p.a_stages * kABytes;
-  uint8_t* stage0 = smem + (p.res_b ? p.a_stages * kABytes + n_k * b_chunk_bytes : kCbStages * kStageBytes);
+  uint8_t* stage0 = smem + (p.res_b ? p.a_stages * kABytes + n_k * b_chunk_bytes : p.a_stages * kStageBytes);
   // Work order.  Streaming: tile t = blockIdx.x + i*grid -> (bh, mt, nt).  Resident: item = blockIdx.x +
   // (i / n_mtiles)*grid -> (bh, nt), and the item's M tiles follow each other on the same CTA.
-  // p.row_order: a CTA takes whole image rows (blockIdx.x + k*grid) and runs the row's N tiles back to back.
   const long long n_rows_bh = p.n_items / p.n_ntiles;
   const uint32_t crank = p.pair ? cluster_ctarank() : 0;
   const long long my_tiles = p.pair ? ((n_rows_bh - (blockIdx.x >> 1) + (gridDim.x >> 1) - 1) / (gridDim.x >> 1)) * p.n_mtiles
       : p.res_b
-      ? (p.row_order ? ((n_rows_bh - blockIdx.x + gridDim.x - 1) / gridDim.x) * p.n_ntiles
-                     : ((p.n_items - blockIdx.x + gridDim.x - 1) / gridDim.x)) * p.n_mtiles
+      ? ((p.n_items - blockIdx.x + gridDim.x - 1) / gridDim.x) * p.n_mtiles
       : (p.n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x;
   auto item_of = [&](long long j) -> long long {          // j-th work item of this CTA -> global item (bh * n_ntiles + nt)
     if (p.pair) return ((blockIdx.x >> 1) + j * (gridDim.x >> 1)) * 2 + crank;
-    if (!p.row_order) return blockIdx.x + j * gridDim.x;
-    return (blockIdx.x + (j / p.n_ntiles) * gridDim.x) * p.n_ntiles + (j % p.n_ntiles);
+    return blockIdx.x + j * gridDim.x;
   };
   auto decode = [&](long long i, int& bh, int& m0, int& n0, int& mt) {
     if (p.res_b) {
@@ -323,31 +303,16 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
         decode(i, bh, m0, n0, mt);
         const int b = bh / p.H, h = bh % p.H;
         const uint32_t bph = static_cast<uint32_t>((i / p.n_mtiles) & 1) ^ 1;     // resident: item parity
-        if (p.l2_prefetch && mt == 0) {
-          // Pull the NEXT item's feature rows into L2 while this item computes: the ring (56 KB) then only
-          // has to cover the L2 latency, not the DRAM latency under load.
-          const long long nxt = (i + p.n_mtiles < my_tiles) ? item_of(i / p.n_mtiles + 1) : p.n_items;
-          if (nxt < p.n_items) {
-            const int nbh = static_cast<int>(nxt / p.n_ntiles), nn0 = static_cast<int>(nxt % p.n_ntiles) * p.NT;
-            const int nb = nbh / p.H, nh = nbh % p.H;
-            for (int d0 = 0; d0 < p.D; d0 += p.pf_channels) {
-              for (int c = 0; c < n_bchunks; ++c)
-                if (nn0 + c * Tr::kChunkW < p.W2) tma_prefetch_l2_4d(&omap.pf[1], nn0 + c * Tr::kChunkW, nh, d0, nb);
-              if (p.l2_prefetch > 1)
-                for (int x = 0; x < p.W1; x += Tr::kChunkW) tma_prefetch_l2_4d(&omap.pf[0], x, nh, d0, nb);
-            }
-          }
-        }
         for (int kc = 0; kc < n_k; ++kc) {
           if (p.res_b && mt == 0) {                      // the item's F2 tile, once, chunk by chunk
-            cb_wait(p.spin, &bar_bempty[kc], bph);
+            mbar_wait(&bar_bempty[kc], bph);
             if ((p.ablate & 4)) mbar_arrive(&bar_bfull[kc]); else
             mbar_expect_tx(&bar_bfull[kc], b_chunk_bytes);
             for (int c = 0; c < n_bchunks && !(p.ablate & 4); ++c)
               tma_load_4d(b_res + kc * b_chunk_bytes + c * kChunkBytes, &map2, &bar_bfull[kc], n0 + c * Tr::kChunkW, h,
                           kc * Tr::kKC, b);
           }
-          cb_wait(p.spin, &bar_empty[s], ph);
+          mbar_wait(&bar_empty[s], ph);
           if ((p.ablate & 4)) { mbar_arrive(&bar_full[s]); if (++s == n_ring) { s = 0; ph ^= 1; } continue; }
           mbar_expect_tx(&bar_full[s], p.res_b ? kABytes : kABytes + b_chunk_bytes);
           uint8_t* st = smem + s * (p.res_b ? kABytes : kStageBytes);
@@ -378,7 +343,8 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
     // took 0.39 ms of the 0.41 ms HBM budget at the 720p 1/4-res shape).
     {
       const bool leader = elect_one();
-      const uint32_t idesc = umma_idesc(Tr::kFmt, /*a MN-major*/ 1, /*b MN-major*/ 1, kCbM, p.NT);
+      const uint32_t idesc = (p.ablate & 32) ? umma_idesc(Tr::kFmt, 0, 0, kCbM, p.NT)      // timing experiment only
+                                            : umma_idesc(Tr::kFmt, /*a MN-major*/ 1, /*b MN-major*/ 1, kCbM, p.NT);
       // MN-major: LBO = stride between 128-byte MN chunks, SBO = one swizzle group of channel rows
       const uint64_t d0 = umma_desc_sw128(0, kChunkBytes, Tr::kSbo, Tr::kLayout);
       const uint32_t desc_hi = static_cast<uint32_t>(d0 >> 32);
@@ -411,11 +377,11 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
         const bool first_m = p.res_b && mt == 0, last_m = p.res_b && mt == p.n_mtiles - 1;
         const uint32_t bph = static_cast<uint32_t>((it / p.n_mtiles) & 1);
         if (first_m) probe1(&bar_bfull[0], bph);
-        cb_wait(p.spin, &bar_acc_empty[buf], static_cast<uint32_t>((it >> 1) & 1) ^ 1);   // epilogue has drained this accumulator
+        mbar_wait(&bar_acc_empty[buf], static_cast<uint32_t>((it >> 1) & 1) ^ 1);   // epilogue has drained this accumulator
         const uint32_t acc = tmem_base + buf * kCbMaxN;
         for (int kc = 0; kc < n_k; ++kc) {
-          if (p.noprobe || !probed0()) cb_wait(p.spin, &bar_full[s], ph);
-          if (first_m && (p.noprobe || !probed1())) cb_wait(p.spin, &bar_bfull[kc], bph);
+          if (!probed0()) mbar_wait(&bar_full[s], ph);
+          if (first_m && (!probed1())) mbar_wait(&bar_bfull[kc], bph);
           tc_fence_after();
           const uint32_t a_lo = a_lo0 + s * a_step;
           const uint32_t b_lo = b_lo0 + (p.res_b ? kc : s) * b_step;
@@ -454,24 +420,24 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
       const long long row = static_cast<long long>(bh) * p.W1 + m;
       const bool row_ok = m < p.W1;
       const int buf = static_cast<int>(it & 1);
-      // staging layout of one buffer: L0 | L1 | L2, each level a run of swizzled [128 rows][2 chunks] boxes (+ a 1-chunk tail box)
-      const int sb = p.stage_bufs == 2 ? static_cast<int>(it & 1) : 0;
-      uint8_t* stg = stage0 + sb * (kCbM * p.NT * 2 * 7 / 4);
-      const bool store_thread = (warp == 2 && lane == 0);
-      if (p.tma_out) {
-        if (store_thread) {                                   // the TMA stores that last read this buffer are done
-          if (p.stage_bufs == 2) bulk_wait_read<1>(); else bulk_wait_read<0>();
-        }
-        epi_barrier(1);
-      }
-      cb_wait(p.spin, &bar_acc_full[buf], static_cast<uint32_t>((it >> 1) & 1));
+      // per-warp staging (3.5 KB): the L0 | L1 | L2 boxes of the chunk in flight; no CTA-wide barrier anywhere
+      uint8_t* wstg = stage0 + (warp - 2) * kCbWarpStage;
+      mbar_wait(&bar_acc_full[buf], static_cast<uint32_t>((it >> 1) & 1));
       tc_fence_after();
       const uint32_t acc = tmem_base + buf * kCbMaxN + (static_cast<uint32_t>(q * 32) << 16);
-      for (int cc = half; cc < n_chunks; cc += 2) {
+      const int cc0 = (half ^ static_cast<int>(it & 1)) & 1;      // the odd chunk alternates between the two warps of a quarter
+      bool released = false;
+      for (int cc = cc0; cc < n_chunks; cc += 2) {
         if (p.ablate & 8) break;
         uint32_t raw[32];
         tmem_ld_x32(acc + cc * 32, raw);
         tmem_ld_wait();
+        if (cc + 2 >= n_chunks) {                     // last read of this accumulator by this warp: hand it back now
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&bar_acc_empty[buf]);
+          released = true;
+        }
         if (p.ablate & 16) {
           uint32_t x = 0;
           #pragma unroll
@@ -502,21 +468,31 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
               }
               if (p.ablate & 1) { if (w[0] == 0x12345678u && l == 4) *reinterpret_cast<uint32_t*>(p.level[0]) = w[0]; continue; }
               if (p.tma_out && l < kCbTmaLevels) {
+                if (l == 0) {                            // the TMA stores of this warp's previous chunk have read the staging
+                  if (lane == 0) bulk_wait_read<0>();
+                  __syncwarp();
+                }
                 if (l <= p.n_levels) {                   // stage this thread's row segment: n bf16 = n/8 pieces of 16 B
-                  const int off_l = l == 0 ? 0 : (l == 1 ? kCbM * p.NT * 2 : kCbM * p.NT * 3);
-                  const bool tail = (n_chunks & 1) && cc == n_chunks - 1;
-                  const int bp = (tail ? 64 : 128) >> l;                      // bytes per box row
-                  const int u0 = tail ? 0 : (cc & 1) * (n / 8);
-                  uint8_t* box = stg + off_l + (cc >> 1) * ((kCbM * 128) >> l);
+                  uint8_t* box = wstg + (l == 0 ? 0 : (l == 1 ? 2048 : 3072));
                   #pragma unroll
                   for (int j = 0; j < n / 8; ++j)
-                    *reinterpret_cast<uint4*>(box + cb_stage_off(q * 32 + lane, u0 + j, bp)) =
+                    *reinterpret_cast<uint4*>(box + cb_stage_off(lane, j, 64 >> l)) =
                         make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
                 }
               } else if (l <= p.n_levels && row_ok) {
                 const int Wl = p.width[l];
                 const int col0 = (n0 + cc * 32) >> l;
                 cb_store_words(reinterpret_cast<__nv_bfloat16*>(p.level[l]) + row * Wl + col0, w, n, Wl - col0, p.vec_ok[l]);
+              }
+            }
+            if (p.tma_out && !(p.ablate & 3)) {
+              fence_proxy_async_smem();                 // staged rows -> visible to the TMA engine
+              __syncwarp();
+              if (lane == 0) {
+                const int nl = p.n_levels < kCbTmaLevels - 1 ? p.n_levels : kCbTmaLevels - 1;
+                for (int l = 0; l <= nl; ++l)             // rows past W1 and columns past W_l are clipped by the TMA unit
+                  tma_store_3d(&omap.m[l], wstg + (l == 0 ? 0 : (l == 1 ? 2048 : 3072)), (n0 + cc * 32) >> l, m0 + q * 32, bh);
+                bulk_commit();
               }
             }
             continue;
@@ -548,28 +524,13 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
           }
         }
       }
-      tc_fence_before();                            // this warp's TMEM reads of the buffer are done
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&bar_acc_empty[buf]);
-      if (p.tma_out) {
-        fence_proxy_async_smem();                   // staged rows -> visible to the TMA engine
-        epi_barrier(2);
-        if (store_thread && !(p.ablate & 3)) {
-          const int nl = p.n_levels < kCbTmaLevels - 1 ? p.n_levels : kCbTmaLevels - 1;
-          for (int l = 0; l <= nl; ++l) {
-            const int off_l = l == 0 ? 0 : (l == 1 ? kCbM * p.NT * 2 : kCbM * p.NT * 3);
-            const int n_pair = n_chunks >> 1;
-            // rows past W1 and columns past W_l are clipped by the TMA unit
-            for (int pi = 0; pi < n_pair; ++pi)
-              tma_store_3d(&omap.m[l][0], stg + off_l + pi * ((kCbM * 128) >> l), (n0 >> l) + pi * (64 >> l), m0, bh);
-            if (n_chunks & 1)
-              tma_store_3d(&omap.m[l][1], stg + off_l + n_pair * ((kCbM * 128) >> l), (n0 >> l) + n_pair * (64 >> l), m0, bh);
-          }
-          bulk_commit();
-        }
+      if (!released) {                              // (a warp without a chunk in this tile, or the ablation paths)
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bar_acc_empty[buf]);
       }
     }
-    if (p.tma_out && warp == 2 && lane == 0) bulk_wait_all();
+    if (p.tma_out && lane == 0) bulk_wait_all();
   }
   __syncthreads();
   if (p.pair) cluster_sync_all();          // no exit while the peer may still signal this CTA's barriers
@@ -584,7 +545,6 @@ static int launch_corr_build(const void* f1, const void* f2, int B, int D, int H
                              int ld1, int ld2, void* const* levels, int n_levels, cudaStream_t st) {
   using Tr = CbTraits<ElemT>;
   constexpr int kStageBytes = (kCbM / Tr::kChunkW + kCbMaxN / Tr::kChunkW) * Tr::kKC * 128;
-  constexpr int kRingBytes = kCbStages * kStageBytes;
   CorrBuildParams p{};
   p.n_levels = n_levels;
   for (int l = 0; l <= n_levels; ++l) { p.level[l] = levels[l]; p.width[l] = W2 >> l; }
@@ -631,76 +591,63 @@ static int launch_corr_build(const void* f1, const void* f2, int B, int D, int H
     int rc = make_tensor_map(&m2, dt, 4, f2, dims, str, box, Tr::kTmaSwizzle);
     if (rc) return rc;
   }
-  // Output path: levels 0..2 of a bf16 pyramid with an exact scale leave through TMA stores from a
-  // staged smem tile (dense [128][NT >> l] rows); needs 16-byte row pitches in global memory.
+  // Output path: levels 0..2 of a bf16 pyramid with an exact scale leave through TMA stores, one
+  // [32 rows][32 >> l columns] box per epilogue warp, chunk and level, from that warp's private
+  // staging; needs 16-byte row pitches in global memory.
   CbStoreMaps om{};
   p.tma_out = 0;
-  p.stage_bufs = 1;
   int stage_bytes = 0;
-  if (sizeof(OutT) == 2 && p.inv_sqrt_d != 0.f) {
+  if (sizeof(OutT) == 2 && p.inv_sqrt_d != 0.f && !getenv("PPM_CB_NOTMA")) {
     bool ok = true;
     const int nl = n_levels < kCbTmaLevels - 1 ? n_levels : kCbTmaLevels - 1;
     for (int l = 0; l <= nl; ++l)
       ok = ok && ((static_cast<size_t>(W2 >> l) * 2) % 16 == 0) && (reinterpret_cast<uintptr_t>(levels[l]) % 16 == 0);
-    static const CUtensorMapSwizzle kSw[4] = {CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_SWIZZLE_64B,
-                                              CU_TENSOR_MAP_SWIZZLE_32B, CU_TENSOR_MAP_SWIZZLE_NONE};
+    static const CUtensorMapSwizzle kSw[3] = {CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_SWIZZLE_32B, CU_TENSOR_MAP_SWIZZLE_NONE};
     for (int l = 0; l <= nl && ok; ++l) {
       const uint64_t Wl = static_cast<uint64_t>(W2 >> l);
       const uint64_t dims[3] = {Wl, (uint64_t)W1, (uint64_t)B * H};
       const uint64_t str[2] = {Wl * 2, (uint64_t)W1 * Wl * 2};
-      for (int t = 0; t < 2 && ok; ++t) {            // t = 0: two chunks per box, t = 1: one chunk
-        const uint32_t obox[3] = {static_cast<uint32_t>((64 >> t) >> l), static_cast<uint32_t>(kCbM), 1};
-        ok = make_tensor_map(&om.m[l][t], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, levels[l], dims, str, obox,
-                             kSw[l + t]) == PPM_OK;
-      }
+      const uint32_t obox[3] = {static_cast<uint32_t>(32 >> l), 32, 1};
+      ok = make_tensor_map(&om.m[l], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, levels[l], dims, str, obox, kSw[l]) == PPM_OK;
     }
     if (ok) {
       p.tma_out = 1;
-      stage_bytes = kCbM * p.NT * 2 * 7 / 4;
+      stage_bytes = kCbEpiWarps * kCbWarpStage;          // 28 KB
     }
   }
   // Operand path: when an image row has several M tiles, keep the F2 tile of a work item (image row x
   // N tile) in shared memory for all of them and stream only F1 -- the streaming form re-reads F2 once
   // per M tile and is bound by L2->SM traffic (measured: 3.2 GB of operand reads for 1.2 GB of features).
+  // Everything left of the 227 KB goes to the F1 ring: the load path is latency-bound by the bytes in
+  // flight (measured at the 720p 1/4-res shape, loads + MMAs only: 0.89 / 0.58 / 0.53 / 0.33 ms with
+  // 1 / 2 / 3 / 8 stages of 16 KB).
   const int kSmemMax = 227 * 1024 - 1024;
   const int n_k = (D + Tr::kKC - 1) / Tr::kKC;
   const int b_bytes = n_k * ((p.NT + Tr::kChunkW - 1) / Tr::kChunkW) * Tr::kKC * 128;
   constexpr int kABytes = (kCbM / Tr::kChunkW) * Tr::kKC * 128;
   p.res_b = 0;
-  p.a_stages = kCbStages;
   p.n_items = static_cast<long long>(B) * H * p.n_ntiles;
-  int ring_bytes = kRingBytes;
-  if (p.n_mtiles >= 2 && n_k <= kCbMaxRing && b_bytes + 4 * kABytes + stage_bytes <= kSmemMax) {
+  {
+    const int st_max = (kSmemMax - stage_bytes) / kStageBytes;
+    p.a_stages = st_max > kCbStages ? kCbStages : st_max;
+  }
+  int ring_bytes = p.a_stages * kStageBytes;
+  if (p.n_mtiles >= 2 && n_k <= kCbMaxRing && b_bytes + 3 * kABytes + stage_bytes <= kSmemMax) {
     p.res_b = 1;
     int a_st = (kSmemMax - b_bytes - stage_bytes) / kABytes;
     p.a_stages = a_st > kCbMaxRing ? kCbMaxRing : a_st;
+    if (getenv("PPM_CB_ASTAGES") && atoi(getenv("PPM_CB_ASTAGES")) < p.a_stages) p.a_stages = atoi(getenv("PPM_CB_ASTAGES"));
     ring_bytes = p.a_stages * kABytes + b_bytes;
   }
-  if (p.tma_out && ring_bytes + 2 * stage_bytes <= kSmemMax) p.stage_bufs = 2;
-  p.l2_prefetch = 0;
-  p.pf_channels = D < 256 ? D : 256;
-  p.row_order = getenv("PPM_CB_ROW_ORDER") ? atoi(getenv("PPM_CB_ROW_ORDER")) : 0;
-  if (p.res_b && getenv("PPM_CB_PREFETCH")) {
-    const uint32_t pbox[4] = {static_cast<uint32_t>(Tr::kChunkW), 1, static_cast<uint32_t>(p.pf_channels), 1};
-    const uint64_t d1[4] = {(uint64_t)W1, (uint64_t)H, (uint64_t)D, (uint64_t)B};
-    const uint64_t s1[3] = {(uint64_t)ld1 * sizeof(ElemT), (uint64_t)ld1 * H * sizeof(ElemT), (uint64_t)ld1 * H * D * sizeof(ElemT)};
-    const uint64_t d2[4] = {(uint64_t)W2, (uint64_t)H, (uint64_t)D, (uint64_t)B};
-    const uint64_t s2[3] = {(uint64_t)ld2 * sizeof(ElemT), (uint64_t)ld2 * H * sizeof(ElemT), (uint64_t)ld2 * H * D * sizeof(ElemT)};
-    if (make_tensor_map(&om.pf[0], dt, 4, f1, d1, s1, pbox, Tr::kTmaSwizzle) == PPM_OK &&
-        make_tensor_map(&om.pf[1], dt, 4, f2, d2, s2, pbox, Tr::kTmaSwizzle) == PPM_OK)
-      p.l2_prefetch = atoi(getenv("PPM_CB_PREFETCH"));
-  }
-  const int smem_bytes = ring_bytes + p.stage_bufs * stage_bytes + 1024;
+  const int smem_bytes = ring_bytes + stage_bytes + 1024;
   auto kern = corr_build_kernel<ElemT, OutT>;
   PPM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
   // persistent: one CTA per SM (it owns all 512 TMEM columns), static round-robin over the tiles
   int dev = 0, n_sm = 148;
   PPM_CUDA(cudaGetDevice(&dev));
   PPM_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
-  p.spin = getenv("PPM_CB_SPIN") ? 1 : 0;
-  p.noprobe = getenv("PPM_CB_NOPROBE") ? 1 : 0;
   p.ablate = getenv("PPM_CB_ABLATE") ? atoi(getenv("PPM_CB_ABLATE")) : 0;
-  p.pair = (p.res_b && p.n_ntiles == 2 && !p.row_order && !getenv("PPM_CB_NO_PAIR")) ? 1 : 0;
+  p.pair = (p.res_b && p.n_ntiles == 2 && !getenv("PPM_CB_NO_PAIR")) ? 1 : 0;
   if (p.pair) {
     cudaLaunchConfig_t cfg{};
     cudaLaunchAttribute at[1];
@@ -721,7 +668,7 @@ static int launch_corr_build(const void* f1, const void* f2, int B, int D, int H
     }
     p.pair = 0;
   }
-  const long long units = p.res_b ? (p.row_order ? p.n_items / p.n_ntiles : p.n_items) : p.n_tiles;
+  const long long units = p.res_b ? p.n_items : p.n_tiles;
   const int grid = static_cast<int>(units < n_sm ? units : n_sm);
   kern<<<grid, kCbThreads, smem_bytes, st>>>(m1, m2, om, p);
   PPM_CUDA(cudaGetLastError());
