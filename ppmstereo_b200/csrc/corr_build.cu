@@ -9,23 +9,29 @@
 // directly (no transpose pass, no repack).  bf16 inputs use kind::f16, fp32 inputs kind::tf32.
 //
 // One work item is a 128 x NT tile (NT <= 256) of one row problem:
-//   warp 0    TMA producer (6-stage mbarrier ring over the channel axis: 144 KB in flight to cover the L2 latency)
-//   warp 1    TMEM allocation + single-thread tcgen05.mma issue, accumulator in TMEM
-//   warps 2-9 epilogue: tcgen05.ld (one output row per thread, 32 columns at a time), scale by
-//             1/sqrt(D), form levels 1..4 by pair-averaging IN REGISTERS (a thread owns whole
-//             row segments, so pooling along j needs no communication) and store every level
-//             through a dense smem tile and ONE TMA store per level and work item (levels 0-2;
-//             a thread's own 64-byte row segments written with LSU stores touch 32 different
-//             128-byte lines per instruction and made the LSU tag stage the bottleneck); the two
-//             small levels (8 and 4 bytes per thread and chunk) go straight from registers.
+//   warp 0    TMA producer (mbarrier ring of 64-channel stages over the channel axis; every byte of shared
+//             memory that is left goes to this ring -- the load path is latency-bound by the bytes in flight)
+//   warp 1    TMEM allocation + tcgen05.mma issue (the warp walks the loop convergently, one elected lane
+//             issues; descriptors formed with one add; the next stage's barrier probed ahead of the MMAs)
+//   warps 2-9 epilogue, every warp on its own: tcgen05.ld (one output row per thread, 32 columns at a
+//             time), hand the accumulator back right after the warp's last load, scale by 1/sqrt(D), form
+//             levels 1..4 by pair-averaging IN REGISTERS (a thread owns whole row segments, so pooling
+//             along j needs no communication).  Level 0 leaves through the warp's private, double-buffered
+//             and swizzled [32 rows][64 B] staging box and one TMA store per chunk (a thread's own 64-byte
+//             row segments written with LSU stores touch 32 different 128-byte lines per instruction);
+//             levels 1-4 (32 ... 4 bytes per thread and chunk) go straight from registers.  No CTA-wide
+//             barrier anywhere in the epilogue.
 // Persistent: one CTA per SM loops over work items; the smem ring runs on across items and the
 // accumulator is double-buffered in TMEM (2 x 256 columns), so the TMA loads and MMAs of tile i+1
 // overlap the epilogue of tile i.  When an image row has several M tiles, a work item is (image
-// row, N tile): its F2 tile stays in shared memory while the F1 tiles stream past it.
-// Measured at the 720p 1/4-res shape (2.67 GB algorithmic, 0.41 ms at the HBM copy peak): 0.58 ms.
-// With the epilogue and the stores removed the load + MMA pipeline alone takes 0.41 ms (2.1 GB of
-// L2->SM operand reads, half of them across the die-to-die fabric), with the stores removed 0.46 ms:
-// the remaining gap is operand traffic competing with the output stream, not arithmetic.
+// row, N tile): its F2 tile stays in shared memory while the F1 tiles stream past it.  When the row
+// has exactly two N tiles (W2 = 320 -> 2 x 160), a 2-CTA cluster owns the image row (CTA rank = N tile)
+// and every F1 tile is fetched once and multicast to both CTAs (each CTA issues half of the boxes; the
+// ring's empty barriers take one tcgen05.commit arrival from each CTA).
+// Measured at the 720p 1/4-res shape (2.67 GB algorithmic, 0.41 ms at the HBM copy peak), CUDA-graph
+// replay: 0.50 ms (0.81); history 2.49 -> 0.84 -> 0.60 -> 0.58 -> 0.50.  Ablations (PPM_CB_ABLATE bit mask,
+// same box): MMA + barrier skeleton 0.25 ms, + loads 0.31, + epilogue arithmetic (no stores) 0.27,
+// + stores (no loads) 0.48 -- the store side (TMA box rows + scattered LSU lines) is what is left.
 // The volume is written exactly once and never re-read: 1.9375 x W1 x W2 elements per row.
 #include <math.h>
 #include <stdio.h>
@@ -57,6 +63,8 @@ struct CorrBuildParams {
   int vec_ok[kCbLevels];             // level rows allow the full-width vector store
   int res_b;                         // 1: the F2 tile of a work item stays in smem for all its M tiles
   int a_stages;                      // res_b: stages of the F1 ring
+  int wstage;                        // bytes of one per-warp staging buffer (levels 0 .. tma_levels-1 of one chunk)
+  int tma_levels;                    // levels 0 .. tma_levels-1 leave through TMA stores, the rest straight from registers
   int tma_out;                       // levels 0..2 leave through TMA stores from a staged smem tile
   int ablate;                        // experiments only (PPM_CB_ABLATE bit mask): 1 no stores, 2 no TMA-store issue, 4 no loads, 8 no epilogue body, 16 tmem_ld only
   int pair;                          // resident mode, 2 N tiles: a 2-CTA cluster owns an image row (CTA rank = N tile)
@@ -413,6 +421,7 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
     const int q = warp & 3;                         // TMEM lane quarter this warp may access
     const int half = (warp - 2) >> 2;               // which chunks this warp takes
     const int n_chunks = p.NT / 32;
+    uint32_t stage_flip = 0;
     for (long long it = 0; it < my_tiles; ++it) {
       int bh, m0, n0, mt_unused;
       decode(it, bh, m0, n0, mt_unused);
@@ -421,12 +430,13 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
       const bool row_ok = m < p.W1;
       const int buf = static_cast<int>(it & 1);
       // per-warp staging (3.5 KB): the L0 | L1 | L2 boxes of the chunk in flight; no CTA-wide barrier anywhere
-      uint8_t* wstg = stage0 + (warp - 2) * kCbWarpStage;
+      uint8_t* const wstg0 = stage0 + (warp - 2) * (2 * p.wstage);   // two buffers: chunk k+1 is staged while the TMA unit reads chunk k
       mbar_wait(&bar_acc_full[buf], static_cast<uint32_t>((it >> 1) & 1));
       tc_fence_after();
       const uint32_t acc = tmem_base + buf * kCbMaxN + (static_cast<uint32_t>(q * 32) << 16);
       const int cc0 = (half ^ static_cast<int>(it & 1)) & 1;      // the odd chunk alternates between the two warps of a quarter
       bool released = false;
+      uint8_t* wstg = wstg0;
       for (int cc = cc0; cc < n_chunks; cc += 2) {
         if (p.ablate & 8) break;
         uint32_t raw[32];
@@ -467,9 +477,11 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
                 }
               }
               if (p.ablate & 1) { if (w[0] == 0x12345678u && l == 4) *reinterpret_cast<uint32_t*>(p.level[0]) = w[0]; continue; }
-              if (p.tma_out && l < kCbTmaLevels) {
+              if (p.tma_out && l < p.tma_levels) {
                 if (l == 0) {                            // the TMA stores of this warp's previous chunk have read the staging
-                  if (lane == 0) bulk_wait_read<0>();
+                  wstg = wstg0 + (stage_flip & 1) * p.wstage;
+                  ++stage_flip;
+                  if (lane == 0) bulk_wait_read<1>();     // the stores that read THIS buffer (two chunks ago) are done
                   __syncwarp();
                 }
                 if (l <= p.n_levels) {                   // stage this thread's row segment: n bf16 = n/8 pieces of 16 B
@@ -489,8 +501,8 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
               fence_proxy_async_smem();                 // staged rows -> visible to the TMA engine
               __syncwarp();
               if (lane == 0) {
-                const int nl = p.n_levels < kCbTmaLevels - 1 ? p.n_levels : kCbTmaLevels - 1;
-                for (int l = 0; l <= nl; ++l)             // rows past W1 and columns past W_l are clipped by the TMA unit
+                const int nl = p.n_levels < p.tma_levels - 1 ? p.n_levels : p.tma_levels - 1;
+                for (int l = (p.ablate & 128) ? 1 : 0; l <= ((p.ablate & 64) ? 0 : nl); ++l)             // rows past W1 and columns past W_l are clipped by the TMA unit
                   tma_store_3d(&omap.m[l], wstg + (l == 0 ? 0 : (l == 1 ? 2048 : 3072)), (n0 + cc * 32) >> l, m0 + q * 32, bh);
                 bulk_commit();
               }
@@ -612,7 +624,13 @@ static int launch_corr_build(const void* f1, const void* f2, int B, int D, int H
     }
     if (ok) {
       p.tma_out = 1;
-      stage_bytes = kCbEpiWarps * kCbWarpStage;          // 28 KB
+      // Measured (720p 1/4-res, same box): levels 0-2 / 0-1 / 0 through TMA = 0.536 / 0.522 / 0.513 ms -- a TMA store
+      // costs ~2.7 clk per box row whatever its width, so only the 64-byte level-0 rows go that way.
+      p.tma_levels = getenv("PPM_CB_TMA_LEVELS") ? atoi(getenv("PPM_CB_TMA_LEVELS")) : 1;
+      if (p.tma_levels < 1) p.tma_levels = 1;
+      if (p.tma_levels > nl + 1) p.tma_levels = nl + 1;
+      p.wstage = p.tma_levels == 1 ? 2048 : (p.tma_levels == 2 ? 3072 : 3584);
+      stage_bytes = kCbEpiWarps * 2 * p.wstage;
     }
   }
   // Operand path: when an image row has several M tiles, keep the F2 tile of a work item (image row x
