@@ -83,6 +83,83 @@ convex_upsample_kernel(const float* __restrict__ flow, const MaskT* __restrict__
   }
 }
 
+// bf16 masks, even W: a thread takes the pixel pair (x, x+1) so that every mask channel is read with 4-byte loads
+// (the one-pixel form issues 144 two-byte loads per thread and is load-instruction-bound at half the HBM rate).
+// Per pixel the arithmetic and its order are those of the kernel above: results are bit-identical.
+__global__ void __launch_bounds__(kCuThreads)
+convex_upsample_bf16x2_kernel(const float* __restrict__ flow, const __nv_bfloat16* __restrict__ mask,
+                              float* __restrict__ out, int H, int W) {
+  const int n = blockIdx.y;
+  const int HW = H * W;
+  const int q = 2 * (blockIdx.x * kCuThreads + threadIdx.x);
+  if (q >= HW) return;
+  const int y = q / W, x = q - y * W;                       // x even, x + 1 < W
+  float fw[2][3][4];                                        // rows y-1..y+1, columns x-1..x+2 of r * flow, zero padded
+  const float* fl = flow + static_cast<long long>(n) * 2 * HW;
+  #pragma unroll
+  for (int dy = 0; dy < 3; ++dy)
+    #pragma unroll
+    for (int dx = 0; dx < 4; ++dx) {
+      const int yy = y + dy - 1, xx = x + dx - 1;
+      const bool in = yy >= 0 && yy < H && xx >= 0 && xx < W;
+      #pragma unroll
+      for (int c = 0; c < 2; ++c)
+        fw[c][dy][dx] = in ? __fmul_rn(static_cast<float>(kCuRate), __ldg(fl + c * HW + yy * W + xx)) : 0.f;
+    }
+  const uint32_t* mk = reinterpret_cast<const uint32_t*>(mask + static_cast<long long>(n) * 9 * kCuRate * kCuRate * HW + q);
+  const long long ch_words = HW / 2;
+  float* o = out + static_cast<long long>(n) * 2 * kCuRate * kCuRate * HW + static_cast<long long>(y) * kCuRate * kCuRate * W +
+             x * kCuRate;
+  #pragma unroll
+  for (int i = 0; i < kCuRate; ++i) {
+    uint32_t mw[9][kCuRate];
+    #pragma unroll
+    for (int k = 0; k < 9; ++k)
+      #pragma unroll
+      for (int j = 0; j < kCuRate; ++j)
+        mw[k][j] = __ldg(mk + static_cast<long long>((k * kCuRate + i) * kCuRate + j) * ch_words);
+    float r[2][2][kCuRate];                                 // [pixel][channel][fine column]
+    #pragma unroll
+    for (int px = 0; px < 2; ++px)
+      #pragma unroll
+      for (int j = 0; j < kCuRate; ++j) {
+        float m[9];
+        #pragma unroll
+        for (int k = 0; k < 9; ++k) m[k] = __uint_as_float(px ? (mw[k][j] & 0xFFFF0000u) : (mw[k][j] << 16));
+        float mx = m[0];
+        #pragma unroll
+        for (int k = 1; k < 9; ++k) mx = fmaxf(mx, m[k]);
+        float e[10], sum = 0.f;
+        #pragma unroll
+        for (int k = 0; k < 9; ++k) { e[k] = ex2_approx((m[k] - mx) * 1.4426950408889634f); sum += e[k]; }
+        const float inv = __frcp_rn(sum);
+        // weights rounded to bf16 two at a time (cvt.rn.bf16x2.f32 runs on the ALU pipe; the scalar cvt shares the
+        // XU pipe with the 144 ex2 per pixel and made it the busiest unit: 61 % in the first ncu capture)
+        float pw[10];
+        #pragma unroll
+        for (int k = 0; k < 10; k += 2) {
+          const uint32_t w2 = pack_bf16x2(e[k] * inv, k + 1 < 9 ? e[k + 1] * inv : 0.f);
+          pw[k] = __uint_as_float(w2 << 16);
+          pw[k + 1] = __uint_as_float(w2 & 0xFFFF0000u);
+        }
+        float a0 = 0.f, a1 = 0.f;
+        #pragma unroll
+        for (int k = 0; k < 9; ++k) {
+          a0 = __fadd_rn(a0, __fmul_rn(pw[k], fw[0][k / 3][k % 3 + px]));
+          a1 = __fadd_rn(a1, __fmul_rn(pw[k], fw[1][k / 3][k % 3 + px]));
+        }
+        r[px][0][j] = a0; r[px][1][j] = a1;
+      }
+    const long long row = static_cast<long long>(i) * kCuRate * W;
+    #pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      float* oc = o + static_cast<long long>(c) * kCuRate * kCuRate * HW + row;
+      *reinterpret_cast<float4*>(oc) = make_float4(r[0][c][0], r[0][c][1], r[0][c][2], r[0][c][3]);
+      *reinterpret_cast<float4*>(oc + kCuRate) = make_float4(r[1][c][0], r[1][c][1], r[1][c][2], r[1][c][3]);
+    }
+  }
+}
+
 }  // namespace ppm
 
 extern "C" int ppm_convex_upsample(const float* flow, const void* mask, int mask_dtype, int N, int H, int W,
@@ -96,7 +173,10 @@ extern "C" int ppm_convex_upsample(const float* flow, const void* mask, int mask
   PPM_CHECK((reinterpret_cast<uintptr_t>(out) & 15) == 0, PPM_ERR_ARG, "ppm_convex_upsample: out must be 16-byte aligned");
   dim3 grid((H * W + kCuThreads - 1) / kCuThreads, N);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (mask_dtype == PPM_BF16)
+  if (mask_dtype == PPM_BF16 && W % 2 == 0 && (reinterpret_cast<uintptr_t>(mask) & 3) == 0) {
+    dim3 grid2((H * W / 2 + kCuThreads - 1) / kCuThreads, N);
+    convex_upsample_bf16x2_kernel<<<grid2, kCuThreads, 0, st>>>(flow, static_cast<const __nv_bfloat16*>(mask), out, H, W);
+  } else if (mask_dtype == PPM_BF16)
     convex_upsample_kernel<__nv_bfloat16><<<grid, kCuThreads, 0, st>>>(flow, static_cast<const __nv_bfloat16*>(mask), out, H, W);
   else
     convex_upsample_kernel<float><<<grid, kCuThreads, 0, st>>>(flow, static_cast<const float*>(mask), out, H, W);

@@ -93,3 +93,18 @@ def test_rejects_cpu_tensors_and_bad_shapes(P):
         P.convex_upsample(torch.zeros(1, 2, 4, 4), torch.zeros(1, 144, 4, 4))
     with pytest.raises(RuntimeError):
         P.convex_upsample(torch.zeros(1, 2, 4, 4).cuda(), torch.zeros(1, 100, 4, 4).cuda())
+
+
+@pytest.mark.parametrize("shape", [(2, 46, 80), (1, 7, 6), (3, 5, 130)])
+def test_bf16_pixel_pair_kernel_equals_one_pixel_kernel(P, shape):
+    """bf16 masks with an even W take the pixel-pair kernel (4-byte mask loads); a mask whose storage is only
+    2-byte aligned takes the one-pixel kernel.  Same arithmetic per pixel -> bit-identical outputs."""
+    N, H, W = shape
+    g = torch.Generator(device="cuda").manual_seed(H * 100 + W)
+    flow = torch.randn(N, 2, H, W, generator=g, device="cuda") * 10
+    n = N * 144 * H * W
+    buf = (torch.randn(n + 1, generator=g, device="cuda") * 3).bfloat16()
+    odd = buf[1:].view(N, 144, H, W)                   # data_ptr % 4 == 2 -> one-pixel kernel
+    even = odd.clone()                                 # fresh allocation -> pixel-pair kernel
+    assert odd.data_ptr() % 4 == 2 and even.data_ptr() % 4 == 0
+    assert torch.equal(P.convex_upsample(flow, even, 4), P.convex_upsample(flow, odd, 4))
