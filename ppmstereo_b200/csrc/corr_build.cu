@@ -63,19 +63,17 @@ struct CorrBuildParams {
   int vec_ok[kCbLevels];             // level rows allow the full-width vector store
   int res_b;                         // 1: the F2 tile of a work item stays in smem for all its M tiles
   int a_stages;                      // res_b: stages of the F1 ring
-  int wstage;                        // bytes of one per-warp staging buffer (levels 0 .. tma_levels-1 of one chunk)
-  int tma_levels;                    // levels 0 .. tma_levels-1 leave through TMA stores, the rest straight from registers
   int tma_out;                       // levels 0..2 leave through TMA stores from a staged smem tile
   int ablate;                        // experiments only (PPM_CB_ABLATE bit mask): 1 no stores, 2 no TMA-store issue, 4 no loads, 8 no epilogue body, 16 tmem_ld only
   int pair;                          // resident mode, 2 N tiles: a 2-CTA cluster owns an image row (CTA rank = N tile)
                                      // and every F1 tile is fetched once and multicast to both CTAs
 };
 
-// Store maps of levels 0..2: box = [32 rows (one epilogue warp)][one 32-column chunk >> l] = 64 / 32 / 16 bytes wide,
-// swizzled 64B / 32B / none so that the warp's row-per-thread 16-byte writes spread over all banks.
-struct CbStoreMaps { CUtensorMap m[3]; };
-constexpr int kCbWarpStage = 2048 + 1024 + 512;   // per-warp staging: L0 | L1 | L2 boxes of one chunk
-constexpr int kCbTmaLevels = 3;
+// Level-0 store maps: [0] = [32 rows (one epilogue warp)][two 32-column chunks = 128 B], SWIZZLE_128B;
+// [1] = [32 rows][one chunk = 64 B], SWIZZLE_64B (the tail unit of a tile with an odd number of chunks).  The swizzle
+// spreads the warp's row-per-thread 16-byte writes over all banks.
+struct CbStoreMaps { CUtensorMap m[2]; };
+constexpr int kCbWarpStage = 4096;                // per-warp staging box
 // Byte offset of 16-byte piece `u` of row `row` inside a staged [128][bp] box (bp = 128, 64, 32 or 16), following
 // the TMA swizzle of that width: the piece index is XORed with the address bits [7, 7 + log2(bp/16)).
 __device__ __forceinline__ int cb_stage_off(int row, int u, int bp) {
@@ -421,7 +419,6 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
     const int q = warp & 3;                         // TMEM lane quarter this warp may access
     const int half = (warp - 2) >> 2;               // which chunks this warp takes
     const int n_chunks = p.NT / 32;
-    uint32_t stage_flip = 0;
     for (long long it = 0; it < my_tiles; ++it) {
       int bh, m0, n0, mt_unused;
       decode(it, bh, m0, n0, mt_unused);
@@ -429,20 +426,27 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
       const long long row = static_cast<long long>(bh) * p.W1 + m;
       const bool row_ok = m < p.W1;
       const int buf = static_cast<int>(it & 1);
-      // per-warp staging (3.5 KB): the L0 | L1 | L2 boxes of the chunk in flight; no CTA-wide barrier anywhere
-      uint8_t* const wstg0 = stage0 + (warp - 2) * (2 * p.wstage);   // two buffers: chunk k+1 is staged while the TMA unit reads chunk k
       mbar_wait(&bar_acc_full[buf], static_cast<uint32_t>((it >> 1) & 1));
       tc_fence_after();
       const uint32_t acc = tmem_base + buf * kCbMaxN + (static_cast<uint32_t>(q * 32) << 16);
-      const int cc0 = (half ^ static_cast<int>(it & 1)) & 1;      // the odd chunk alternates between the two warps of a quarter
+      // A warp takes units of two adjacent chunks (one 128-byte-wide TMA store box per unit); the two warps of a
+      // lane quarter take alternate units, and the odd unit alternates between them from tile to tile.
+      const int hsel = (half ^ static_cast<int>(it & 1)) & 1;
+      const int n_units = (n_chunks + 1) >> 1;
+      int last_cc = -1;
+      {
+        int ul = n_units - 1;
+        if ((ul & 1) != hsel) --ul;
+        if (ul >= 0) last_cc = 2 * ul + 1 < n_chunks ? 2 * ul + 1 : n_chunks - 1;
+      }
       bool released = false;
-      uint8_t* wstg = wstg0;
-      for (int cc = cc0; cc < n_chunks; cc += 2) {
-        if (p.ablate & 8) break;
+      uint8_t* const wstg = stage0 + (warp - 2) * kCbWarpStage;   // this warp's private staging box
+      for (int u = hsel; u < n_units && !(p.ablate & 8); u += 2)
+      for (int cc = 2 * u; cc < 2 * u + 2 && cc < n_chunks; ++cc) {
         uint32_t raw[32];
         tmem_ld_x32(acc + cc * 32, raw);
         tmem_ld_wait();
-        if (cc + 2 >= n_chunks) {                     // last read of this accumulator by this warp: hand it back now
+        if (cc == last_cc) {                          // last read of this accumulator by this warp: hand it back now
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(&bar_acc_empty[buf]);
@@ -477,33 +481,27 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
                 }
               }
               if (p.ablate & 1) { if (w[0] == 0x12345678u && l == 4) *reinterpret_cast<uint32_t*>(p.level[0]) = w[0]; continue; }
-              if (p.tma_out && l < p.tma_levels) {
-                if (l == 0) {                            // the TMA stores of this warp's previous chunk have read the staging
-                  wstg = wstg0 + (stage_flip & 1) * p.wstage;
-                  ++stage_flip;
-                  if (lane == 0) bulk_wait_read<1>();     // the stores that read THIS buffer (two chunks ago) are done
+              if (p.tma_out && l == 0) {                 // level 0: this thread's 64-byte row segment -> the warp's staging box
+                const bool single = (n_chunks & 1) && cc == n_chunks - 1;      // tail unit of one chunk: [32][64 B] box
+                if ((cc & 1) == 0) {                     // first chunk of the unit: the previous unit's store has read the box
+                  if (lane == 0) bulk_wait_read<0>();
                   __syncwarp();
                 }
-                if (l <= p.n_levels) {                   // stage this thread's row segment: n bf16 = n/8 pieces of 16 B
-                  uint8_t* box = wstg + (l == 0 ? 0 : (l == 1 ? 2048 : 3072));
-                  #pragma unroll
-                  for (int j = 0; j < n / 8; ++j)
-                    *reinterpret_cast<uint4*>(box + cb_stage_off(lane, j, 64 >> l)) =
-                        make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
-                }
+                #pragma unroll
+                for (int j = 0; j < 4; ++j)
+                  *reinterpret_cast<uint4*>(wstg + (single ? cb_stage_off(lane, j, 64) : cb_stage_off(lane, (cc & 1) * 4 + j, 128))) =
+                      make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
               } else if (l <= p.n_levels && row_ok) {
                 const int Wl = p.width[l];
                 const int col0 = (n0 + cc * 32) >> l;
                 cb_store_words(reinterpret_cast<__nv_bfloat16*>(p.level[l]) + row * Wl + col0, w, n, Wl - col0, p.vec_ok[l]);
               }
             }
-            if (p.tma_out && !(p.ablate & 3)) {
+            if (p.tma_out && !(p.ablate & 3) && ((cc & 1) || cc == n_chunks - 1)) {     // unit complete
               fence_proxy_async_smem();                 // staged rows -> visible to the TMA engine
               __syncwarp();
-              if (lane == 0) {
-                const int nl = p.n_levels < p.tma_levels - 1 ? p.n_levels : p.tma_levels - 1;
-                for (int l = (p.ablate & 128) ? 1 : 0; l <= ((p.ablate & 64) ? 0 : nl); ++l)             // rows past W1 and columns past W_l are clipped by the TMA unit
-                  tma_store_3d(&omap.m[l], wstg + (l == 0 ? 0 : (l == 1 ? 2048 : 3072)), (n0 + cc * 32) >> l, m0 + q * 32, bh);
+              if (lane == 0) {                          // rows past W1 and columns past W2 are clipped by the TMA unit
+                tma_store_3d(&omap.m[cc & 1 ? 0 : 1], wstg, n0 + (cc & ~1) * 32, m0 + q * 32, bh);
                 bulk_commit();
               }
             }
@@ -603,34 +601,25 @@ static int launch_corr_build(const void* f1, const void* f2, int B, int D, int H
     int rc = make_tensor_map(&m2, dt, 4, f2, dims, str, box, Tr::kTmaSwizzle);
     if (rc) return rc;
   }
-  // Output path: levels 0..2 of a bf16 pyramid with an exact scale leave through TMA stores, one
-  // [32 rows][32 >> l columns] box per epilogue warp, chunk and level, from that warp's private
-  // staging; needs 16-byte row pitches in global memory.
+  // Output path: level 0 of a bf16 pyramid with an exact scale leaves through TMA stores, one [32 rows][128 B] box
+  // per epilogue warp and pair of chunks, from that warp's private staging; needs a 16-byte row pitch in global memory.
   CbStoreMaps om{};
   p.tma_out = 0;
   int stage_bytes = 0;
   if (sizeof(OutT) == 2 && p.inv_sqrt_d != 0.f && !getenv("PPM_CB_NOTMA")) {
-    bool ok = true;
-    const int nl = n_levels < kCbTmaLevels - 1 ? n_levels : kCbTmaLevels - 1;
-    for (int l = 0; l <= nl; ++l)
-      ok = ok && ((static_cast<size_t>(W2 >> l) * 2) % 16 == 0) && (reinterpret_cast<uintptr_t>(levels[l]) % 16 == 0);
-    static const CUtensorMapSwizzle kSw[3] = {CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_SWIZZLE_32B, CU_TENSOR_MAP_SWIZZLE_NONE};
-    for (int l = 0; l <= nl && ok; ++l) {
-      const uint64_t Wl = static_cast<uint64_t>(W2 >> l);
-      const uint64_t dims[3] = {Wl, (uint64_t)W1, (uint64_t)B * H};
-      const uint64_t str[2] = {Wl * 2, (uint64_t)W1 * Wl * 2};
-      const uint32_t obox[3] = {static_cast<uint32_t>(32 >> l), 32, 1};
-      ok = make_tensor_map(&om.m[l], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, levels[l], dims, str, obox, kSw[l]) == PPM_OK;
+    bool ok = ((static_cast<size_t>(W2) * 2) % 16 == 0) && (reinterpret_cast<uintptr_t>(levels[0]) % 16 == 0);
+    if (ok) {
+      const uint64_t dims[3] = {(uint64_t)W2, (uint64_t)W1, (uint64_t)B * H};
+      const uint64_t str[2] = {(uint64_t)W2 * 2, (uint64_t)W1 * W2 * 2};
+      const uint32_t box2[3] = {64, 32, 1}, box1[3] = {32, 32, 1};
+      ok = make_tensor_map(&om.m[0], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, levels[0], dims, str, box2, CU_TENSOR_MAP_SWIZZLE_128B) == PPM_OK &&
+           make_tensor_map(&om.m[1], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, levels[0], dims, str, box1, CU_TENSOR_MAP_SWIZZLE_64B) == PPM_OK;
     }
     if (ok) {
+      // Only level 0 goes through TMA: a TMA store costs ~2.7 clk per box row whatever its width (measured, same box:
+      // levels 0-2 / 0-1 / 0 through TMA = 0.536 / 0.522 / 0.513 ms), so the narrow rows of levels 1-4 leave from registers.
       p.tma_out = 1;
-      // Measured (720p 1/4-res, same box): levels 0-2 / 0-1 / 0 through TMA = 0.536 / 0.522 / 0.513 ms -- a TMA store
-      // costs ~2.7 clk per box row whatever its width, so only the 64-byte level-0 rows go that way.
-      p.tma_levels = getenv("PPM_CB_TMA_LEVELS") ? atoi(getenv("PPM_CB_TMA_LEVELS")) : 1;
-      if (p.tma_levels < 1) p.tma_levels = 1;
-      if (p.tma_levels > nl + 1) p.tma_levels = nl + 1;
-      p.wstage = p.tma_levels == 1 ? 2048 : (p.tma_levels == 2 ? 3072 : 3584);
-      stage_bytes = kCbEpiWarps * 2 * p.wstage;
+      stage_bytes = kCbEpiWarps * kCbWarpStage;          // 32 KB
     }
   }
   // Operand path: when an image row has several M tiles, keep the F2 tile of a work item (image row x
