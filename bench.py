@@ -178,9 +178,9 @@ def run_clip(P, inputs, beta, from_host: bool, time_attend: bool = False, runner
 # --------------------------------------------------------------------------------------------
 # CPU arm: the oracle port of the reference's path on the host cores (bounded sample)
 # --------------------------------------------------------------------------------------------
-SAMPLE_DS, SAMPLE_T = 16, KERNEL_SIZE
-SAMPLE_DESC = ("one update iteration of the 1/16-res level of a 20-frame 720p window (h x w = 46 x 80, hw = 3680, "
-               "T = 20, K = 5): corr pyramid build + lookup + full PPM read, oracle/ppm_oracle.py (port of the "
+SAMPLE_DS, SAMPLE_T, SAMPLE_ITERS = 16, KERNEL_SIZE, 5
+SAMPLE_DESC = ("pyramid build + 5 update iterations of the 1/16-res level of a 20-frame 720p window (h x w = 46 x 80, hw = 3680, "
+               "T = 20, K = 5; each iteration = lookup + full PPM read; about 10 s), oracle/ppm_oracle.py (port of the "
                "reference's PyTorch CPU path) on all host threads; frames/s extrapolated to the 40-frame clip by "
                "attention FLOPs")
 
@@ -200,14 +200,16 @@ def cpu_sample_step(s) -> float:
     from oracle import ppm_oracle as O          # the CPU baseline is the one place bench.py runs the oracle
     t0 = time.perf_counter()
     lv = O.corr_pyramid(s["f1"], s["f2"], mode="bf16")
-    O.corr_lookup(lv, s["flow"])
-    O.ppm_memory_read(s["q"], s["k"], O.temporal_pe(SAMPLE_T, C_QKV), s["v"], s["mf"], s["sim"], s["strive"],
-                      s["unc"], 0.5)
+    strive = s["strive"].clone()
+    for _ in range(SAMPLE_ITERS):
+        O.corr_lookup(lv, s["flow"])
+        O.ppm_memory_read(s["q"], s["k"], O.temporal_pe(SAMPLE_T, C_QKV), s["v"], s["mf"], s["sim"], strive,
+                          s["unc"], 0.5)
     return time.perf_counter() - t0
 
 
 def cpu_frames_per_s(seconds_per_sample: float) -> float:
-    f_sample = attention_flops(SAMPLE_T, (PAD_H // SAMPLE_DS) * (PAD_W // SAMPLE_DS))
+    f_sample = SAMPLE_ITERS * attention_flops(SAMPLE_T, (PAD_H // SAMPLE_DS) * (PAD_W // SAMPLE_DS))
     return CLIP_FRAMES / (seconds_per_sample * clip_attention_flops() / f_sample)
 
 
@@ -352,10 +354,10 @@ def main():
         ms4 = time_kernel(lambda: P.convex_upsample(x["flow_a"], up_mask))
         b4 = T4 * h4 * w4 * (144.0 * 2 + 8 + 128)
         del up_mask
-        for name, ms, byts, traffic in (("corr_build_kernel (K1, 1/4-res, T=20, D=256, bf16 in/out)", ms1, b1, 2.61e9),
-                                        ("corr_lookup_l0_kernel (K2b, 1/4-res, T=20, 4 levels from one level-0 span, r=4)", ms2, b2, 4.69e8),
-                                        ("convex_upsample_kernel (K4, SURVEY 8f glue op, 1/4-res, T=20, bf16 mask; "
-                                         "not part of the timed step)", ms4, b4, None)):
+        for name, ms, byts, traffic in (("corr_build_kernel (K1, 1/4-res, T=20, D=256, bf16 in/out)", ms1, b1, 2.63e9),
+                                        ("corr_lookup_l0_kernel (K2b, 1/4-res, T=20, 4 levels from one level-0 span, r=4)", ms2, b2, 4.70e8),
+                                        ("convex_upsample_bf16x2_kernel (K4, SURVEY 8f glue op, 1/4-res, T=20, bf16 mask; "
+                                         "not part of the timed step)", ms4, b4, 4.71e8)):
             other.append({"kernel": name, "bound": "hbm", "achieved": byts / (ms * 1e-3) / 1e9, "peak": hbm,
                           "unit": "GB/s", "frac": byts / (ms * 1e-3) / 1e9 / hbm, "algorithmic_bytes": byts,
                           "traffic": traffic, "avg_launch_ms": ms,
@@ -403,7 +405,7 @@ def main():
             "clocks": clocks,
             "roofline": {"kernel": "ppm_attend3_kernel (1/4-res level, T=20, hw=58880, K=5)", "bound": "tensor",
                          "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
-                         "peak_source": "bf16_tflops_sustained, " + pk_src, "traffic": 1.65e10,
+                         "peak_source": "bf16_tflops_sustained, " + pk_src, "traffic": 2.09e10,
                          "flops_per_launch": fl, "avg_launch_ms": avg, "launches_timed": len(att_ms),
                          "share_of_step": sum(att_ms) / args.steps / ms_step},
             "attention_tflops_whole_step": clip_attention_flops() / (ms_step * 1e-3) / 1e12,

@@ -177,3 +177,28 @@ def test_lookup_from_level0_equals_generic_lookup(P, shape):
         assert torch.equal(got, want), (shape, lo, hi, float((got - want).abs().max()))
     blk = P.CorrBlock1D(f1, f2)
     assert torch.equal(blk(flow.cuda()), P.lookup(blk.corr_pyramid, flow.cuda(), W2=W2))
+
+
+@pytest.mark.parametrize("shape", [(1, 256, 1, 320, 320), (2, 128, 75, 320, 320), (1, 256, 3, 288, 320), (1, 64, 2, 130, 272),
+                                   (2, 192, 2, 320, 320)])
+@pytest.mark.parametrize("out_dtype", [torch.bfloat16, torch.float32])
+def test_build_cluster_path_all_rows(P, shape, out_dtype):
+    """Rows with exactly two N tiles (256 < W2 <= 512) and several M tiles are built by 2-CTA clusters: CTA rank =
+    N tile, F1 tiles multicast to both CTAs.  Every output row of every level is checked (1 row = 1 cluster, 150 rows = more rows than
+    co-resident clusters, partial M tiles, W1 != W2, a D that is not a multiple of the 64-channel stage)."""
+    B, D, H, W1, W2 = shape
+    g = torch.Generator(device="cuda").manual_seed(D + H + W1)
+    f1 = torch.randn(B, D, H, W1, generator=g, device="cuda").bfloat16()
+    f2 = torch.randn(B, D, H, W2, generator=g, device="cuda").bfloat16()
+    lv = P.build_pyramid(f1, f2, 4, out_dtype=out_dtype)
+    want = torch.einsum("bdhi,bdhj->bhij", f1.float(), f2.float()).reshape(B * H * W1, W2) / float(D) ** 0.5
+    for l in range(5):
+        got = lv[l].reshape(B * H * W1, W2 >> l).float()
+        assert bool(torch.isfinite(got).all()), l
+        tol = 1e-5 if out_dtype == torch.float32 else 5e-3          # fp32 out: accumulation order only; bf16 out: cascaded bf16 rounding
+        assert rel(got, want) <= tol, (l, rel(got, want))
+        # per-tile check: no (M tile, N half) may be off (a wrong descriptor shows up in one CTA rank only)
+        for n_half in range(2):
+            c0, c1 = (n_half * (W2 >> l)) // 2, ((n_half + 1) * (W2 >> l)) // 2
+            assert rel(got[:, c0:c1], want[:, c0:c1]) <= tol, (l, n_half)
+        want = (want[:, 0:2 * (want.shape[1] // 2):2] + want[:, 1:2 * (want.shape[1] // 2):2]) * 0.5
