@@ -320,7 +320,7 @@ def main():
         with torch.cuda.stream(side):
             fn()
             graph = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(graph, stream=side):
+            with torch.cuda.graph(graph, stream=side, capture_error_mode="thread_local"):   # NCCL watchdog thread may poll events
                 for _ in range(reps):
                     fn()
         torch.cuda.synchronize()
@@ -412,7 +412,7 @@ def main():
             "roofline_other_kernels": other,
             "same_box_reference_attention": same_box,
         }
-        if not args.no_cpu_baseline:
+        if not args.no_cpu_baseline and world == 1:           # the CPU arm is timed on rank 0 at N = 1 only
             cores = os.cpu_count() or 1
             torch.set_num_threads(cores)
             s = make_cpu_sample()
