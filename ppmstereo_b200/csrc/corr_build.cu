@@ -441,7 +441,10 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
       }
       bool released = false;
       uint8_t* const wstg = stage0 + (warp - 2) * kCbWarpStage;   // this warp's private staging box
-      for (int u = hsel; u < n_units && !(p.ablate & 8); u += 2)
+      // a warp whose 32 rows all lie past W1 (the partial last M tile) has nothing to store: it only hands the
+      // accumulator back
+      const bool warp_has_rows = m0 + q * 32 < p.W1;
+      for (int u = hsel; u < n_units && warp_has_rows && !(p.ablate & 8); u += 2)
       for (int cc = 2 * u; cc < 2 * u + 2 && cc < n_chunks; ++cc) {
         uint32_t raw[32];
         tmem_ld_x32(acc + cc * 32, raw);
