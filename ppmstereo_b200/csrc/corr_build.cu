@@ -58,6 +58,7 @@ struct CorrBuildParams {
   int D, H, W1, W2, NT, n_ntiles, n_mtiles;
   long long n_tiles, n_items;        // n_items = image rows x N tiles (resident mode)
   float sqrt_d;
+  float rcp_sqrt_d;                  // RN(1 / sqrt_d)
   float inv_sqrt_d;                  // 1/sqrt(D) when that is exact (sqrt(D) a power of two), else 0
   uint32_t inv_bf16x2;               // the same as a (bf16, bf16) pair
   int vec_ok[kCbLevels];             // level rows allow the full-width vector store
@@ -463,15 +464,30 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
           continue;
         }
         if constexpr (sizeof(OutT) == 2) {
-          if (p.inv_sqrt_d != 0.f) {
-            // fast path: bf16 pyramid, exact power-of-two scale, packed bf16x2 arithmetic:
-            //   level 0   bf16(acc) * 2^-k            (F2FP pack, HMUL2.BF16 -- exact)
+          {
+            // bf16 pyramid: packed bf16x2 arithmetic
+            //   level 0   bf16(acc) * 2^-k            (F2FP pack, HMUL2.BF16 -- exact) when sqrt(D) is a power of two,
+            //             else bf16(bf16(acc) / sqrt(D)), the quotient correctly rounded in fp32 (D = 128: the reference's
+            //             bf16 / fp32-scalar division)
             //   level l   bf16(lo/2 + hi/2) per word  (2 PRMT + HMUL2 + HFMA2 per two outputs; one rounding,
             //             the same value as the reference's fp32 average rounded to bf16)
             uint32_t w[16];
-            #pragma unroll
-            for (int j = 0; j < 16; ++j)
-              w[j] = cb_mul_bf16x2(pack_bf16x2(__uint_as_float(raw[2 * j]), __uint_as_float(raw[2 * j + 1])), p.inv_bf16x2);
+            if (p.inv_sqrt_d != 0.f) {
+              #pragma unroll
+              for (int j = 0; j < 16; ++j)
+                w[j] = cb_mul_bf16x2(pack_bf16x2(__uint_as_float(raw[2 * j]), __uint_as_float(raw[2 * j + 1])), p.inv_bf16x2);
+            } else {
+              #pragma unroll
+              for (int j = 0; j < 16; ++j) {
+                const uint32_t pk = pack_bf16x2(__uint_as_float(raw[2 * j]), __uint_as_float(raw[2 * j + 1]));
+                // x / s as q = x*r, q += (x - q*s)*r with r = RN(1/s): the correctly rounded quotient (Markstein), 3 instructions
+                const float x0 = __uint_as_float(pk << 16), x1 = __uint_as_float(pk & 0xFFFF0000u);
+                float q0 = __fmul_rn(x0, p.rcp_sqrt_d), q1 = __fmul_rn(x1, p.rcp_sqrt_d);
+                q0 = __fmaf_rn(__fmaf_rn(-q0, p.sqrt_d, x0), p.rcp_sqrt_d, q0);
+                q1 = __fmaf_rn(__fmaf_rn(-q1, p.sqrt_d, x1), p.rcp_sqrt_d, q1);
+                w[j] = pack_bf16x2(q0, q1);
+              }
+            }
             #pragma unroll
             for (int l = 0; l < kCbLevels; ++l) {
               const int n = 32 >> l;
@@ -568,6 +584,7 @@ static int launch_corr_build(const void* f1, const void* f2, int B, int D, int H
   p.n_tiles = static_cast<long long>(B) * H * p.n_mtiles * p.n_ntiles;
   p.NT = (((W2 + p.n_ntiles - 1) / p.n_ntiles) + 31) / 32 * 32;
   p.sqrt_d = sqrtf(static_cast<float>(D));
+  p.rcp_sqrt_d = 1.f / p.sqrt_d;
   {
     int e = 0;
     const float mant = frexpf(p.sqrt_d, &e);
@@ -604,12 +621,12 @@ static int launch_corr_build(const void* f1, const void* f2, int B, int D, int H
     int rc = make_tensor_map(&m2, dt, 4, f2, dims, str, box, Tr::kTmaSwizzle);
     if (rc) return rc;
   }
-  // Output path: level 0 of a bf16 pyramid with an exact scale leaves through TMA stores, one [32 rows][128 B] box
+  // Output path: level 0 of a bf16 pyramid leaves through TMA stores, one [32 rows][128 B] box
   // per epilogue warp and pair of chunks, from that warp's private staging; needs a 16-byte row pitch in global memory.
   CbStoreMaps om{};
   p.tma_out = 0;
   int stage_bytes = 0;
-  if (sizeof(OutT) == 2 && p.inv_sqrt_d != 0.f && !getenv("PPM_CB_NOTMA")) {
+  if (sizeof(OutT) == 2 && !getenv("PPM_CB_NOTMA")) {
     bool ok = ((static_cast<size_t>(W2) * 2) % 16 == 0) && (reinterpret_cast<uintptr_t>(levels[0]) % 16 == 0);
     if (ok) {
       const uint64_t dims[3] = {(uint64_t)W2, (uint64_t)W1, (uint64_t)B * H};
