@@ -524,9 +524,9 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
                 bulk_commit();
               }
             }
-            continue;
           }
-        }
+        } else {
+        // fp32 pyramid (generic epilogue): unpacked arithmetic, element / vector stores from registers
         float v[32];
         if (p.inv_sqrt_d != 0.f) {                  // sqrt(D) is a power of two: multiplying is exact
           #pragma unroll
@@ -551,6 +551,7 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
             OutT* dst = static_cast<OutT*>(p.level[l]) + row * Wl + col0;
             cb_store_row<OutT>(dst, v, n, Wl - col0, p.vec_ok[l] != 0);
           }
+        }
         }
       }
       if (!released) {                              // (a warp without a chunk in this tile, or the ablation paths)
