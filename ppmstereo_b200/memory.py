@@ -68,7 +68,8 @@ class PPMMemory:
                                            ctypes.byref(vb)), "ppm_pack_bytes")
         self.q_packed = torch.empty(qb.value // 2, dtype=torch.bfloat16, device=dev)
         self.k_packed = torch.empty(kb.value // 2, dtype=torch.bfloat16, device=dev)
-        self.v_packed = torch.empty(vb.value // 2, dtype=torch.bfloat16, device=dev)
+        self._v_buf = torch.empty(vb.value // 2, dtype=torch.bfloat16, device=dev)
+        self.v_packed = self._v_buf
         self.frame_score = torch.empty(b, 1, T, T, dtype=torch.float32, device=dev)
         self.picked = torch.empty(b, T, top_k, dtype=torch.int32, device=dev)
         self.score_norm = torch.empty(b, T, top_k, dtype=torch.float32, device=dev)
@@ -120,8 +121,19 @@ class PPMMemory:
         _lib.check(self.lib.ppm_pack_key(self.key.data_ptr(), _lib.dtype_code(self.key), *self.k_strides,
                                          self.pe.data_ptr(), self.picked.data_ptr(), self.score_norm.data_ptr(),
                                          b, T, self.top_k, hw, self.k_packed.data_ptr(), st), "ppm_pack_key")
-        _lib.check(self.lib.ppm_pack_value(value.data_ptr(), _lib.dtype_code(value), *vs, b, T, hw,
-                                           self.v_packed.data_ptr(), st), "ppm_pack_value")
+        # SURVEY 8f rank 1 (`to_v` -> V pack): the packed V layout (frame, 128, round_up(hw, 8)) bf16 IS the NCHW layout
+        # of a contiguous (b*T, 128, h, w) bf16 tensor when hw % 8 == 0 -- which is exactly what `aggregator.to_v` writes
+        # under autocast (reference ppmtereo_update.py:945-950, rearranged as a view at ppmstereo.py:498).  Then there is
+        # nothing to pack: the conv's output is the attention kernel's V operand (value must stay unmodified until
+        # aggregate() has been enqueued on the same stream).
+        frame_major = (vs[1] == hw and vs[2] == C * hw and (b == 1 or vs[0] == T * C * hw))
+        if value.dtype == torch.bfloat16 and hw % 8 == 0 and frame_major and value.data_ptr() % 16 == 0:
+            self.v_packed = value.permute(0, 2, 1, 3, 4).reshape(-1)          # a view, no copy
+            assert self.v_packed.data_ptr() == value.data_ptr()
+        else:
+            self.v_packed = self._v_buf
+            _lib.check(self.lib.ppm_pack_value(value.data_ptr(), _lib.dtype_code(value), *vs, b, T, hw,
+                                               self.v_packed.data_ptr(), st), "ppm_pack_value")
 
     def aggregate(self, motion_features: torch.Tensor, beta: torch.Tensor,
                   scale: Optional[float] = None, out: Optional[torch.Tensor] = None,

@@ -344,3 +344,25 @@ def test_tiny_and_odd_pixel_counts(P, shape):
     key past a tile): every masking path of the aggregation."""
     b, T, h, w = shape
     check_vs_oracle(P, make_case(b, T, h, w, seed=40 + h * w))
+
+
+@pytest.mark.parametrize("shape", [(1, 7, 8, 16), (2, 6, 12, 10), (1, 6, 5, 5)])
+def test_frame_major_bf16_value_is_used_in_place(P, shape):
+    """SURVEY 8f rank 1 (`to_v` -> V pack): a contiguous (b*T, 128, h, w) bf16 conv output, handed over as the
+    reference's rearranged (b, c, T, h, w) view, already has the packed V layout when hw % 8 == 0 -- no pack kernel runs,
+    the attention kernel reads the tensor in place, and the result is bit-identical to the packed path.  hw % 8 != 0
+    (5 x 5) must still go through the pack."""
+    b, T, h, w = shape
+    t = make_case(b, T, h, w, seed=5 + T)
+    conv_out = torch.randn(b * T, 128, h, w, generator=torch.Generator().manual_seed(9)).bfloat16().cuda()   # to_v output
+    view = conv_out.reshape(b, T, 128, h, w).permute(0, 2, 1, 3, 4)          # "(b t) c h w -> b c t h w"
+    beta = torch.tensor([0.5], device="cuda")
+    outs = []
+    for value in (view, view.contiguous()):                                   # in place / channel-major copy -> pack kernel
+        mem = P.PPMMemory(t["query"].cuda(), t["key"].cuda(), None, top_k=5)
+        mem.pick(t["sim"].cuda(), t["strive_before"].clone().cuda(), t["uncertainty"].cuda())
+        mem.pack_kv(value)
+        aliased = mem.v_packed.data_ptr() == conv_out.data_ptr()
+        outs.append((mem.aggregate(t["motion_features"].cuda(), beta), aliased))
+    assert outs[0][1] == ((h * w) % 8 == 0) and not outs[1][1]
+    assert torch.equal(outs[0][0], outs[1][0])
