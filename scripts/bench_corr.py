@@ -72,6 +72,9 @@ k2_bytes = B * H * W * 228.0
 best, med = timeit(lambda: P.lookup(blk.corr_pyramid, flow, W2=W), reps=20)
 print(f"K2  per-level lookup {B*H*W} px: best {best*1e3:.1f} us median {med*1e3:.1f} us -> "
       f"{k2_bytes/med/1e6:.0f} GB/s algorithmic ({k2_bytes/med/1e6/peak:.2f} of {peak:.0f})")
+best, med = graph_time(lambda: blk(flow), reps=20)
+print(f"K2b graph replay: best {best*1e3:.1f} us median {med*1e3:.1f} us -> {k2_bytes/med/1e6:.0f} GB/s algorithmic "
+      f"({k2_bytes/med/1e6/peak:.2f} of {peak:.0f})")
 best, med = timeit(lambda: blk(flow), reps=20)
 print(f"K2b lookup from level 0 {B*H*W} px: best {best*1e3:.1f} us median {med*1e3:.1f} us -> "
       f"{k2_bytes/med/1e6:.0f} GB/s algorithmic ({k2_bytes/med/1e6/peak:.2f} of {peak:.0f})")
