@@ -104,8 +104,6 @@ template <> struct CbTraits<float> {
   static constexpr CUtensorMapSwizzle kTmaSwizzle = CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B;
 };
 
-__device__ __forceinline__ float cb_round(float v, float) { return v; }
-__device__ __forceinline__ float cb_round(float v, __nv_bfloat16) { return bf16_round_f(v); }
 
 // packed bf16 helpers of the fast epilogue (HMUL2.BF16 / HFMA2.BF16)
 __device__ __forceinline__ uint32_t cb_mul_bf16x2(uint32_t a, uint32_t b) {
@@ -196,37 +194,21 @@ __device__ __forceinline__ void cb_store_words(__nv_bfloat16* dst, const uint32_
   }
 }
 
-// Store v[0..n) (n = 32, 16, 8, 4 or 2, compile-time at every call after unrolling) to dst[0..n),
-// only the first `valid` elements exist in the row.  vec: dst is aligned to min(16, n*sizeof) bytes.
-template <typename OutT>
-__device__ __forceinline__ void cb_store_row(OutT* dst, const float (&v)[32], int n, int valid, bool vec) {
+// fp32 pyramid: store v[0..n) (n = 32, 16, 8, 4 or 2, compile-time at every call after unrolling) to dst[0..n);
+// only the first `valid` elements exist in the row.  vec: dst is aligned to min(16, n*4) bytes.
+__device__ __forceinline__ void cb_store_row(float* dst, const float (&v)[32], int n, int valid, bool vec) {
   if (vec && valid >= n) {
-    if constexpr (sizeof(OutT) == 2) {
-      uint32_t pk[16];
+    if (n >= 4) {
       #pragma unroll
-      for (int j = 0; j < 16; ++j) pk[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
-      if (n >= 8) {
-        #pragma unroll
-        for (int j = 0; j < 4; ++j)
-          if (8 * j < n) reinterpret_cast<uint4*>(dst)[j] = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
-      } else if (n == 4) {
-        *reinterpret_cast<uint2*>(dst) = make_uint2(pk[0], pk[1]);
-      } else {
-        *reinterpret_cast<uint32_t*>(dst) = pk[0];
-      }
+      for (int j = 0; j < 8; ++j)
+        if (4 * j < n) reinterpret_cast<float4*>(dst)[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
     } else {
-      if (n >= 4) {
-        #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          if (4 * j < n) reinterpret_cast<float4*>(dst)[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-      } else {
-        *reinterpret_cast<float2*>(dst) = make_float2(v[0], v[1]);
-      }
+      *reinterpret_cast<float2*>(dst) = make_float2(v[0], v[1]);
     }
   } else {
     #pragma unroll
     for (int j = 0; j < 32; ++j)
-      if (j < n && j < valid) dst[j] = OutT(v[j]);
+      if (j < n && j < valid) dst[j] = v[j];
   }
 }
 
@@ -531,11 +513,11 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
         if (p.inv_sqrt_d != 0.f) {                  // sqrt(D) is a power of two: multiplying is exact
           #pragma unroll
           for (int j = 0; j < 32; ++j)
-            v[j] = cb_round(__fmul_rn(cb_round(__uint_as_float(raw[j]), OutT()), p.inv_sqrt_d), OutT());
+            v[j] = __fmul_rn(__uint_as_float(raw[j]), p.inv_sqrt_d);
         } else {
           #pragma unroll
           for (int j = 0; j < 32; ++j)
-            v[j] = cb_round(__fdiv_rn(cb_round(__uint_as_float(raw[j]), OutT()), p.sqrt_d), OutT());
+            v[j] = __fdiv_rn(__uint_as_float(raw[j]), p.sqrt_d);
         }
         #pragma unroll
         for (int l = 0; l < kCbLevels; ++l) {
@@ -543,13 +525,12 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
           if (l > 0) {
             #pragma unroll
             for (int j = 0; j < n; ++j)
-              v[j] = cb_round(__fmul_rn(__fadd_rn(v[2 * j], v[2 * j + 1]), 0.5f), OutT());
+              v[j] = __fmul_rn(__fadd_rn(v[2 * j], v[2 * j + 1]), 0.5f);
           }
           if (l <= p.n_levels && row_ok) {
             const int Wl = p.width[l];
             const int col0 = (n0 + cc * 32) >> l;
-            OutT* dst = static_cast<OutT*>(p.level[l]) + row * Wl + col0;
-            cb_store_row<OutT>(dst, v, n, Wl - col0, p.vec_ok[l] != 0);
+            cb_store_row(static_cast<float*>(p.level[l]) + row * Wl + col0, v, n, Wl - col0, p.vec_ok[l] != 0);
           }
         }
         }
