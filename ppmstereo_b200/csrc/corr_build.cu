@@ -61,6 +61,7 @@ struct CorrBuildParams {
   float rcp_sqrt_d;                  // RN(1 / sqrt_d)
   float inv_sqrt_d;                  // 1/sqrt(D) when that is exact (sqrt(D) a power of two), else 0
   uint32_t inv_bf16x2;               // the same as a (bf16, bf16) pair
+  int pair_vec[kCbLevels];           // levels 2-4: rows allow one aligned store per 64-column unit (bf16 pyramid)
   int vec_ok[kCbLevels];             // level rows allow the full-width vector store
   int res_b;                         // 1: the F2 tile of a work item stays in smem for all its M tiles
   int a_stages;                      // res_b: stages of the F1 ring
@@ -412,23 +413,28 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
       mbar_wait(&bar_acc_full[buf], static_cast<uint32_t>((it >> 1) & 1));
       tc_fence_after();
       const uint32_t acc = tmem_base + buf * kCbMaxN + (static_cast<uint32_t>(q * 32) << 16);
-      // A warp takes units of two adjacent chunks (one 128-byte-wide TMA store box per unit); the two warps of a
-      // lane quarter take alternate units, and the odd unit alternates between them from tile to tile.
+      // A warp takes units of two adjacent chunks whose first column is a multiple of 64 in the IMAGE row (global
+      // chunk index g = n0/32 + cc, unit = g >> 1), so that a unit is one 128-byte line of level 0 (one TMA store box),
+      // one 32-byte sector of level 2, 16 bytes of level 3 and 8 of level 4 whatever n0 is (n0 = 160: units {5}, {6,7},
+      // {8,9}).  The two warps of a lane quarter take alternate units and swap from tile to tile.
       const int hsel = (half ^ static_cast<int>(it & 1)) & 1;
-      const int n_units = (n_chunks + 1) >> 1;
+      const int g_first = n0 >> 5, g_last = g_first + n_chunks - 1;
+      const int u_first = g_first >> 1, u_last = g_last >> 1;
       int last_cc = -1;
-      {
-        int ul = n_units - 1;
-        if ((ul & 1) != hsel) --ul;
-        if (ul >= 0) last_cc = 2 * ul + 1 < n_chunks ? 2 * ul + 1 : n_chunks - 1;
-      }
+      for (int ug = u_last; ug >= u_first; --ug)
+        if (((ug - u_first) & 1) == hsel) { last_cc = (2 * ug + 1 < g_last ? 2 * ug + 1 : g_last) - g_first; break; }
       bool released = false;
       uint8_t* const wstg = stage0 + (warp - 2) * kCbWarpStage;   // this warp's private staging box
       // a warp whose 32 rows all lie past W1 (the partial last M tile) has nothing to store: it only hands the
       // accumulator back
       const bool warp_has_rows = m0 + q * 32 < p.W1;
-      for (int u = hsel; u < n_units && warp_has_rows && !(p.ablate & 8); u += 2)
-      for (int cc = 2 * u; cc < 2 * u + 2 && cc < n_chunks; ++cc) {
+      for (int ug = u_first + hsel; ug <= u_last && warp_has_rows && !(p.ablate & 8); ug += 2) {
+      const int ga = 2 * ug > g_first ? 2 * ug : g_first, gb = 2 * ug + 1 < g_last ? 2 * ug + 1 : g_last;
+      const bool single = ga == gb;                              // edge unit of one chunk: [32][64 B] box
+      const bool pair_full = !single && 64 * ug + 64 <= p.W2;    // levels 2-4 of the unit leave in one store each
+      uint32_t keep[7];                                          // levels 2 | 3 | 4 of the unit's first chunk
+      for (int g = ga; g <= gb; ++g) {
+        const int cc = g - g_first;
         uint32_t raw[32];
         tmem_ld_x32(acc + cc * 32, raw);
         tmem_ld_wait();
@@ -483,26 +489,46 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
               }
               if (p.ablate & 1) { if (w[0] == 0x12345678u && l == 4) *reinterpret_cast<uint32_t*>(p.level[0]) = w[0]; continue; }
               if (p.tma_out && l == 0) {                 // level 0: this thread's 64-byte row segment -> the warp's staging box
-                const bool single = (n_chunks & 1) && cc == n_chunks - 1;      // tail unit of one chunk: [32][64 B] box
-                if ((cc & 1) == 0) {                     // first chunk of the unit: the previous unit's store has read the box
+                if (g == ga) {                           // first chunk of the unit: the previous unit's store has read the box
                   if (lane == 0) bulk_wait_read<0>();
                   __syncwarp();
                 }
                 #pragma unroll
                 for (int j = 0; j < 4; ++j)
-                  *reinterpret_cast<uint4*>(wstg + (single ? cb_stage_off(lane, j, 64) : cb_stage_off(lane, (cc & 1) * 4 + j, 128))) =
+                  *reinterpret_cast<uint4*>(wstg + (single ? cb_stage_off(lane, j, 64) : cb_stage_off(lane, (g & 1) * 4 + j, 128))) =
                       make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
               } else if (l <= p.n_levels && row_ok) {
                 const int Wl = p.width[l];
-                const int col0 = (n0 + cc * 32) >> l;
-                cb_store_words(reinterpret_cast<__nv_bfloat16*>(p.level[l]) + row * Wl + col0, w, n, Wl - col0, p.vec_ok[l]);
+                if (l >= 2 && pair_full && p.pair_vec[l]) {
+                  // levels 2-4: the unit's two chunks are adjacent halves of one aligned 32 / 16 / 8-byte piece: keep
+                  // the first chunk's words and store once (every LSU request of this kernel touches 32 sectors, one
+                  // per lane; half-filled sectors made l1tex the busiest unit at 65 %)
+                  const int ko = l == 2 ? 0 : (l == 3 ? 4 : 6);
+                  if (g == ga) {
+                    #pragma unroll
+                    for (int j = 0; j < n / 2; ++j) keep[ko + j] = w[j];
+                  } else {
+                    __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.level[l]) + row * Wl + ((64 * ug) >> l);
+                    if (l == 2) {
+                      const uint32_t w8[8] = {keep[0], keep[1], keep[2], keep[3], w[0], w[1], w[2], w[3]};
+                      cb_st256(dst, w8);
+                    } else if (l == 3) {
+                      *reinterpret_cast<uint4*>(dst) = make_uint4(keep[4], keep[5], w[0], w[1]);
+                    } else {
+                      *reinterpret_cast<uint2*>(dst) = make_uint2(keep[6], w[0]);
+                    }
+                  }
+                } else {
+                  const int col0 = (n0 + cc * 32) >> l;
+                  cb_store_words(reinterpret_cast<__nv_bfloat16*>(p.level[l]) + row * Wl + col0, w, n, Wl - col0, p.vec_ok[l]);
+                }
               }
             }
-            if (p.tma_out && !(p.ablate & 3) && ((cc & 1) || cc == n_chunks - 1)) {     // unit complete
+            if (p.tma_out && !(p.ablate & 3) && g == gb) {     // unit complete
               fence_proxy_async_smem();                 // staged rows -> visible to the TMA engine
               __syncwarp();
               if (lane == 0) {                          // rows past W1 and columns past W2 are clipped by the TMA unit
-                tma_store_3d(&omap.m[cc & 1 ? 0 : 1], wstg, n0 + (cc & ~1) * 32, m0 + q * 32, bh);
+                tma_store_3d(&omap.m[single ? 1 : 0], wstg, single ? 32 * g : 64 * ug, m0 + q * 32, bh);
                 bulk_commit();
               }
             }
@@ -534,6 +560,7 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
           }
         }
         }
+      }
       }
       if (!released) {                              // (a warp without a chunk in this tile, or the ablation paths)
         tc_fence_before();
@@ -584,6 +611,9 @@ static int launch_corr_build(const void* f1, const void* f2, int B, int D, int H
     if (p.vec_ok[l] && chunk >= 32 && (static_cast<size_t>(W2 >> l) * esz) % 32 == 0 &&
         reinterpret_cast<uintptr_t>(levels[l]) % 32 == 0)
       p.vec_ok[l] = 2;                               // 256-bit stores (bf16 fast path)
+    const size_t unit = 2 * chunk;                   // bytes of a 64-column unit at this level
+    p.pair_vec[l] = (esz == 2 && l >= 2 && (static_cast<size_t>(W2 >> l) * esz) % unit == 0 &&
+                     reinterpret_cast<uintptr_t>(levels[l]) % unit == 0) ? 1 : 0;
   }
   const CUtensorMapDataType dt = sizeof(ElemT) == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
                                                     : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
