@@ -16,11 +16,12 @@
 //   warps 2-9 epilogue, every warp on its own: tcgen05.ld (one output row per thread, 32 columns at a
 //             time), hand the accumulator back right after the warp's last load, scale by 1/sqrt(D), form
 //             levels 1..4 by pair-averaging IN REGISTERS (a thread owns whole row segments, so pooling
-//             along j needs no communication).  Level 0 leaves through the warp's private, double-buffered
-//             and swizzled [32 rows][64 B] staging box and one TMA store per chunk (a thread's own 64-byte
-//             row segments written with LSU stores touch 32 different 128-byte lines per instruction);
-//             levels 1-4 (32 ... 4 bytes per thread and chunk) go straight from registers.  No CTA-wide
-//             barrier anywhere in the epilogue.
+//             along j needs no communication).  A warp takes units of two adjacent chunks aligned to 64 columns
+//             of the image row: level 0 of a unit goes into the warp's private, XOR-swizzled [32 rows][128 B]
+//             staging box and leaves through one TMA store (a thread's own row segments written with LSU stores
+//             touch 32 different lines per instruction); level 1 (one 32-byte sector per thread and chunk) and
+//             levels 2-4 (one aligned 32 / 16 / 8-byte piece per thread and UNIT) go straight from registers.
+//             No CTA-wide barrier anywhere in the epilogue.
 // Persistent: one CTA per SM loops over work items; the smem ring runs on across items and the
 // accumulator is double-buffered in TMEM (2 x 256 columns), so the TMA loads and MMAs of tile i+1
 // overlap the epilogue of tile i.  When an image row has several M tiles, a work item is (image
@@ -29,7 +30,7 @@
 // and every F1 tile is fetched once and multicast to both CTAs (each CTA issues half of the boxes; the
 // ring's empty barriers take one tcgen05.commit arrival from each CTA).
 // Measured at the 720p 1/4-res shape (2.67 GB algorithmic, 0.41 ms at the HBM copy peak), CUDA-graph
-// replay: 0.50 ms (0.81); history 2.49 -> 0.84 -> 0.60 -> 0.58 -> 0.50.  Ablations (PPM_CB_ABLATE bit mask,
+// replay: 0.465 ms (0.88); history 2.49 -> 0.84 -> 0.60 -> 0.58 -> 0.50 -> 0.465.  Ablations (PPM_CB_ABLATE bit mask,
 // same box): MMA + barrier skeleton 0.25 ms, + loads 0.31, + epilogue arithmetic (no stores) 0.27,
 // + stores (no loads) 0.48 -- the store side (TMA box rows + scattered LSU lines) is what is left.
 // The volume is written exactly once and never re-read: 1.9375 x W1 x W2 elements per row.
