@@ -1,4 +1,5 @@
 // Experiment: DRAM/L2 traffic of random one-sector gathers under different load flavours.
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 scripts/exp/gather_exp.cu -o scripts/exp/gather_exp
 #include <cstdio>
 #include <cstdint>
 #include <cuda_runtime.h>
