@@ -202,3 +202,23 @@ def test_build_cluster_path_all_rows(P, shape, out_dtype):
             c0, c1 = (n_half * (W2 >> l)) // 2, ((n_half + 1) * (W2 >> l)) // 2
             assert rel(got[:, c0:c1], want[:, c0:c1]) <= tol, (l, n_half)
         want = (want[:, 0:2 * (want.shape[1] // 2):2] + want[:, 1:2 * (want.shape[1] // 2):2]) * 0.5
+
+
+@pytest.mark.parametrize("shape", [(1, 256, 3, 320, 320), (2, 128, 40, 320, 288)])
+@pytest.mark.parametrize("out_dtype", [torch.float32, torch.bfloat16])
+def test_build_cluster_path_tf32_inputs(P, shape, out_dtype):
+    """fp32 feature maps (kind::tf32, four 32-pixel boxes per F1 stage, two multicast by each CTA of the cluster):
+    level 0 of both N halves vs the fp64 contraction.  TF32 operands vs fp32: <= 1e-3 relative (measured 7.7e-4);
+    a bf16 pyramid adds its own rounding (measured 1.8e-3 .. 2.5e-3)."""
+    B, D, H, W1, W2 = shape
+    g = torch.Generator(device="cuda").manual_seed(1)
+    f1 = torch.randn(B, D, H, W1, generator=g, device="cuda")
+    f2 = torch.randn(B, D, H, W2, generator=g, device="cuda")
+    lv = P.build_pyramid(f1, f2, 4, out_dtype=out_dtype)
+    want = torch.einsum("bdhi,bdhj->bhij", f1.double(), f2.double()).reshape(B * H * W1, W2) / float(D) ** 0.5
+    got = lv[0].reshape(B * H * W1, W2).double()
+    tol = 1e-3 if out_dtype == torch.float32 else 5e-3
+    for a, b in ((0, W2 // 2), (W2 // 2, W2)):
+        assert rel(got[:, a:b], want[:, a:b]) <= tol, (a, b, rel(got[:, a:b], want[:, a:b]))
+    for l in range(5):
+        assert bool(torch.isfinite(lv[l].float()).all()), l
