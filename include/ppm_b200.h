@@ -46,7 +46,9 @@ const char* ppm_last_error(void);
  * kind::tf32.  With out_dtype == PPM_BF16 the result is rounded the way the reference's
  * autocast path rounds it (accumulator -> bf16, / sqrt(D) -> bf16, every level -> bf16).
  * Requires ld % 8 == 0 for bf16 (4 for f32) and 16-byte aligned fmaps (TMA row pitch),
- * W2 >> n_levels >= 1, n_levels <= 4.  `levels` is a HOST array of device pointers. */
+ * W2 >> n_levels >= 1, n_levels <= 4.  `levels` is a HOST array of device pointers.
+ * (The PPM_CB_* environment variables read by this entry point select timing ablations for
+ * profiles/r01_k1_ablation.md; they are debugging aids, not part of the ABI, and produce garbage results.) */
 int ppm_corr_build(const void* fmap1, const void* fmap2, int in_dtype, int B, int D, int H,
                    int W1, int W2, int ld1, int ld2, void* const* levels, int n_levels,
                    int out_dtype, void* stream);
