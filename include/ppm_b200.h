@@ -21,6 +21,8 @@ extern "C" {
 #endif
 
 #define PPM_ABI_VERSION 1
+/* The library is built with -fvisibility=hidden: exactly the functions declared here are exported. */
+#define PPM_API __attribute__((visibility("default")))
 
 enum ppm_dtype { PPM_F32 = 0, PPM_BF16 = 1 };
 
@@ -31,8 +33,8 @@ enum ppm_status {
   PPM_ERR_UNSUPPORTED = 3  /* valid request the kernels do not cover (e.g. T > 64) */
 };
 
-int ppm_abi_version(void);
-const char* ppm_last_error(void);
+PPM_API int ppm_abi_version(void);
+PPM_API const char* ppm_last_error(void);
 
 /* ---------------------------------------------------------------------------------------
  * K1  correlation pyramid build.
@@ -47,9 +49,9 @@ const char* ppm_last_error(void);
  * autocast path rounds it (accumulator -> bf16, / sqrt(D) -> bf16, every level -> bf16).
  * Requires ld % 8 == 0 for bf16 (4 for f32) and 16-byte aligned fmaps (TMA row pitch),
  * W2 >> n_levels >= 1, n_levels <= 4.  `levels` is a HOST array of device pointers.
- * (The PPM_CB_* environment variables read by this entry point select timing ablations for
- * profiles/r01_k1_ablation.md; they are debugging aids, not part of the ABI, and produce garbage results.) */
-int ppm_corr_build(const void* fmap1, const void* fmap2, int in_dtype, int B, int D, int H,
+ * (The library reads no environment variable.  The PPM_CB_* timing ablations behind profiles/r01_k1_ablation.md
+ * exist only in an experiments build compiled with -DPPM_EXPERIMENTS; see scripts/.) */
+PPM_API int ppm_corr_build(const void* fmap1, const void* fmap2, int in_dtype, int B, int D, int H,
                    int W1, int W2, int ld1, int ld2, void* const* levels, int n_levels,
                    int out_dtype, void* stream);
 
@@ -61,7 +63,7 @@ int ppm_corr_build(const void* fmap1, const void* fmap2, int in_dtype, int B, in
  * levels[l], l = 0..n_levels-1 as written by ppm_corr_build (dtype vol_dtype); `levels` is a
  * HOST array of device pointers.  flow (B,2,H,W1) fp32 (only channel 0 is read).
  * out (B, n_levels*(2r+1), H, W1) fp32.  radius <= 4, n_levels <= 4. */
-int ppm_corr_lookup(const void* const* levels, int vol_dtype, const float* flow, int B, int H,
+PPM_API int ppm_corr_lookup(const void* const* levels, int vol_dtype, const float* flow, int B, int H,
                     int W1, int W2, int radius, int n_levels, float* out, void* stream);
 
 /* K2b  the same lookup (radius 4, 4 levels, bf16 volume) sampled from LEVEL 0 ONLY: the 80-element level-0 span
@@ -69,7 +71,7 @@ int ppm_corr_lookup(const void* const* levels, int vol_dtype, const float* flow,
  * registers with ppm_corr_build's arithmetic, so the result equals ppm_corr_lookup on a pyramid written by
  * ppm_corr_build bit for bit while touching ~2.2 instead of ~4.6 128-byte lines per pixel (B200 fetches a
  * whole line for every random sector).  level0 (B*H*W1, W2) bf16, 32-byte aligned, W2 % 8 == 0. */
-int ppm_corr_lookup_l0(const void* level0, const float* flow, int B, int H, int W1, int W2, float* out,
+PPM_API int ppm_corr_lookup_l0(const void* level0, const float* flow, int B, int H, int W1, int W2, float* out,
                        void* stream);
 
 /* ---------------------------------------------------------------------------------------
@@ -78,8 +80,11 @@ int ppm_corr_lookup_l0(const void* level0, const float* flow, int B, int H, int 
  *   x_[b,t,:]  = mean over the 128 channels of AdaptiveMaxPool2d((h/4, w/4))(x[b,:,t])   x = query, key
  *   sim[b,i,j] = cos(k_[b,i], q_[b,j]) with F.cosine_similarity's eps = 1e-8 clamp on each norm
  * query, key indexed src[b*sb + c*sc + t*st + y*w + x], dtype `dtype`; pooled_ws: 2*b*T*(h/4)*(w/4) fp32
- * scratch; sim (b,T,T) fp32.  fp32 arithmetic, deterministic reduction order. */
-int ppm_qk_similarity(const void* query, const void* key, int dtype, int64_t sb, int64_t sc, int64_t st,
+ * scratch; sim (b,T,T) fp32.  fp32 arithmetic, deterministic reduction order.
+ * dtype rule: dtype == PPM_BF16 is the reference's autocast regime (ppmstereo.py:617), where `.mean(dim=1)` of the
+ * bf16 pooled tensor returns bf16 (mean is not an autocast-fp32 op) and only F.cosine_similarity up-casts: the
+ * pooled channel mean x_ is rounded to bf16 (fp32 accumulation, one rounding).  PPM_F32: nothing is rounded. */
+PPM_API int ppm_qk_similarity(const void* query, const void* key, int dtype, int64_t sb, int64_t sc, int64_t st,
                       int b, int T, int h, int w, float* pooled_ws, float* sim, void* stream);
 
 /* ---------------------------------------------------------------------------------------
@@ -92,8 +97,11 @@ int ppm_qk_similarity(const void* query, const void* key, int dtype, int64_t sb,
  *   score_norm[b,i,n] = score[b,i,picked n] / mean_{b,n} score[b,i,picked n]
  * sim, strive, frame_score: (b,T,T) fp32; uncertainty (b*T, hw) dtype unc_dtype;
  * picked (b,T,top_k) int32; score_norm (b,T,top_k) fp32; mask (b,T,T) uint8 (may be NULL).
- * conf_ws: (b*T) fp32 scratch.  T <= 64, top_k <= 16. */
-int ppm_qam_pick(const float* sim, float* strive, const void* uncertainty, int unc_dtype, int b,
+ * conf_ws: (b*T) fp32 scratch.  T <= 64, top_k <= 16.
+ * dtype rule: unc_dtype == PPM_BF16 is the reference's autocast regime, where `uncertainty_score...mean(-1)`
+ * (ppmstereo.py:506) returns a bf16 tensor: conf = bf16(sum_fp32 * (1/hw)), promoted back to fp32 by the add at
+ * :507.  PPM_F32: conf = sum * (1/hw), unrounded.  Means are sum * (1/n), as ATen's CUDA mean computes them. */
+PPM_API int ppm_qam_pick(const float* sim, float* strive, const void* uncertainty, int unc_dtype, int b,
                  int T, int hw, int top_k, float* frame_score, int32_t* picked,
                  float* score_norm, uint8_t* mask, float* conf_ws, void* stream);
 
@@ -106,12 +114,12 @@ int ppm_qam_pick(const float* sim, float* strive, const void* uncertainty, int u
  *                    j = picked[b,i,n]; rows with j < 0 are zero-filled             (:524-548)
  *   ppm_pack_value : V[(b*T+t), c, p_pad]        = bf16(value), p_pad = round_up(hw, 8) (:529)
  * pe: (T,128) fp32. */
-int ppm_pack_query(const void* query, int src_dtype, int64_t sb, int64_t sc, int64_t st,
+PPM_API int ppm_pack_query(const void* query, int src_dtype, int64_t sb, int64_t sc, int64_t st,
                    const float* pe, int b, int T, int hw, void* q_out, void* stream);
-int ppm_pack_key(const void* key, int src_dtype, int64_t sb, int64_t sc, int64_t st,
+PPM_API int ppm_pack_key(const void* key, int src_dtype, int64_t sb, int64_t sc, int64_t st,
                  const float* pe, const int32_t* picked, const float* score_norm, int b, int T,
                  int Kp, int hw, void* k_out, void* stream);
-int ppm_pack_value(const void* value, int src_dtype, int64_t sb, int64_t sc, int64_t st, int b,
+PPM_API int ppm_pack_value(const void* value, int src_dtype, int64_t sb, int64_t sc, int64_t st, int b,
                    int T, int hw, void* v_out, void* stream);
 
 /* ---------------------------------------------------------------------------------------
@@ -122,7 +130,7 @@ int ppm_pack_value(const void* value, int src_dtype, int64_t sb, int64_t sc, int
  * Q, K, V as written by the pack calls; mf dtype mf_dtype; beta: device fp32 scalar;
  * out (b*T, 128, hw) fp32.  bf16 operands, fp32 scores/softmax, P rounded to bf16 before
  * P.V (FlashAttention-2 rounding), tcgen05 MMAs with TMEM accumulators. */
-int ppm_memory_attend(const void* Q, const void* K, const void* V, const int32_t* picked,
+PPM_API int ppm_memory_attend(const void* Q, const void* K, const void* V, const int32_t* picked,
                       const void* mf, int mf_dtype, int64_t mb, int64_t mc, int64_t mt,
                       const float* beta, float scale, int b, int T, int Kp, int hw, float* out,
                       void* stream);
@@ -132,7 +140,7 @@ int ppm_memory_attend(const void* Q, const void* K, const void* V, const int32_t
  * out keep the full-frame layouts above, keys and values of ALL hw pixels take part.  A rank that
  * owns a band of image rows calls this after gathering the value bands of the other ranks.
  * ppm_memory_attend == ppm_memory_attend_band(..., 0, hw, ...). */
-int ppm_memory_attend_band(const void* Q, const void* K, const void* V, const int32_t* picked,
+PPM_API int ppm_memory_attend_band(const void* Q, const void* K, const void* V, const int32_t* picked,
                            const void* mf, int mf_dtype, int64_t mb, int64_t mc, int64_t mt,
                            const float* beta, float scale, int b, int T, int Kp, int hw, int q_begin,
                            int q_count, float* out, void* stream);
@@ -145,11 +153,11 @@ int ppm_memory_attend_band(const void* Q, const void* K, const void* V, const in
  * flow (N,2,H,W) fp32; mask (N, 9*rate*rate, H, W) dtype mask_dtype (for PPM_BF16 the softmax result is
  * rounded to bf16 before the product, as torch.softmax does for a bf16 input); out (N,2,rate*H,rate*W)
  * fp32, 16-byte aligned.  rate must be 4. */
-int ppm_convex_upsample(const float* flow, const void* mask, int mask_dtype, int N, int H, int W,
+PPM_API int ppm_convex_upsample(const float* flow, const void* mask, int mask_dtype, int N, int H, int W,
                         int rate, float* out, void* stream);
 
 /* Bytes of the packed operands for (b, T, Kp, hw): q, k, v in that order. */
-int ppm_pack_bytes(int b, int T, int Kp, int hw, size_t* q_bytes, size_t* k_bytes,
+PPM_API int ppm_pack_bytes(int b, int T, int Kp, int hw, size_t* q_bytes, size_t* k_bytes,
                    size_t* v_bytes);
 
 #ifdef __cplusplus

@@ -176,6 +176,12 @@ def qk_similarity(query: torch.Tensor, key: torch.Tensor) -> torch.Tensor:
     PPMStereo.compute_qk_similarity (models/core/ppmstereo.py:397-423), with
     F.cosine_similarity's eps = 1e-8 clamp on each norm.
     query, key: (b, c, T, h, w).  Returns (b, 1, T, T) fp32.
+
+    dtype rule (the reference's GPU path runs under bf16 autocast, ppmstereo.py:617): q/k come out of the
+    ``to_qk`` conv as bf16; ``AdaptiveMaxPool2d`` keeps bf16 (exact); ``.mean(dim=1)`` (:409) is NOT an
+    autocast-fp32 op, so it returns a bf16 tensor (fp32 accumulation, ONE rounding of the mean);
+    ``F.cosine_similarity`` IS an autocast-fp32 op and up-casts those bf16 means.  So: for bf16 inputs the
+    pooled channel mean is rounded to bf16 here; for fp32 inputs nothing is rounded.
     """
     b, c, T, h, w = query.shape
     oh, ow = h // 4, w // 4
@@ -189,9 +195,15 @@ def qk_similarity(query: torch.Tensor, key: torch.Tensor) -> torch.Tensor:
                 cols.append(x[..., r0:r1, c0:c1].amax(dim=(-2, -1)))
             rows.append(torch.stack(cols, -1))
         p = torch.stack(rows, -2)                  # b,c,T,oh,ow
-        return p.mean(dim=1).reshape(b, T, oh * ow)
+        m = p.mean(dim=1)
+        if x_is_bf16:
+            m = bf16_round(m)                      # torch.mean of a bf16 tensor returns bf16 (:409)
+        return m.reshape(b, T, oh * ow)
 
-    q_, k_ = pooled(query), pooled(key)
+    x_is_bf16 = query.dtype == torch.bfloat16
+    q_ = pooled(query)
+    x_is_bf16 = key.dtype == torch.bfloat16
+    k_ = pooled(key)
     dots = torch.einsum("bin,bjn->bij", k_, q_)
     nk = k_.norm(dim=-1).clamp_min(1e-8)
     nq = q_.norm(dim=-1).clamp_min(1e-8)
@@ -204,10 +216,16 @@ def qam_frame_score(sim: torch.Tensor, strive: torch.Tensor,
     conf_j the mean over pixels of frame j's uncertainty map.
     Follows models/core/ppmstereo.py:501-507.
     sim, strive: (b,1,T,T); uncertainty: (b*T, 1, h, w).
+
+    dtype rule: under the reference's bf16 autocast ``uncertainty_score`` (conv -> sigmoid) is bf16 and
+    ``.mean(-1)`` (:506) returns a bf16-ROUNDED frame confidence (mean is not an autocast-fp32 op); the add at
+    :507 then promotes it back to fp32.  So a bf16 uncertainty map gives conf = bf16(mean); fp32 gives fp32.
     """
     b, _, T, _ = sim.shape
     penalty = torch.exp(-strive / (strive.sum(3, keepdim=True) + T))
     conf = uncertainty.float().reshape(b, 1, 1, T, -1).mean(-1)
+    if uncertainty.dtype == torch.bfloat16:
+        conf = bf16_round(conf)
     return penalty * sim + conf
 
 
@@ -314,13 +332,11 @@ def ppm_memory_read(query, key, pe, value, motion_features, sim, strive, uncerta
 # ---------------------------------------------------------------------------------------------
 def convex_upsample(flow: torch.Tensor, mask: torch.Tensor, rate: int = 4) -> torch.Tensor:
     """out[n,c,rate*y+i,rate*x+j] = sum_k softmax_k(mask[n,(k*rate+i)*rate+j,y,x]) * rate*flow[n,c,y+k//3-1,x+k%3-1],
-    zero outside the image.  flow (N,2,H,W); mask (N,9*rate^2,H,W) fp32 or bf16 -- torch.softmax returns the
-    input dtype, so for a bf16 mask the weights are bf16-rounded before the fp32 product (:188, :193).
-    The rounding restated here is torch's CUDA softmax (fp32 math, ONE rounding of the result), which is what
-    the reference runs; torch's CPU softmax rounds a bf16 input twice (exp stored as bf16, then the
-    normalised value), so 0.7 % of its weights differ by one bf16 ulp from this function."""
+    zero outside the image.  flow (N,2,H,W); mask (N,9*rate^2,H,W) fp32 or bf16.  A bf16 mask only ever reaches
+    the reference inside ``with autocast(...)`` (ppmstereo.py:617), and torch.softmax is on autocast's fp32 list:
+    the mask is up-cast, the weights are fp32 and are NOT rounded to bf16 (:188, :193)."""
     N, _, H, W = flow.shape
-    w = torch.softmax(mask.float().reshape(N, 9, rate, rate, H, W), dim=1).to(mask.dtype).float()
+    w = torch.softmax(mask.float().reshape(N, 9, rate, rate, H, W), dim=1)
     fp = torch.nn.functional.pad(rate * flow.float(), (1, 1, 1, 1))              # zero padding (:190)
     out = torch.zeros(N, 2, rate, rate, H, W)
     for k in range(9):

@@ -9,9 +9,9 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libppm_sm100.so")
-SOURCES = ["api.cu", "corr_build.cu", "corr_lookup.cu", "ppm_prep.cu", "ppm_attend.cu", "ppm_attend2.cu", "ppm_attend3.cu", "convex_upsample.cu", "qk_similarity.cu"]
+SOURCES = ["api.cu", "corr_build.cu", "corr_lookup.cu", "ppm_prep.cu", "ppm_attend3.cu", "convex_upsample.cu", "qk_similarity.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",
-              "-Xcompiler", "-fPIC", "--use_fast_math=false"]
+              "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden", "--use_fast_math=false"]
 
 
 def _nvcc() -> str:
@@ -37,7 +37,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     objdir = os.path.join(HERE, "build")
     os.makedirs(objdir, exist_ok=True)
     flags = [f for f in NVCC_FLAGS if not f.startswith("--use_fast_math")]
-    flags += os.environ.get("PPM_EXTRA_NVCC_FLAGS", "").split()      # e.g. -DPPM_A3_EXPERIMENTS (scripts/ only)
+    flags += os.environ.get("PPM_EXTRA_NVCC_FLAGS", "").split()      # e.g. -DPPM_EXPERIMENTS (scripts/ only)
     procs = []
     for src in SOURCES:
         obj = os.path.join(objdir, src.replace(".cu", ".o"))

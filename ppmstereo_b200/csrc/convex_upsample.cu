@@ -8,8 +8,9 @@
 // HBM-bound: 9*r*r*e_mask + 2*r*r*4 (+ 8 for the flow) bytes per coarse pixel.
 //   thread = one coarse pixel (n, y, x); lanes = consecutive x, so each of the 9*r*r mask channels is read with
 //   a full-width coalesced request and every store instruction writes r*4 contiguous bytes per lane;
-//   per fine row i: softmax of the r columns' 9 taps in fp32 (rounded to bf16 when the mask is bf16 -- that is
-//   what torch.softmax returns for a bf16 input), then the two flow channels.
+//   per fine row i: softmax of the r columns' 9 taps in fp32, then the two flow channels.  A bf16 mask is a STORAGE
+//   type only: the reference reaches this op under torch.autocast (ppmstereo.py:617), where torch.softmax is an
+//   autocast-to-fp32 op -- the weights are fp32 and are never rounded to bf16.
 #include <math.h>
 
 #include "../../include/ppm_b200.h"
@@ -22,8 +23,6 @@ constexpr int kCuRate = 4;
 
 __device__ __forceinline__ float cu_ld(const float* p) { return __ldg(p); }
 __device__ __forceinline__ float cu_ld(const __nv_bfloat16* p) { return __bfloat162float(__ldg(p)); }
-__device__ __forceinline__ float cu_round(float v, const float*) { return v; }
-__device__ __forceinline__ float cu_round(float v, const __nv_bfloat16*) { return bf16_round_f(v); }
 
 template <typename MaskT>
 __global__ void __launch_bounds__(kCuThreads)
@@ -71,7 +70,7 @@ convex_upsample_kernel(const float* __restrict__ flow, const MaskT* __restrict__
       float a0 = 0.f, a1 = 0.f;
       #pragma unroll
       for (int k = 0; k < 9; ++k) {
-        const float pk = cu_round(e[k] * inv, mask);
+        const float pk = e[k] * inv;
         a0 = __fadd_rn(a0, __fmul_rn(pk, f[0][k]));
         a1 = __fadd_rn(a1, __fmul_rn(pk, f[1][k]));
       }
@@ -129,19 +128,13 @@ convex_upsample_bf16x2_kernel(const float* __restrict__ flow, const __nv_bfloat1
         float mx = m[0];
         #pragma unroll
         for (int k = 1; k < 9; ++k) mx = fmaxf(mx, m[k]);
-        float e[10], sum = 0.f;
+        float e[9], sum = 0.f;
         #pragma unroll
         for (int k = 0; k < 9; ++k) { e[k] = ex2_approx((m[k] - mx) * 1.4426950408889634f); sum += e[k]; }
         const float inv = __frcp_rn(sum);
-        // weights rounded to bf16 two at a time (cvt.rn.bf16x2.f32 runs on the ALU pipe; the scalar cvt shares the
-        // XU pipe with the 144 ex2 per pixel and made it the busiest unit: 61 % in the first ncu capture)
-        float pw[10];
+        float pw[9];
         #pragma unroll
-        for (int k = 0; k < 10; k += 2) {
-          const uint32_t w2 = pack_bf16x2(e[k] * inv, k + 1 < 9 ? e[k + 1] * inv : 0.f);
-          pw[k] = __uint_as_float(w2 << 16);
-          pw[k + 1] = __uint_as_float(w2 & 0xFFFF0000u);
-        }
+        for (int k = 0; k < 9; ++k) pw[k] = e[k] * inv;
         float a0 = 0.f, a1 = 0.f;
         #pragma unroll
         for (int k = 0; k < 9; ++k) {

@@ -52,6 +52,18 @@ constexpr int kCbMaxN = 256;
 constexpr int kCbTmemCols = 512;     // two 256-column accumulators: MMA of tile i+1 overlaps the epilogue of tile i
 constexpr int kCbEpiWarps = 8;
 constexpr int kCbLevels = 5;
+
+// Timing ablations and tuning switches (PPM_CB_* environment variables, CorrBuildParams::ablate) exist only in an
+// experiments build (-DPPM_EXPERIMENTS, scripts/ only).  The library build reads no environment variable and the
+// ablation branches fold away at compile time.
+#ifdef PPM_EXPERIMENTS
+#define CB_ABLATE(p) ((p).ablate)
+static inline const char* cb_env(const char* name) { return getenv(name); }
+#else
+#define CB_ABLATE(p) 0
+static inline const char* cb_env(const char*) { return nullptr; }
+#endif
+
 struct CorrBuildParams {
   void* level[kCbLevels];
   int width[kCbLevels];
@@ -297,14 +309,14 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
         for (int kc = 0; kc < n_k; ++kc) {
           if (p.res_b && mt == 0) {                      // the item's F2 tile, once, chunk by chunk
             mbar_wait(&bar_bempty[kc], bph);
-            if ((p.ablate & 4)) mbar_arrive(&bar_bfull[kc]); else
+            if ((CB_ABLATE(p) & 4)) mbar_arrive(&bar_bfull[kc]); else
             mbar_expect_tx(&bar_bfull[kc], b_chunk_bytes);
-            for (int c = 0; c < n_bchunks && !(p.ablate & 4); ++c)
+            for (int c = 0; c < n_bchunks && !(CB_ABLATE(p) & 4); ++c)
               tma_load_4d(b_res + kc * b_chunk_bytes + c * kChunkBytes, &map2, &bar_bfull[kc], n0 + c * Tr::kChunkW, h,
                           kc * Tr::kKC, b);
           }
           mbar_wait(&bar_empty[s], ph);
-          if ((p.ablate & 4)) { mbar_arrive(&bar_full[s]); if (++s == n_ring) { s = 0; ph ^= 1; } continue; }
+          if ((CB_ABLATE(p) & 4)) { mbar_arrive(&bar_full[s]); if (++s == n_ring) { s = 0; ph ^= 1; } continue; }
           mbar_expect_tx(&bar_full[s], p.res_b ? kABytes : kABytes + b_chunk_bytes);
           uint8_t* st = smem + s * (p.res_b ? kABytes : kStageBytes);
           #pragma unroll
@@ -334,7 +346,7 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
     // took 0.39 ms of the 0.41 ms HBM budget at the 720p 1/4-res shape).
     {
       const bool leader = elect_one();
-      const uint32_t idesc = (p.ablate & 32) ? umma_idesc(Tr::kFmt, 0, 0, kCbM, p.NT)      // timing experiment only
+      const uint32_t idesc = (CB_ABLATE(p) & 32) ? umma_idesc(Tr::kFmt, 0, 0, kCbM, p.NT)      // timing experiment only
                                             : umma_idesc(Tr::kFmt, /*a MN-major*/ 1, /*b MN-major*/ 1, kCbM, p.NT);
       // MN-major: LBO = stride between 128-byte MN chunks, SBO = one swizzle group of channel rows
       const uint64_t d0 = umma_desc_sw128(0, kChunkBytes, Tr::kSbo, Tr::kLayout);
@@ -429,7 +441,7 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
       // a warp whose 32 rows all lie past W1 (the partial last M tile) has nothing to store: it only hands the
       // accumulator back
       const bool warp_has_rows = m0 + q * 32 < p.W1;
-      for (int ug = u_first + hsel; ug <= u_last && warp_has_rows && !(p.ablate & 8); ug += 2) {
+      for (int ug = u_first + hsel; ug <= u_last && warp_has_rows && !(CB_ABLATE(p) & 8); ug += 2) {
       const int ga = 2 * ug > g_first ? 2 * ug : g_first, gb = 2 * ug + 1 < g_last ? 2 * ug + 1 : g_last;
       const bool single = ga == gb;                              // edge unit of one chunk: [32][64 B] box
       const bool pair_full = !single && 64 * ug + 64 <= p.W2;    // levels 2-4 of the unit leave in one store each
@@ -445,7 +457,7 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
           if (lane == 0) mbar_arrive(&bar_acc_empty[buf]);
           released = true;
         }
-        if (p.ablate & 16) {
+        if (CB_ABLATE(p) & 16) {
           uint32_t x = 0;
           #pragma unroll
           for (int j = 0; j < 32; ++j) x ^= raw[j];
@@ -488,7 +500,7 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
                   w[j] = cb_avg_bf16x2(lo, hi);
                 }
               }
-              if (p.ablate & 1) { if (w[0] == 0x12345678u && l == 4) *reinterpret_cast<uint32_t*>(p.level[0]) = w[0]; continue; }
+              if (CB_ABLATE(p) & 1) { if (w[0] == 0x12345678u && l == 4) *reinterpret_cast<uint32_t*>(p.level[0]) = w[0]; continue; }
               if (p.tma_out && l == 0) {                 // level 0: this thread's 64-byte row segment -> the warp's staging box
                 if (g == ga) {                           // first chunk of the unit: the previous unit's store has read the box
                   if (lane == 0) bulk_wait_read<0>();
@@ -525,7 +537,7 @@ corr_build_kernel(const __grid_constant__ CUtensorMap map1, const __grid_constan
                 }
               }
             }
-            if (p.tma_out && !(p.ablate & 3) && g == gb) {     // unit complete
+            if (p.tma_out && !(CB_ABLATE(p) & 3) && g == gb) {     // unit complete
               fence_proxy_async_smem();                 // staged rows -> visible to the TMA engine
               __syncwarp();
               if (lane == 0) {                          // rows past W1 and columns past W2 are clipped by the TMA unit
@@ -639,7 +651,7 @@ static int launch_corr_build(const void* f1, const void* f2, int B, int D, int H
   CbStoreMaps om{};
   p.tma_out = 0;
   int stage_bytes = 0;
-  if (sizeof(OutT) == 2 && !getenv("PPM_CB_NOTMA")) {
+  if (sizeof(OutT) == 2 && !cb_env("PPM_CB_NOTMA")) {
     bool ok = ((static_cast<size_t>(W2) * 2) % 16 == 0) && (reinterpret_cast<uintptr_t>(levels[0]) % 16 == 0);
     if (ok) {
       const uint64_t dims[3] = {(uint64_t)W2, (uint64_t)W1, (uint64_t)B * H};
@@ -676,7 +688,7 @@ static int launch_corr_build(const void* f1, const void* f2, int B, int D, int H
     p.res_b = 1;
     int a_st = (kSmemMax - b_bytes - stage_bytes) / kABytes;
     p.a_stages = a_st > kCbMaxRing ? kCbMaxRing : a_st;
-    if (getenv("PPM_CB_ASTAGES") && atoi(getenv("PPM_CB_ASTAGES")) < p.a_stages) p.a_stages = atoi(getenv("PPM_CB_ASTAGES"));
+    if (cb_env("PPM_CB_ASTAGES") && atoi(cb_env("PPM_CB_ASTAGES")) < p.a_stages) p.a_stages = atoi(cb_env("PPM_CB_ASTAGES"));
     ring_bytes = p.a_stages * kABytes + b_bytes;
   }
   const int smem_bytes = ring_bytes + stage_bytes + 1024;
@@ -686,8 +698,8 @@ static int launch_corr_build(const void* f1, const void* f2, int B, int D, int H
   int dev = 0, n_sm = 148;
   PPM_CUDA(cudaGetDevice(&dev));
   PPM_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
-  p.ablate = getenv("PPM_CB_ABLATE") ? atoi(getenv("PPM_CB_ABLATE")) : 0;
-  p.pair = (p.res_b && p.n_ntiles == 2 && !getenv("PPM_CB_NO_PAIR")) ? 1 : 0;
+  p.ablate = cb_env("PPM_CB_ABLATE") ? atoi(cb_env("PPM_CB_ABLATE")) : 0;
+  p.pair = (p.res_b && p.n_ntiles == 2 && !cb_env("PPM_CB_NO_PAIR")) ? 1 : 0;
   if (p.pair) {
     cudaLaunchConfig_t cfg{};
     cudaLaunchAttribute at[1];
@@ -699,7 +711,7 @@ static int launch_corr_build(const void* f1, const void* f2, int B, int D, int H
     PPM_CUDA(cudaOccupancyMaxActiveClusters(&n_cl, kern, &cfg));     // clusters that can be co-resident (persistent kernel)
     const long long rows = p.n_items / 2;
     if (n_cl > rows) n_cl = static_cast<int>(rows);
-    if (getenv("PPM_CB_VERBOSE")) fprintf(stderr, "corr_build: %d co-resident 2-CTA clusters\n", n_cl);
+    if (cb_env("PPM_CB_VERBOSE")) fprintf(stderr, "corr_build: %d co-resident 2-CTA clusters\n", n_cl);
     if (n_cl >= 1) {
       cfg.gridDim = dim3(static_cast<unsigned>(2 * n_cl));
       PPM_CUDA(cudaLaunchKernelEx(&cfg, kern, m1, m2, om, p));

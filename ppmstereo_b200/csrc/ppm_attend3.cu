@@ -1,7 +1,13 @@
-// K3c (v3): PPM memory read, two 128-query tiles per CTA, fine-grained P hand-off.
-// Replaces the flash_attn_func call and residual at reference models/core/ppmstereo.py:550-555.
+// K3c: query-adaptive softmax aggregation over the picked memory frames (the PPM "read"): two 128-query tiles per
+// CTA, fine-grained P hand-off.  Replaces the flash_attn_func call and residual at reference
+// models/core/ppmstereo.py:550-555:
+//   hidden[p, :] = softmax_{p'}(scale * Q'[p] . K'[p']) V[p'],  p' over all pixels of the picked frames
+//   out[c, p]    = motion_features[c, p] + beta * bf16(hidden[p, c])
+// FlashAttention-2 rounding contract: bf16 operands, fp32 softmax, P rounded to bf16 before P.V, bf16 hidden.
+// (Two earlier generations of this kernel -- one query tile per CTA; two tiles with a whole-row P hand-off -- are
+// kept as history under scripts/exp/attend_generations/; they are not part of the library.)
 //
-// What changed against ppm_attend2.cu (same tiling, same TMEM map, same arithmetic contract):
+// Design points (against those generations; same TMEM map, same arithmetic contract):
 //  * P is handed to the tensor pipe in four 32-key chunks (one mbarrier each), so P.V of a
 //    query tile starts while its softmax warps are still exponentiating the rest of the row:
 //    the S-ready -> P-ready latency no longer sits between two MMAs.
@@ -13,7 +19,7 @@
 //    (16/clk/SM) needing as many cycles per tile as the two MMAs.  Measured on this B200 it
 //    LOSES 5-13 %: the kernel runs at the 1000 W power cap (SM clock 1.55 GHz of 1.97), a run
 //    with the exponential removed altogether is only 1.3 % faster, and the polynomial costs
-//    more energy than the MUFU op it replaces.  Default kEmu = 0; kEmu = 4 is kept as a
+//    more energy than the MUFU op it replaces.  The library instantiates kEmu = 0 only; kEmu = 4 stays in the source as a
 //    tested alternative for parts with more power headroom.
 //  * the MMA warp walks its loop convergently and forms each descriptor with one integer add
 //    (the first version rebuilt two 64-bit descriptors per MMA in one thread: +4 %).
@@ -27,6 +33,7 @@
 // TMEM columns: S_A 0-127, S_B 128-255, O_A 256-383, O_B 384-511; P (bf16) overwrites the first
 // 64 columns of its S (all of S is in registers before the first P chunk is stored).
 #include <math.h>
+#include <atomic>
 
 #include "../../include/ppm_b200.h"
 #include "common.cuh"
@@ -39,6 +46,7 @@ constexpr int kA3TileBytes = kA3Tile * kA3Tile * 2;       // 32 KB
 constexpr int kA3HalfBytes = kA3TileBytes / 2;
 constexpr int kA3Slots = 5;
 constexpr uint32_t kA3TmemCols = 512;
+constexpr float kA3RescaleThreshold = 8.0f;              // lazy rescale of O: only when the running max grows by > 2^8
 
 struct Attend3Params {
   const int32_t* picked;
@@ -436,36 +444,96 @@ ppm_attend3_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
   }
 }
 
+// cudaFuncSetAttribute once per (kernel instantiation, device), not once per call.
 template <int kEmu, typename MfT>
 static int launch_attend3(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv, const Attend3Params& p,
                           int n_qtiles, int n_frames, cudaStream_t st) {
   constexpr int kSmem = (2 + kA3Slots) * kA3TileBytes + 1024;
   auto kern = ppm_attend3_kernel<kEmu, MfT>;
-  PPM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+  static std::atomic<uint64_t> attr_done{0};                  // bit d: attribute set on device d (d < 64)
+  int dev = 0;
+  PPM_CUDA(cudaGetDevice(&dev));
+  if (dev >= 64 || !((attr_done.load(std::memory_order_acquire) >> dev) & 1)) {
+    PPM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+    if (dev < 64) attr_done.fetch_or(1ull << dev, std::memory_order_release);
+  }
   kern<<<dim3(n_qtiles, n_frames), kA3Threads, kSmem, st>>>(mq, mk, mv, p);
   PPM_CUDA(cudaGetLastError());
   return PPM_OK;
 }
 
-template <int kEmu>
-static int launch_attend3_mf(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv,
-                             const Attend3Params& p, int mf_dtype, int n_qtiles, int n_frames, cudaStream_t st) {
-  if (mf_dtype == PPM_BF16) return launch_attend3<kEmu, __nv_bfloat16>(mq, mk, mv, p, n_qtiles, n_frames, st);
-  return launch_attend3<kEmu, float>(mq, mk, mv, p, n_qtiles, n_frames, st);
-}
+// Tensor maps depend only on (base pointer, pixel count, frame count, operand kind): the per-level operands (Q', the
+// K' workspace, the V buffer) keep their addresses over a level's iterations, so the three cuTensorMapEncodeTiled
+// calls per read are served from a small per-thread cache (the only state the library keeps; no caller memory is
+// retained -- a stale entry is a 128-byte descriptor that is simply never matched again).
+struct MapKey { const void* base; int hw, frames, kind, dev; };
+struct MapEntry { MapKey k; CUtensorMap m; };
+constexpr int kMapCache = 16;
 
-// Entry used by ppm_memory_attend (ppm_attend.cu).  `emu` = exponentials per 8 evaluated on the FMA pipe.
-int attend3_dispatch(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv, const int32_t* picked,
-                     const void* mf, int mf_dtype, long long mb, long long mc, long long mt, const float* beta,
-                     float scale_log2, float rescale_thr, int emu, int b, int T, int Kp, int hw, int q_begin,
-                     int q_count, float* out, cudaStream_t st) {
-  Attend3Params p{};
-  p.picked = picked; p.mf = mf; p.mb = mb; p.mc = mc; p.mt = mt; p.beta = beta; p.out = out;
-  p.scale_log2 = scale_log2; p.rescale_thr = rescale_thr; p.T = T; p.Kp = Kp; p.hw = hw;
-  p.q_begin = q_begin; p.q_end = q_begin + q_count;
-  const int n_qtiles = (q_count + 2 * kA3Tile - 1) / (2 * kA3Tile);
-  if (emu == 4) return launch_attend3_mf<4>(mq, mk, mv, p, mf_dtype, n_qtiles, b * T, st);
-  return launch_attend3_mf<0>(mq, mk, mv, p, mf_dtype, n_qtiles, b * T, st);
+static int cached_map(const CUtensorMap** out, const void* base, int hw, int frames, int kind) {
+  static thread_local MapEntry cache[kMapCache];
+  static thread_local int n_used = 0, next = 0;
+  int dev = 0;
+  PPM_CUDA(cudaGetDevice(&dev));
+  for (int i = 0; i < n_used; ++i) {
+    const MapKey& k = cache[i].k;
+    if (k.base == base && k.hw == hw && k.frames == frames && k.kind == kind && k.dev == dev) { *out = &cache[i].m; return PPM_OK; }
+  }
+  MapEntry& e = cache[next];
+  const uint32_t box[3] = {64, 128, 1};
+  int rc;
+  if (kind < 2) {                       // Q' / K': (frames, hw, 128) bf16, channels contiguous
+    const uint64_t dims[3] = {128, (uint64_t)hw, (uint64_t)frames};
+    const uint64_t str[2] = {256, (uint64_t)hw * 256};
+    rc = make_tensor_map(&e.m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, base, dims, str, box, CU_TENSOR_MAP_SWIZZLE_128B);
+  } else {                              // V: (frames, 128, hw_pad) bf16, pixels contiguous
+    const int hw_pad = (hw + 7) / 8 * 8;
+    const uint64_t dims[3] = {(uint64_t)hw_pad, 128, (uint64_t)frames};
+    const uint64_t str[2] = {(uint64_t)hw_pad * 2, (uint64_t)hw_pad * 256};
+    rc = make_tensor_map(&e.m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, base, dims, str, box, CU_TENSOR_MAP_SWIZZLE_128B);
+  }
+  if (rc) { e.k = MapKey{nullptr, 0, 0, -1, -1}; return rc; }
+  e.k = MapKey{base, hw, frames, kind, dev};
+  *out = &e.m;
+  if (n_used < kMapCache) ++n_used;
+  next = (next + 1) % kMapCache;
+  return PPM_OK;
 }
 
 }  // namespace ppm
+
+extern "C" int ppm_memory_attend(const void* Q, const void* K, const void* V, const int32_t* picked, const void* mf,
+                                 int mf_dtype, int64_t mb, int64_t mc, int64_t mt, const float* beta, float scale,
+                                 int b, int T, int Kp, int hw, float* out, void* stream) {
+  return ppm_memory_attend_band(Q, K, V, picked, mf, mf_dtype, mb, mc, mt, beta, scale, b, T, Kp, hw, 0, hw, out, stream);
+}
+
+extern "C" int ppm_memory_attend_band(const void* Q, const void* K, const void* V, const int32_t* picked,
+                                      const void* mf, int mf_dtype, int64_t mb, int64_t mc, int64_t mt,
+                                      const float* beta, float scale, int b, int T, int Kp, int hw, int q_begin,
+                                      int q_count, float* out, void* stream) {
+  using namespace ppm;
+  PPM_CHECK(q_begin >= 0 && q_count >= 0 && q_begin + q_count <= hw, PPM_ERR_ARG,
+            "ppm_memory_attend_band: query band [%d, %d) outside [0, %d)", q_begin, q_begin + q_count, hw);
+  if (q_count == 0) return PPM_OK;
+  PPM_CHECK(Q && K && V && picked && mf && beta && out, PPM_ERR_ARG, "ppm_memory_attend: null pointer");
+  PPM_CHECK(b > 0 && T > 0 && Kp > 0 && hw > 0, PPM_ERR_ARG, "ppm_memory_attend: bad shape");
+  PPM_CHECK(mf_dtype == PPM_F32 || mf_dtype == PPM_BF16, PPM_ERR_ARG, "ppm_memory_attend: bad dtype");
+  PPM_CHECK(b * T <= 65535, PPM_ERR_UNSUPPORTED, "ppm_memory_attend: b*T > 65535");
+  PPM_CHECK(((reinterpret_cast<uintptr_t>(Q) | reinterpret_cast<uintptr_t>(K) | reinterpret_cast<uintptr_t>(V)) & 15) == 0,
+            PPM_ERR_ARG, "ppm_memory_attend: packed operands must be 16-byte aligned");
+  const CUtensorMap *mq, *mk, *mv;
+  if (int rc = cached_map(&mq, Q, hw, b * T, 0)) return rc;
+  if (int rc = cached_map(&mk, K, hw, b * T * Kp, 1)) return rc;
+  if (int rc = cached_map(&mv, V, hw, b * T, 2)) return rc;
+  Attend3Params p{};
+  p.picked = picked; p.mf = mf; p.mb = mb; p.mc = mc; p.mt = mt; p.beta = beta; p.out = out;
+  p.scale_log2 = scale * 1.4426950408889634f;
+  p.rescale_thr = kA3RescaleThreshold;
+  p.T = T; p.Kp = Kp; p.hw = hw;
+  p.q_begin = q_begin; p.q_end = q_begin + q_count;
+  const int n_qtiles = (q_count + 2 * kA3Tile - 1) / (2 * kA3Tile);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (mf_dtype == PPM_BF16) return launch_attend3<0, __nv_bfloat16>(*mq, *mk, *mv, p, n_qtiles, b * T, st);
+  return launch_attend3<0, float>(*mq, *mk, *mv, p, n_qtiles, b * T, st);
+}

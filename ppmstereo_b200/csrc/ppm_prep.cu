@@ -14,7 +14,9 @@ __device__ __forceinline__ float ld_as_float(const __nv_bfloat16* p) { return __
 
 // ------------------------------------------------------------------ frame confidence
 // conf[f] = mean over hw of uncertainty[f, :]   (ppmstereo.py:506).  One CTA per frame,
-// fixed reduction tree => deterministic.
+// fixed reduction tree => deterministic.  dtype rule (include/ppm_b200.h, ppm_qam_pick): torch.mean is not an
+// autocast-fp32 op, so for the bf16 uncertainty map of the reference's autocast regime `.mean(-1)` returns a
+// bf16 tensor -- fp32 accumulation, sum * (1/hw) (ATen MeanOps), ONE rounding to bf16.  Mirrored here.
 template <typename T>
 __global__ void __launch_bounds__(512) frame_mean_kernel(const T* __restrict__ unc, int hw,
                                                          float* __restrict__ conf) {
@@ -38,7 +40,10 @@ __global__ void __launch_bounds__(512) frame_mean_kernel(const T* __restrict__ u
     float t = threadIdx.x < 16 ? part[threadIdx.x] : 0.f;
     #pragma unroll
     for (int o = 8; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
-    if (threadIdx.x == 0) conf[blockIdx.x] = t / static_cast<float>(hw);
+    if (threadIdx.x == 0) {
+      const float m = __fmul_rn(t, 1.0f / static_cast<float>(hw));
+      conf[blockIdx.x] = sizeof(T) == 2 ? bf16_round_f(m) : m;
+    }
   }
 }
 
@@ -113,7 +118,7 @@ __global__ void __launch_bounds__(256) qam_pick_kernel(const float* __restrict__
     for (int e = lane; e < b * K; e += 32) s += sel[((e / K) * T + i) * top_k + (e % K)];
     #pragma unroll
     for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-    const float mean = s / static_cast<float>(b * K);
+    const float mean = __fmul_rn(s, 1.0f / static_cast<float>(b * K));   // ATen CUDA mean: sum * (1/n)
     for (int e = lane; e < b * top_k; e += 32) {
       const int bb = e / top_k, n = e % top_k;
       const int idx = (bb * T + i) * top_k + n;

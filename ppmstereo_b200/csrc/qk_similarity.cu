@@ -3,7 +3,9 @@
 //   x_[b,t,:]   = mean_c AdaptiveMaxPool2d((h//4, w//4))(x[b,:,t])          for x = query, key
 //   sim[b,i,j]  = <k_[b,i], q_[b,j]> / (max(|k_[b,i]|, eps) * max(|q_[b,j]|, eps)),  eps = 1e-8
 // fp32 arithmetic (inputs fp32 or bf16), fixed reduction orders => run-to-run deterministic, which matters
-// because sim feeds the top-k frame pick.  HBM-bound: both tensors are read exactly once.
+// because sim feeds the top-k frame pick.  dtype rule: for bf16 inputs (the reference's autocast regime) the pooled
+// channel mean is rounded to bf16 -- `q_.mean(dim=1)` of a bf16 tensor returns bf16 (:409), only
+// F.cosine_similarity up-casts; for fp32 inputs nothing is rounded.  HBM-bound: both tensors are read exactly once.
 //   pool kernel  : CTA = (pooled row, frame); thread = pooled column; loops over the 128 channels and the
 //                  adaptive window (start = floor(i*n/o), end = ceil((i+1)*n/o)); consecutive threads read
 //                  consecutive windows of an image row, so requests are coalesced.
@@ -40,7 +42,8 @@ sim_pool_kernel(const T* __restrict__ x, long long sb, long long sc, long long s
         for (int q = c0; q < c1; ++q) m = fmaxf(m, sim_ld(pc + r * w + q));
       acc += m;
     }
-    pooled[(static_cast<long long>(frame) * oh + oy) * ow + ox] = acc / static_cast<float>(C);
+    const float m = __fmul_rn(acc, 1.0f / static_cast<float>(C));
+    pooled[(static_cast<long long>(frame) * oh + oy) * ow + ox] = sizeof(T) == 2 ? bf16_round_f(m) : m;
   }
 }
 

@@ -1,5 +1,5 @@
-"""GPU aid: time ppm_memory_attend at the 1/4-res 720p shape (T=20, hw=58880, K=5) for the kernel
-generations / exp-emulation settings, and report the deviation between them.
+"""GPU aid: time ppm_memory_attend at the 1/4-res 720p shape (T=20, hw=58880, K=5), with the SM clock and board
+power sampled during the run.
   python scripts/bench_attend.py [T] [h] [w] [reps]"""
 import ctypes, os, subprocess, sys, threading, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -11,11 +11,8 @@ T = int(sys.argv[1]) if len(sys.argv) > 1 else 20
 h = int(sys.argv[2]) if len(sys.argv) > 2 else 184
 w = int(sys.argv[3]) if len(sys.argv) > 3 else 320
 reps = int(sys.argv[4]) if len(sys.argv) > 4 else 3
-variants = [tuple(int(x) for x in v.split(":")) for v in
-            (sys.argv[5].split(",") if len(sys.argv) > 5 else ["3:0", "3:4", "2:0", "1:0"])]
+variants = [(3, 0)]
 lib = _lib.load()
-lib.ppm_debug_set_attend_version.argtypes = [ctypes.c_int]
-lib.ppm_debug_set_exp_emulation.argtypes = [ctypes.c_int]
 dev = torch.device("cuda")
 g = torch.Generator(device=dev).manual_seed(0)
 rn = lambda *s: torch.randn(*s, generator=g, device=dev).bfloat16()
@@ -41,8 +38,6 @@ def smi_sampler(stop, out):
 
 ref = None
 for ver, emu in variants:
-    lib.ppm_debug_set_attend_version(ver)
-    lib.ppm_debug_set_exp_emulation(emu)
     out = mem.aggregate(mf, beta)
     torch.cuda.synchronize()
     stop, lines = threading.Event(), []
@@ -65,5 +60,3 @@ for ver, emu in variants:
     print(f"v{ver} emu{emu}: {min(ms):8.2f} ms best, {sum(ms)/len(ms):8.2f} avg  -> {flops/min(ms)/1e9:7.1f} TFLOP/s best, "
           f"{flops/(sum(ms)/len(ms))/1e9:7.1f} avg | vs first: max {float(d.max()):.3e} mean {float(d.mean()):.3e} "
           f"(|hidden| max {float(ref.abs().max()):.3f}) | sm clock median {clk:.0f} MHz, power max {pw:.0f} W ({len(vals)} samples)", flush=True)
-lib.ppm_debug_set_attend_version(3)
-lib.ppm_debug_set_exp_emulation(0)

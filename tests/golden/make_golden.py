@@ -158,8 +158,11 @@ def upsample_cases():
     flow = torch.randn(N, 2, H, W, generator=g) * 6.0
     mask = torch.randn(N, 9 * 16, H, W, generator=g) * 2.0
     out32 = ppm.PPMStereo.convex_upsample(None, flow, mask, 4)
+    # A bf16 mask reaches the op only under the reference's torch.cuda.amp.autocast (ppmstereo.py:617), where
+    # torch.softmax up-casts its input to fp32 (autocast's fp32 op list).  That context is a no-op on CPU, so the
+    # up-cast autocast would perform is applied to the argument here.
     mask16 = mask.bfloat16()
-    out16 = ppm.PPMStereo.convex_upsample(None, flow, mask16, 4)
+    out16 = ppm.PPMStereo.convex_upsample(None, flow, mask16.float(), 4)
     np.savez_compressed(os.path.join(HERE, "convex_upsample.npz"), flow=flow.numpy(), mask=mask.numpy(),
                         out_fp32_mask=out32.float().numpy(), mask_bf16=bf16_bits(mask16),
                         out_bf16_mask=out16.float().numpy())

@@ -23,12 +23,33 @@ def lib():
 
 def test_exports_every_declared_symbol(lib):
     header = open(os.path.join(ROOT, "include", "ppm_b200.h")).read()
-    declared = set(re.findall(r"^(?:int|const char\*)\s+(ppm_\w+)\s*\(", header, flags=re.M))
+    declared = set(re.findall(r"^PPM_API (?:int|const char\*)\s+(ppm_\w+)\s*\(", header, flags=re.M))
     assert len(declared) >= 10
     assert declared == set(_lib.SIGNATURES), (declared ^ set(_lib.SIGNATURES))
     for name in declared:
         assert hasattr(lib, name), name
     assert lib.ppm_abi_version() == 1
+
+
+def test_exports_nothing_but_the_declared_symbols(lib):
+    """The converse: the dynamic symbol table of the library holds exactly the header's functions -- no debug
+    hooks, no C++ internals (-fvisibility=hidden) -- and the library reads no environment variable."""
+    import subprocess
+    header = open(os.path.join(ROOT, "include", "ppm_b200.h")).read()
+    declared = set(re.findall(r"^PPM_API (?:int|const char\*)\s+(ppm_\w+)\s*\(", header, flags=re.M))
+    out = subprocess.run(["nm", "-D", "--defined-only", _lib.LIB_PATH], capture_output=True, text=True, check=True).stdout
+    exported = {ln.split()[-1] for ln in out.splitlines() if ln.split() and ln.split()[-2] in ("T", "t", "W", "V", "D", "B")}
+    assert exported == declared, exported ^ declared
+    # (libcudart_static itself imports getenv, so the import table cannot be used): no switch name in the binary,
+    # and every getenv in the sources sits behind PPM_EXPERIMENTS
+    blob = open(_lib.LIB_PATH, "rb").read()
+    assert b"PPM_CB_" not in blob and b"ppm_debug" not in blob
+    csrc = os.path.join(ROOT, "ppmstereo_b200", "csrc")
+    for fn in os.listdir(csrc):
+        src = open(os.path.join(csrc, fn)).read()
+        for m in re.finditer(r"\bgetenv\(", src):
+            guard = src.rfind("#ifdef PPM_EXPERIMENTS", 0, m.start())
+            assert guard >= 0 and "#else" not in src[guard:m.start()], (fn, "getenv outside PPM_EXPERIMENTS")
 
 
 def test_argument_errors_are_reported(lib):

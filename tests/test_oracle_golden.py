@@ -94,10 +94,5 @@ def test_convex_upsample_matches_reference(golden_dir, kind):
         ref = torch.from_numpy(g["out_bf16_mask"])
     out = O.convex_upsample(flow, mask, 4)
     assert out.shape == ref.shape
-    if kind == "fp32":
-        assert (out - ref).abs().max() <= 1e-5 * ref.abs().max()   # fp32 summation order only
-    else:
-        # the fixture comes from torch's CPU softmax, which rounds a bf16 input twice; the oracle restates the
-        # CUDA softmax the reference actually runs (one rounding): 0.7 % of the weights differ by one bf16 ulp
-        assert (out - ref).abs().max() <= 2.0 ** -8 * ref.abs().max()
-        assert (out - ref).abs().mean() <= 1e-4 * ref.abs().mean()
+    # bf16 mask = storage only: under the reference's CUDA autocast the softmax runs (and stays) in fp32
+    assert (out - ref).abs().max() <= 1e-5 * ref.abs().max()   # fp32 summation order only
