@@ -12,7 +12,7 @@ There is no CPU or PyTorch fallback: every op fails loudly without libppm_sm100.
 """
 from .corr import CorrBlock1D, build_pyramid, lookup, lookup_l0
 from .memory import PPMMemory, ppm_memory_read, softmax_scale, temporal_pe_table
-from .install import install, forward_update_block
+from .install import install, uninstall, forward_update_block
 from .pipeline import StagedRunner
 from . import shard
 from .upsample import convex_upsample
@@ -21,5 +21,5 @@ from .window import FrameFeatureCache, forward_batch_test
 from . import window
 
 __all__ = ["CorrBlock1D", "build_pyramid", "lookup", "lookup_l0", "PPMMemory", "ppm_memory_read", "softmax_scale",
-           "temporal_pe_table", "install", "forward_update_block", "StagedRunner", "shard", "convex_upsample", "RowBandMemory", "gather_bands", "row_bands",
+           "temporal_pe_table", "install", "uninstall", "forward_update_block", "StagedRunner", "shard", "convex_upsample", "RowBandMemory", "gather_bands", "row_bands",
            "FrameFeatureCache", "forward_batch_test", "window"]

@@ -20,8 +20,16 @@ from .upsample import convex_upsample
 from .window import forward_batch_test
 
 
+def _inference_only(inp, *params):
+    """The kernels have no backward: refuse to run where autograd would silently drop gradients."""
+    if torch.is_grad_enabled() and (inp.requires_grad or any(p.requires_grad for p in params)):
+        raise RuntimeError("ppmstereo_b200 is inference only (no autograd through the sm_100a kernels): call the "
+                           "installed model under torch.no_grad(), or ppmstereo_b200.uninstall() for training")
+
+
 def forward_update_block(self, image1, update_block, corr_fn, flow, net, inp, motion_hidden_state,
                          attn_block, predictions, uncertainties, iters, interp_scale, t):
+    _inference_only(inp, attn_block.to_qk.weight, update_block.aggregator.beta)
     bt, c, h, w = inp.shape
     b = bt // t
     if c != C:
@@ -62,9 +70,30 @@ def forward_update_block(self, image1, update_block, corr_fn, flow, net, inp, mo
     return flow_out, net, motion_hidden_state
 
 
+_ORIGINALS = "_ppmstereo_b200_originals"
+
+
 def install(ppmstereo_module):
-    """Patch the reference module in place; returns it."""
+    """Patch the reference module in place; returns it.  Idempotent; ``uninstall`` restores the originals."""
+    if not hasattr(ppmstereo_module, _ORIGINALS):
+        cls = ppmstereo_module.PPMStereo
+        setattr(ppmstereo_module, _ORIGINALS, {
+            "CorrBlock1D": ppmstereo_module.CorrBlock1D,
+            "forward_update_block": cls.forward_update_block,
+            "forward_batch_test": cls.forward_batch_test,
+        })
     ppmstereo_module.CorrBlock1D = CorrBlock1D
     ppmstereo_module.PPMStereo.forward_update_block = forward_update_block
     ppmstereo_module.PPMStereo.forward_batch_test = forward_batch_test      # window scheduler (ppmstereo.py:238-320)
+    return ppmstereo_module
+
+
+def uninstall(ppmstereo_module):
+    """Put the reference's own CorrBlock1D / forward_update_block / forward_batch_test back."""
+    orig = getattr(ppmstereo_module, _ORIGINALS, None)
+    if orig is not None:
+        ppmstereo_module.CorrBlock1D = orig["CorrBlock1D"]
+        ppmstereo_module.PPMStereo.forward_update_block = orig["forward_update_block"]
+        ppmstereo_module.PPMStereo.forward_batch_test = orig["forward_batch_test"]
+        delattr(ppmstereo_module, _ORIGINALS)
     return ppmstereo_module

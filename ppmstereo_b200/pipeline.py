@@ -13,7 +13,7 @@ CUDA only: there is no CPU path.
 """
 from __future__ import annotations
 
-from typing import Callable, Dict, Iterable, List, Sequence, Tuple
+from typing import Callable, Dict, Iterable, List, Optional, Sequence, Tuple
 
 import torch
 
@@ -28,13 +28,13 @@ class StagedRunner:
         self.d2h = torch.cuda.Stream(self.device)
         self._host_out: Dict[Tuple, List[torch.Tensor]] = {}
 
-    # -- pinned result buffers, `depth` per distinct (shape, dtype), reused across jobs
-    def _out_buffer(self, t: torch.Tensor, turn: int, idx: int) -> torch.Tensor:
+    # -- pinned result buffers per distinct (result index, shape, dtype): `slots` of them, reused across run() calls
+    def _out_buffer(self, t: torch.Tensor, slot: int, slots: int, idx: int) -> torch.Tensor:
         key = (idx, tuple(t.shape), t.dtype)
         pool = self._host_out.setdefault(key, [])
-        while len(pool) < self.depth:
+        while len(pool) < slots:
             pool.append(torch.empty(t.shape, dtype=t.dtype, pin_memory=True))
-        return pool[turn % self.depth]
+        return pool[slot]
 
     def _upload(self, job: Dict[str, torch.Tensor], after=None):
         with torch.cuda.stream(self.h2d):
@@ -50,15 +50,30 @@ class StagedRunner:
         return dev, ev
 
     def run(self, jobs: Sequence[Dict[str, torch.Tensor]],
-            fn: Callable[[Dict[str, torch.Tensor], int], Iterable[torch.Tensor]]) -> List[List[torch.Tensor]]:
+            fn: Callable[[Dict[str, torch.Tensor], int], Iterable[torch.Tensor]],
+            on_result: Optional[Callable[[int, List[torch.Tensor]], None]] = None) -> List[List[torch.Tensor]]:
         """Run ``fn(device_inputs, job_index) -> device tensors`` over ``jobs`` (dicts of pinned host
-        tensors).  Returns, per job, the results in pinned host memory.  The host buffers of job i are
-        reused by job i + depth: consume (or copy) a result before that many further jobs complete --
-        ``run`` itself returns only after every copy has finished."""
+        tensors); returns only after every copy has finished.
+
+        Without ``on_result``: returns, per job, the results in pinned host memory -- one buffer set per job, no
+        two jobs share one (the sets are kept and reused by the next ``run`` of the same length / shapes).
+        With ``on_result(i, host_tensors)``: results stream through a ring of ``depth`` pinned buffer sets; the
+        callback is invoked on the host once job i's download has completed and before its buffers are reused
+        (copy or consume them there); ``run`` then returns an empty list."""
         compute = torch.cuda.current_stream(self.device)
         results: List[List[torch.Tensor]] = []
         done_copy: List[torch.cuda.Event] = []
         computed: List[torch.cuda.Event] = []
+        slots = self.depth if on_result is not None else max(1, len(jobs))
+        delivered = 0
+
+        def deliver(upto: int) -> int:
+            d = delivered
+            while on_result is not None and d < upto:
+                done_copy[d].synchronize()
+                on_result(d, results[d])
+                d += 1
+            return d
         nxt = self._upload(jobs[0]) if jobs else None
         for i, _ in enumerate(jobs):
             dev, ready = nxt
@@ -70,14 +85,14 @@ class StagedRunner:
             finished = torch.cuda.Event()
             finished.record(compute)
             computed.append(finished)
-            if i >= self.depth:
-                done_copy[i - self.depth].synchronize()    # the pinned buffers of that turn are free again
+            if on_result is not None and i >= self.depth:
+                delivered = deliver(i - self.depth + 1)     # job i - depth consumed: its ring slot is free again
             with torch.cuda.stream(self.d2h):
                 self.d2h.wait_event(finished)
                 host = []
                 for n, t in enumerate(outs):
                     t.record_stream(self.d2h)
-                    hb = self._out_buffer(t, i, n)
+                    hb = self._out_buffer(t, i % slots, slots, n)
                     hb.copy_(t, non_blocking=True)
                     host.append(hb)
                 ev = torch.cuda.Event()
@@ -86,4 +101,7 @@ class StagedRunner:
             results.append(host)
         for ev in done_copy:
             ev.synchronize()
+        if on_result is not None:
+            deliver(len(results))
+            return []
         return results

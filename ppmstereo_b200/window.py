@@ -90,8 +90,16 @@ class FrameFeatureCache(nn.Module):
             raise RuntimeError(f"FrameFeatureCache: {rows} input rows for {len(self._ids)} announced frames")
         missing = [r for r, f in enumerate(self._ids) if f not in self._store]
         if missing:
-            idx = torch.as_tensor(missing, device=(x[0] if is_list else x).device)
-            sub = [t.index_select(0, idx) for t in x] if is_list else x.index_select(0, idx)
+            if missing == list(range(missing[0], missing[-1] + 1)):
+                # the usual case (the new frames are the tail of the window): a view, no index upload
+                pick = lambda t: t[missing[0]:missing[-1] + 1]
+            else:
+                dev = (x[0] if is_list else x).device
+                idx = torch.tensor(missing, dtype=torch.long)
+                if dev.type == "cuda":                      # pinned + non_blocking: no host sync on the schedule
+                    idx = idx.pin_memory().to(dev, non_blocking=True)
+                pick = lambda t: t.index_select(0, idx)
+            sub = [pick(t) for t in x] if is_list else pick(x)
             out = self.inner(sub)
             self._single = torch.is_tensor(out)
             outs = (out,) if self._single else tuple(out)
@@ -167,7 +175,12 @@ def forward_batch_test(self, batch_dict: Dict, kernel_size: int = 20, iters: int
         for n, (start, stop) in enumerate(wins):
             ids = list(range(start, stop))
             if ready is not None:
-                torch.cuda.current_stream(dev).wait_event(ready)
+                cur = torch.cuda.current_stream(dev)
+                cur.wait_event(ready)
+                # the frame buffers were allocated on copy_in: tell the caching allocator that the compute stream
+                # reads them, or a later upload could reuse a freed block before this stack has executed
+                for f in ids:
+                    resident[f].record_stream(cur)
             clip = torch.stack([resident[f] for f in ids])              # (t, 2, 3, H, W)
             if n + 1 < len(wins):
                 ready = upload(range(*wins[n + 1]))                     # overlaps this window's kernels

@@ -1,0 +1,170 @@
+"""The drop-in running AS a drop-in on the B200 (BASELINE configs[0] and [3]).
+
+The UNMODIFIED reference model (staged byte for byte under oracle/_ref/ by oracle/stage_ref.py -- the GPU box has
+no /root/reference) runs on the GPU the way the reference runs it: bf16 autocast (mixed_precision=True, as
+models/ppm_stereo_model.py:26 sets it), its own einsum / avg_pool2d / grid_sample / argsort / masked_select and the
+installed flash_attn.  Next to it the same weights run after ``ppmstereo_b200.install()``.
+
+  * teacher-forced: every memory read of the reference run is replayed through PPMMemory on the tensors the
+    reference produced on the device (bf16 q / k / value / uncertainty, fp32 motion features): top-k masks must be
+    IDENTICAL, frame scores within 1e-6, ``motion_features_global`` within the bf16 rounding of the attention;
+  * free-running: final disparity of the installed model within 0.01 px mean absolute difference (north_star) of
+    the reference's, uncertainty within 1e-3, on the T = 6 fixture shape, on BASELINE configs[0] (5 x 320 x 512,
+    iters 10) and on a T = 8 clip (top-5 of 8 bites); per-iteration masks compared as well;
+  * ``forward_batch_test`` through window.py (per-frame encoder cache around the real fnet / cnet, staged copies)
+    against the reference's own loop on a 13-frame clip.
+beta = 0.5 and temporal_fc ~ N(0, 0.02) as in oracle/ref_import.build_reference_model (both are zero-initialised in
+the reference, which would hide the memory read).
+"""
+import pytest
+import torch
+
+from oracle import ref_import
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def env():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    if not ref_import.available():
+        pytest.skip("reference sources not staged (python oracle/stage_ref.py in the build container)")
+    import ppmstereo_b200 as P
+    model, ppm = ref_import.build_reference_model(seed=0, beta=0.5, mixed_precision=True)
+    model = model.cuda().eval()
+    yield P, model, ppm
+    P.uninstall(ppm)
+
+
+def clip(T, H, W, seed):
+    return torch.rand(T, 2, 3, H, W, generator=torch.Generator().manual_seed(seed)) * 255.0
+
+
+def run_forward(model, video, iters):
+    with torch.no_grad():
+        d, u = model(video[None, :, 0].cuda(), video[None, :, 1].cuda(), iters=iters, test_mode=True)
+    torch.cuda.synchronize()
+    return d.float(), u.float()
+
+
+def test_reference_runs_its_own_stack_on_the_gpu(env):
+    P, model, ppm = env
+    import flash_attn
+    assert ppm.flash_attn_func is flash_attn.flash_attn_func          # the real library, not the CPU stand-in
+    assert ppm.CorrBlock1D.__module__ == "models.core.corr"           # not installed yet
+    assert model.mixed_precision is True
+
+
+@pytest.mark.parametrize("T,H,W,iters", [(6, 64, 256, 4), (8, 96, 256, 4)])
+def test_teacher_forced_memory_reads(env, T, H, W, iters):
+    P, model, ppm = env
+    P.uninstall(ppm)
+    video = clip(T, H, W, 7)
+    with ref_import.MemoryReadRecorder(model, T) as rec:
+        run_forward(model, video, iters)
+    n = 0
+    worst = {"score": 0.0, "sim": 0.0, "out": 0.0}
+    mems = {}
+    for lvl, it, t in rec.reads(iters):
+        assert t["query"].dtype == torch.bfloat16 and t["uncertainty"].dtype == torch.bfloat16   # autocast regime
+        if lvl not in mems:
+            mems[lvl] = P.PPMMemory(t["query"], t["key"], None, top_k=5)
+            sim = mems[lvl].similarity()
+            worst["sim"] = max(worst["sim"], float((sim - t["sim"]).abs().max()))
+        mem = mems[lvl]
+        strive = t["strive_before"].clone()
+        out, mask = mem.read(t["value"], t["motion_features"], t["sim"], strive, t["uncertainty"],
+                             torch.tensor([0.5], device="cuda"), P.softmax_scale(128))
+        torch.cuda.synchronize()
+        worst["score"] = max(worst["score"], float((mem.frame_score - t["frame_score"]).abs().max()))
+        assert torch.equal(mask, t["mask"]), (lvl, it, mem.frame_score, t["frame_score"])   # bit-exact top-k sets
+        assert torch.equal(strive, t["strive_before"] + t["mask"].float())
+        ref = t["motion_features_global"].float()
+        hid = (ref - t["motion_features"].permute(0, 2, 1, 3, 4).reshape(ref.shape).float()) / 0.5
+        hmax = float(hid.abs().max())
+        d = (out - ref).abs()
+        worst["out"] = max(worst["out"], float(d.max()) / hmax)
+        assert float(d.max()) <= 3e-2 * hmax + 1e-6, (lvl, it, float(d.max()), hmax)
+        assert float(d.mean()) <= 3e-3 * hmax + 1e-7
+        n += 1
+    assert n == 2 * (iters // 2) + iters
+    print(f"teacher-forced T={T}: {n} reads, max |frame_score diff| {worst['score']:.2e}, max |sim diff| "
+          f"{worst['sim']:.2e}, max |mfg diff| / max|hidden| {worst['out']:.2e}")
+    assert worst["score"] <= 1e-6
+    assert worst["sim"] <= 1e-4
+
+
+@pytest.mark.parametrize("T,H,W,iters", [(6, 64, 256, 4), (5, 320, 512, 10), (8, 96, 256, 6)])
+def test_installed_model_matches_reference_disparity(env, T, H, W, iters):
+    """(5, 320, 512, iters 10) is BASELINE configs[0] at the model's GPU precision."""
+    P, model, ppm = env
+    video = clip(T, H, W, 11)
+    P.uninstall(ppm)
+    with ref_import.MemoryReadRecorder(model, T) as rec:
+        d_ref, u_ref = run_forward(model, video, iters)
+    ref_masks = [t["mask"] for _, _, t in rec.reads(iters)]
+    d_ref2, _ = run_forward(model, video, iters)                        # run-to-run noise floor of the reference
+    P.install(ppm)
+    got_masks = []
+    orig_pick = P.PPMMemory.pick
+
+    def pick(self, *a, **k):
+        m = orig_pick(self, *a, **k)
+        got_masks.append(m.clone())
+        return m
+
+    P.PPMMemory.pick = pick
+    try:
+        assert ppm.CorrBlock1D is P.CorrBlock1D
+        d_got, u_got = run_forward(model, video, iters)
+    finally:
+        P.PPMMemory.pick = orig_pick
+        P.uninstall(ppm)
+    assert d_got.shape == d_ref.shape == (1, T, 1, H, W)
+    mad = float((d_got - d_ref).abs().mean())
+    noise = float((d_ref2 - d_ref).abs().mean())
+    umad = float((u_got - u_ref).abs().mean())
+    same = [bool(torch.equal(a, b)) for a, b in zip(got_masks, ref_masks)]
+    print(f"installed vs reference T={T} {H}x{W} iters={iters}: mean |d disparity| {mad:.5f} px (|disparity| mean "
+          f"{float(d_ref.abs().mean()):.3f} px, reference run-to-run {noise:.2e}), max {float((d_got - d_ref).abs().max()):.4f}, "
+          f"uncertainty MAD {umad:.2e}, masks equal in {sum(same)}/{len(same)} iterations")
+    assert len(got_masks) == len(ref_masks) == 2 * (iters // 2) + iters
+    assert mad <= 0.01, mad                                             # north_star: final disparity within 0.01 px
+    assert umad <= 1e-3
+    assert same[0]                                                      # same inputs -> same pick
+    assert sum(same) >= 0.9 * len(same)                                 # trajectories may drift apart by rounding only
+
+
+def test_forward_batch_test_window_scheduler_vs_reference_loop(env):
+    """13-frame clip, kernel_size 6 -> windows [0:6] [3:9] [6:12] [9:13] [12:13]; the reference's loop encodes every
+    window from scratch, ours encodes each frame once (FrameFeatureCache changes the cuDNN batch shapes)."""
+    P, model, ppm = env
+    T, H, W, ks, iters = 13, 64, 256, 6, 4
+    video = clip(T, H, W, 13)
+    P.uninstall(ppm)
+    with torch.no_grad():
+        want = model.forward_batch_test({"stereo_video": video}, kernel_size=ks, iters=iters)
+    P.install(ppm)
+    try:
+        with torch.no_grad():
+            got = model.forward_batch_test({"stereo_video": video}, kernel_size=ks, iters=iters)
+    finally:
+        P.uninstall(ppm)
+    assert got["disparity"].shape == want["disparity"].shape == (T, 1, H, W)
+    mad = float((got["disparity"].float() - want["disparity"].float()).abs().mean())
+    umad = float((got["uncertainties"].float() - want["uncertainties"].float()).abs().mean())
+    print(f"forward_batch_test 13 frames: mean |d disparity| {mad:.5f} px, uncertainty MAD {umad:.2e}")
+    assert mad <= 0.01
+    assert umad <= 1e-3
+
+
+def test_installed_model_refuses_autograd(env):
+    P, model, ppm = env
+    P.install(ppm)
+    try:
+        video = clip(5, 64, 256, 3)
+        with pytest.raises(RuntimeError, match="inference only"):
+            model(video[None, :, 0].cuda(), video[None, :, 1].cuda(), iters=2, test_mode=True)
+    finally:
+        P.uninstall(ppm)

@@ -308,3 +308,94 @@ def test_frame_major_bf16_value_is_used_in_place(P, shape):
         outs.append((mem.aggregate(t["motion_features"].cuda(), beta), aliased))
     assert outs[0][1] == ((h * w) % 8 == 0) and not outs[1][1]
     assert torch.equal(outs[0][0], outs[1][0])
+
+
+# ------------------------------------------------------------------------------------------------------------
+# The reference's GPU dtype flow (bf16 autocast, ppmstereo.py:617), pinned against the reference's LITERAL torch op
+# sequence executed by torch on the GPU under autocast -- needs no reference code, only torch.  What is pinned:
+#   * `uncertainty_score...mean(-1)` of a bf16 map returns bf16 (mean is not an autocast-fp32 op)  -> conf rounded
+#   * `q_.mean(dim=1)` of the bf16 pooled tensor returns bf16; F.cosine_similarity up-casts          -> pooled rounded
+# ------------------------------------------------------------------------------------------------------------
+def _torch_qam_sequence(sim, strive, unc, b, T, top_k=5):
+    """ppmstereo.py:505-513 verbatim (names shortened), under the reference's autocast."""
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        penality_score = torch.exp(-(strive) / (strive.sum(3, keepdim=True) + T))
+        frame_confidence = unc.reshape(b, 1, 1, T, -1).contiguous().mean(-1)
+        frame_score = penality_score * sim + frame_confidence
+        frame_idx = torch.argsort(frame_score, dim=-1, descending=True)
+        mask = torch.zeros_like(frame_score, dtype=torch.bool).scatter_(3, frame_idx[:, :, :, :top_k], True)
+    return frame_score, frame_confidence, mask
+
+
+@pytest.mark.parametrize("T", [6, 10, 20])
+def test_qam_pick_vs_torch_autocast_sequence_bf16(P, T):
+    """>= 100 seeded cases per T, half of them with frame confidences packed closer than one bf16 ulp (the case
+    an unrounded fp32 mean gets wrong): identical masks, frame_score <= 1e-6."""
+    b, h, w = 1, 23, 40
+    n_cases = n_close = n_checked_rows = 0
+    for seed in range(104):
+        g = torch.Generator(device="cuda").manual_seed(1000 * T + seed)
+        close = seed % 2 == 1
+        if close:      # per-frame means differ by < 2^-9 (bf16 spacing in [0.25, 0.5) is 2^-9)
+            base = 0.3 + 0.0015 * torch.rand(T, 1, 1, 1, generator=g, device="cuda")
+            unc = (base + 0.05 * (torch.rand(T, 1, h, w, generator=g, device="cuda") - 0.5)).bfloat16()
+            sim = (torch.rand(b, 1, T, T, generator=g, device="cuda") * 2 - 1) * 1e-3
+        else:
+            unc = torch.rand(T, 1, h, w, generator=g, device="cuda").bfloat16()
+            sim = torch.rand(b, 1, T, T, generator=g, device="cuda") * 2 - 1
+        strive = torch.ones(b, 1, T, T, device="cuda") + torch.randint(0, 4, (b, 1, T, T), generator=g, device="cuda").float()
+        score, conf, mask = _torch_qam_sequence(sim, strive, unc, b, T)
+        assert conf.dtype == torch.bfloat16 and score.dtype == torch.float32         # the premise of the rule
+        q = torch.zeros(b, 128, T, h, w, device="cuda", dtype=torch.bfloat16)
+        mem = P.PPMMemory(q, q, None, top_k=5)
+        s2 = strive.clone()
+        got = mem.pick(sim, s2, unc)
+        assert float((mem.frame_score - score).abs().max()) <= 1e-6, (T, seed)
+        srt = torch.sort(score, dim=-1, descending=True).values
+        well_posed = (srt[..., 4] != srt[..., 5])[0, 0]        # exact ties are undefined in the reference (unstable argsort)
+        assert torch.equal(got[0, 0][well_posed], mask[0, 0][well_posed]), (T, seed)
+        assert torch.equal(s2[0, 0][well_posed], (strive + mask.float())[0, 0][well_posed])
+        n_cases += 1
+        n_close += int(close)
+        n_checked_rows += int(well_posed.sum())
+    assert n_cases >= 100 and n_close >= 50 and n_checked_rows >= 0.9 * n_cases * T
+
+
+def _torch_similarity_sequence(q, k, t):
+    """PPMStereo.compute_qk_similarity (ppmstereo.py:397-423) verbatim, under the reference's autocast."""
+    import torch.nn as nn
+    import torch.nn.functional as F
+    from einops import rearrange
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        q = rearrange(q, "b c t h w -> (b t) c h w")
+        k = rearrange(k, "b c t h w -> (b t) c h w")
+        bt, channels, height, width = q.shape
+        b = bt // t
+        global_max_pool = nn.AdaptiveMaxPool2d((height // 4, width // 4))
+        q_, k_ = global_max_pool(q), global_max_pool(k)
+        q_, k_ = q_.mean(dim=1).reshape(b, t, -1), k_.mean(dim=1).reshape(b, t, -1)
+        assert q_.dtype == torch.bfloat16
+        sim = F.cosine_similarity(q_.unsqueeze(1), k_.unsqueeze(2), dim=-1).unsqueeze(1)
+    return sim
+
+
+@pytest.mark.parametrize("shape", [(1, 6, 46, 80), (1, 20, 23, 40), (2, 10, 12, 16), (1, 7, 9, 13)])
+def test_similarity_vs_torch_autocast_sequence_bf16(P, shape):
+    b, T, h, w = shape
+    g = torch.Generator(device="cuda").manual_seed(b * 1000 + T * 10 + h)
+    q = torch.randn(b, 128, T, h, w, generator=g, device="cuda").bfloat16()
+    k = (0.5 * q.float() + torch.randn(b, 128, T, h, w, generator=g, device="cuda")).bfloat16()
+    want = _torch_similarity_sequence(q, k, T)
+    assert want.dtype == torch.float32
+    got = P.PPMMemory(q, k, None, top_k=5).similarity()
+    # pooled means are bf16 on both sides; a differing fp32 summation order can flip one of them by one bf16 ulp,
+    # which moves a cosine over >= 12 pooled positions by < 1e-4
+    assert float((got - want).abs().max()) <= 1e-4
+    assert float((got - want).abs().mean()) <= 1e-5
+    # and the rule matters: an unrounded fp32 pooled mean is further away than the tolerance allows at this size
+    from oracle import ppm_oracle as O
+    unrounded = O.qk_similarity(q.float().cpu(), k.float().cpu())
+    rounded = O.qk_similarity(q.cpu(), k.cpu())
+    assert float((rounded - want.cpu()).abs().max()) <= 1e-4
+    print("similarity: |kernel - torch| max %.2e, |fp32-mean oracle - torch| max %.2e" %
+          (float((got - want).abs().max()), float((unrounded - want.cpu()).abs().max())))
