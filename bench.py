@@ -176,13 +176,24 @@ def run_clip(P, inputs, beta, from_host: bool, time_attend: bool = False, runner
 
 
 # --------------------------------------------------------------------------------------------
-# CPU arm: the oracle port of the reference's path on the host cores (bounded sample)
+# CPU arm: the reference's path on the host cores (bounded sample)
+#   kind "reference": the reference's OWN code -- CorrBlock1D.__init__ / __call__ (models/core/corr.py:56-94) and
+#     PPMStereo.forward_update_block (models/core/ppmstereo.py:426-594), imported unmodified from the staged copy
+#     under oracle/_ref (or /root/reference), with the glue modules it calls replaced by constants exactly as this
+#     file's GPU arm replaces them by synthetic tensors, and the CUDA-only flash_attn by the CPU stand-in of
+#     oracle/ref_import.py (the one third-party dependency on the path);
+#   kind "port": oracle/ppm_oracle.py, when no reference tree is available.
 # --------------------------------------------------------------------------------------------
-SAMPLE_DS, SAMPLE_T, SAMPLE_ITERS = 16, KERNEL_SIZE, 5
-SAMPLE_DESC = ("pyramid build + 5 update iterations of the 1/16-res level of a 20-frame 720p window (h x w = 46 x 80, hw = 3680, "
-               "T = 20, K = 5; each iteration = lookup + full PPM read; about 10 s), oracle/ppm_oracle.py (port of the "
-               "reference's PyTorch CPU path) on all host threads; frames/s extrapolated to the 40-frame clip by "
-               "attention FLOPs")
+SAMPLE_DS, SAMPLE_T, SAMPLE_ITERS = 16, KERNEL_SIZE, 2
+SAMPLE_WHAT = ("pyramid build + 2 update iterations of the 1/16-res level of a 20-frame 720p window (h x w = 46 x 80, hw = 3680, "
+               "T = 20, K = 5; each iteration = lookup + full PPM read; about 10-25 s)")
+SAMPLE_DESC = {
+    "reference": SAMPLE_WHAT + ": the reference's own CorrBlock1D + PPMStereo.forward_update_block (unmodified, oracle/_ref) "
+                 "with constant glue outputs and the CPU stand-in for CUDA-only flash_attn, fp32, all host threads; frames/s "
+                 "extrapolated to the 40-frame clip by attention FLOPs",
+    "port": SAMPLE_WHAT + ", oracle/ppm_oracle.py (port of the reference's PyTorch CPU path) on all host threads; frames/s "
+            "extrapolated to the 40-frame clip by attention FLOPs",
+}
 
 
 def make_cpu_sample(seed: int = 0):
@@ -193,10 +204,78 @@ def make_cpu_sample(seed: int = 0):
     flow[:, 0] = torch.rand(T, h, w, generator=g) * -10.0
     return dict(f1=rn(T, D_FEAT, h, w), f2=rn(T, D_FEAT, h, w), q=rn(1, C_QKV, T, h, w), k=rn(1, C_QKV, T, h, w),
                 v=rn(1, C_QKV, T, h, w), mf=rn(1, C_QKV, T, h, w), unc=torch.rand(T, 1, h, w, generator=g),
-                sim=torch.rand(1, 1, T, T, generator=g) * 2 - 1, strive=torch.ones(1, 1, T, T), flow=flow)
+                sim=torch.rand(1, 1, T, T, generator=g) * 2 - 1, strive=torch.ones(1, 1, T, T), flow=flow,
+                up_mask=rn(T, 144, h, w))
 
 
-def cpu_sample_step(s) -> float:
+def cpu_kind() -> str:
+    from oracle import ref_import
+    return "reference" if ref_import.available() else "port"
+
+
+_REF_SHELL = {}
+
+
+def _reference_shell():
+    """The reference's own loop shell + correlation class, bound to constant glue (see the section header)."""
+    if _REF_SHELL:
+        return _REF_SHELL
+    import importlib
+    from oracle import ref_import
+    ref_import.load_reference()
+    ppm = importlib.import_module("models.core.ppmstereo")
+    ppm.flash_attn_func = ref_import._flash_attn_cpu          # the CPU arm always uses the CPU stand-in for flash_attn
+
+    class Shell:                                         # borrows the reference's unbound methods; no parameters needed
+        mixed_precision = False
+        use_convex_3d = False
+        forward_update_block = ppm.PPMStereo.forward_update_block
+        compute_qk_similarity = ppm.PPMStereo.compute_qk_similarity
+        convex_upsample = ppm.PPMStereo.convex_upsample
+
+    _REF_SHELL.update(ppm=ppm, shell=Shell())
+    return _REF_SHELL
+
+
+class _ConstGlue:
+    """Stands where SequenceUpdateBlock3D / Attention_qk stand; returns the sample's constant tensors."""
+
+    def __init__(self, s):
+        T = s["q"].shape[2]
+        self.s = s
+        self.mf = s["mf"][0].permute(1, 0, 2, 3).contiguous()                  # (T, 128, h, w)
+        self.v = s["v"][0].permute(1, 0, 2, 3).contiguous()
+        self.qk = torch.cat([s["q"][0].permute(1, 0, 2, 3), s["k"][0].permute(1, 0, 2, 3)], dim=1).contiguous()
+        self.aggregator = type("Agg", (), {"beta": torch.tensor([0.5])})()
+        self.delta = torch.zeros_like(s["flow"])
+
+    def to_qk(self, inp):
+        return self.qk
+
+    def get_motion_and_value(self, flow, corr, mhs, inp):
+        return self.mf, mhs, self.v
+
+    def get_uncertainty(self, x):
+        return self.s["unc"]
+
+    def __call__(self, net, inp, mf, mfg, t=1):
+        return net, self.s["up_mask"], self.delta
+
+
+def cpu_sample_step(s, kind: str) -> float:
+    if kind == "reference":
+        r = _reference_shell()
+        glue = _ConstGlue(s)
+        T, _, h, w = s["f1"].shape
+        inp = torch.zeros(T, C_QKV, h, w)
+        net = torch.zeros(T, C_QKV, h, w)
+        t0 = time.perf_counter()
+        with torch.no_grad():
+            blk = r["ppm"].CorrBlock1D(s["f1"], s["f2"])
+            r["shell"].forward_update_block(image1=None, update_block=glue, corr_fn=blk, flow=s["flow"], net=net, inp=inp,
+                                            motion_hidden_state=None, attn_block=glue, predictions=[], uncertainties=[],
+                                            iters=SAMPLE_ITERS, interp_scale=4, t=T)
+        return time.perf_counter() - t0
     from oracle import ppm_oracle as O          # the CPU baseline is the one place bench.py runs the oracle
     t0 = time.perf_counter()
     lv = O.corr_pyramid(s["f1"], s["f2"], mode="bf16")
@@ -219,9 +298,10 @@ def run_reference_arm(args, rank: int):
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     s = make_cpu_sample()
-    for _ in range(args.warmup):
-        cpu_sample_step(s)
-    ts = [cpu_sample_step(s) for _ in range(args.steps)]
+    kind = cpu_kind()
+    for _ in range(min(args.warmup, 1)):
+        cpu_sample_step(s, kind)
+    ts = [cpu_sample_step(s, kind) for _ in range(args.steps)]
     sec = sum(ts) / len(ts)
     v = cpu_frames_per_s(sec)
     print(json.dumps({
@@ -229,7 +309,7 @@ def run_reference_arm(args, rank: int):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
         "config": workload_config(args.gpus),
-        "cpu_baseline": {"value": v, "unit": "frames/s", "cores": cores, "kind": "port", "sample": SAMPLE_DESC},
+        "cpu_baseline": {"value": v, "unit": "frames/s", "cores": cores, "kind": kind, "sample": SAMPLE_DESC[kind]},
         "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }))
@@ -416,10 +496,11 @@ def main():
             cores = os.cpu_count() or 1
             torch.set_num_threads(cores)
             s = make_cpu_sample()
-            cpu_sample_step(s)
-            sec = min(cpu_sample_step(s) for _ in range(2))
+            kind = cpu_kind()
+            cpu_sample_step(s, kind)
+            sec = cpu_sample_step(s, kind)
             out["cpu_baseline"] = {"value": cpu_frames_per_s(sec), "unit": "frames/s", "cores": cores,
-                                   "kind": "port", "sample": SAMPLE_DESC, "sample_seconds": sec}
+                                   "kind": kind, "sample": SAMPLE_DESC[kind], "sample_seconds": sec}
         print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()

@@ -112,8 +112,10 @@ def run_clip(model, ppm, video, kernel_size: int, iters: int, installed: bool, s
              repeats: int = 1) -> Dict:
     """One (or ``repeats``) forward_batch_test over ``video`` (T,2,3,H,W host tensor).  Returns frames/s by device
     events and by wall clock, the phase split in ms per clip, and the result (host)."""
+    import importlib
     import ppmstereo_b200 as P
-    from ppmstereo_b200 import install as inst, memory as mem_mod
+    inst = importlib.import_module("ppmstereo_b200.install")       # (the package attribute `install` is the function)
+    mem_mod = importlib.import_module("ppmstereo_b200.memory")
     if installed:
         P.install(ppm)
     else:

@@ -103,7 +103,27 @@ class CorrBlock1D:
         self._w2 = fmap2.shape[3]
         self._grid = (B, H, W1, fmap1.device)
         self._coords = None
-        self.corr_pyramid = build_pyramid(fmap1.detach(), fmap2.detach(), num_levels)
+        # The lookup the model performs (4 levels, r = 4, bf16 pyramid) reads level 0 only (K2b rebuilds the pooled
+        # taps in registers, bit-identically).  Levels 1-4 -- 48 % of the pyramid's bytes -- are then written for
+        # nobody: build level 0 now and the pooled levels only if someone asks for `corr_pyramid`.
+        self._l0_only = (num_levels == 4 and radius == 4 and fmap1.dtype == torch.bfloat16 and self._w2 % 8 == 0)
+        if self._l0_only:
+            self._level0 = build_pyramid(fmap1.detach(), fmap2.detach(), 0)[0]
+            self._l0_only = self._level0.data_ptr() % 32 == 0
+        self._pyramid = None if self._l0_only else self._full_pyramid(fmap1, fmap2)
+        self._fmaps = (fmap1.detach(), fmap2.detach()) if self._l0_only else None
+
+    def _full_pyramid(self, fmap1, fmap2) -> List[torch.Tensor]:
+        return build_pyramid(fmap1.detach(), fmap2.detach(), self.num_levels)
+
+    @property
+    def corr_pyramid(self) -> List[torch.Tensor]:
+        """The reference's attribute: num_levels + 1 tensors (B*H*W1, 1, 1, W2 >> l); pooled levels are materialised
+        on first access (same kernel, same rounding: level 0 is rewritten with identical bits)."""
+        if self._pyramid is None:
+            self._pyramid = self._full_pyramid(*self._fmaps)
+            self._level0 = self._pyramid[0]
+        return self._pyramid
 
     @property
     def coords(self) -> torch.Tensor:
@@ -116,11 +136,9 @@ class CorrBlock1D:
         return self._coords
 
     def __call__(self, flow: torch.Tensor) -> torch.Tensor:
-        lv = self.corr_pyramid
-        if (self.num_levels == 4 and self.radius == 4 and lv[0].dtype == torch.bfloat16 and self._w2 % 8 == 0
-                and lv[0].data_ptr() % 32 == 0):
-            return lookup_l0(lv[0], flow.detach(), self._w2)           # K2b: all levels from one level-0 span
-        return lookup(lv, flow.detach(), self._w2, self.radius, self.num_levels)
+        if self._l0_only:
+            return lookup_l0(self._level0, flow.detach(), self._w2)    # K2b: all levels from one level-0 span
+        return lookup(self.corr_pyramid, flow.detach(), self._w2, self.radius, self.num_levels)
 
     @staticmethod
     def corr(fmap1: torch.Tensor, fmap2: torch.Tensor) -> torch.Tensor:

@@ -222,3 +222,28 @@ def test_build_cluster_path_tf32_inputs(P, shape, out_dtype):
         assert rel(got[:, a:b], want[:, a:b]) <= tol, (a, b, rel(got[:, a:b], want[:, a:b]))
     for l in range(5):
         assert bool(torch.isfinite(lv[l].float()).all()), l
+
+
+def test_block_at_headline_shape_sampled_pixels_vs_oracle(P):
+    """(20, 256, 184, 320) bf16 through CorrBlock1D.__init__ / __call__ -- the route the model takes (K1, then the
+    level-0-span lookup K2b) -- against O.corr_pyramid(mode="bf16") + O.corr_lookup on 96 sampled image rows."""
+    g = torch.Generator(device="cuda").manual_seed(31)
+    B, D, H, W = 20, 256, 184, 320
+    f1 = torch.randn(B, D, H, W, generator=g, device="cuda").bfloat16()
+    f2 = torch.randn(B, D, H, W, generator=g, device="cuda").bfloat16()
+    flow = torch.zeros(B, 2, H, W, device="cuda")
+    flow[:, 0] = torch.rand(B, H, W, generator=g, device="cuda") * -60.0 + 10.0      # incl. taps left of the row
+    blk = P.CorrBlock1D(f1, f2)
+    out = blk(flow)
+    assert out.shape == (B, 36, H, W) and out.dtype == torch.float32
+    rows = torch.randperm(B * H, generator=torch.Generator().manual_seed(32))[:96].tolist() + [0, B * H - 1]
+    for r in rows:
+        b, h = divmod(r, H)
+        lv = O.corr_pyramid(f1[b:b + 1, :, h:h + 1].float().cpu(), f2[b:b + 1, :, h:h + 1].float().cpu(), mode="bf16")
+        want = O.corr_lookup(lv, flow[b:b + 1, :, h:h + 1].cpu())
+        got = out[b:b + 1, :, h:h + 1].cpu()
+        # bf16 volume entries: the tensor-core accumulation order differs from the oracle's matmul, which flips a
+        # rare bf16 rounding (one ulp = 2^-8 relative of an O(1) entry); everything else is exact lerp arithmetic
+        assert float((got - want).abs().max()) <= 2.0 ** -6, r
+        assert float((got - want).abs().mean()) <= 1e-4, r
+        assert rel(got, want) <= 1e-3, r

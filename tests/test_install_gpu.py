@@ -103,7 +103,8 @@ def test_installed_model_matches_reference_disparity(env, T, H, W, iters):
     P.uninstall(ppm)
     with ref_import.MemoryReadRecorder(model, T) as rec:
         d_ref, u_ref = run_forward(model, video, iters)
-    ref_masks = [t["mask"] for _, _, t in rec.reads(iters)]
+    ref_reads = [t for _, _, t in rec.reads(iters)]
+    ref_masks = [t["mask"] for t in ref_reads]
     d_ref2, _ = run_forward(model, video, iters)                        # run-to-run noise floor of the reference
     P.install(ppm)
     got_masks = []
@@ -133,7 +134,18 @@ def test_installed_model_matches_reference_disparity(env, T, H, W, iters):
     assert mad <= 0.01, mad                                             # north_star: final disparity within 0.01 px
     assert umad <= 1e-3
     assert same[0]                                                      # same inputs -> same pick
-    assert sum(same) >= 0.9 * len(same)                                 # trajectories may drift apart by rounding only
+    # Free-running, the two trajectories differ by bf16 rounding (attention output, then every conv after it), so
+    # the uncertainty maps -- and with them the bf16 frame confidences, one ulp = 2e-3..4e-3 -- drift apart.  A pick
+    # may therefore differ ONLY in rows where the reference's own 5th / 6th scores are closer than that drift; the
+    # bit-exact claim proper (identical inputs -> identical masks) is test_teacher_forced_memory_reads.
+    for it, ok in enumerate(same):
+        if ok or T <= 5:
+            continue
+        srt = torch.sort(ref_reads[it]["frame_score"], dim=-1, descending=True).values
+        gap = (srt[..., 4] - srt[..., 5])[0, 0]
+        rows = (got_masks[it] != ref_masks[it]).any(-1)[0, 0]
+        assert float(gap[rows].max()) <= 8e-3, (it, gap[rows])
+    assert sum(same) >= 0.5 * len(same)
 
 
 def test_forward_batch_test_window_scheduler_vs_reference_loop(env):

@@ -399,3 +399,68 @@ def test_similarity_vs_torch_autocast_sequence_bf16(P, shape):
     assert float((rounded - want.cpu()).abs().max()) <= 1e-4
     print("similarity: |kernel - torch| max %.2e, |fp32-mean oracle - torch| max %.2e" %
           (float((got - want).abs().max()), float((unrounded - want.cpu()).abs().max())))
+
+
+# ------------------------------------------------------------------------------------------------------------
+# The shape the roofline and frames/s are quoted on: 720p 1/4 res, hw = 58 880, T = 20, K = 5
+# ------------------------------------------------------------------------------------------------------------
+def test_headline_shape_sampled_rows_vs_oracle(P):
+    """256 sampled query rows per frame against O.ppm_memory_read(rows=...) on the full (b, 128, 20, 184, 320)
+    operands in the autocast dtypes (bf16 q / k / value / uncertainty)."""
+    b, T, h, w = 1, 20, 184, 320
+    g = torch.Generator(device="cuda").manual_seed(2024)
+    rn = lambda *s: torch.randn(*s, generator=g, device="cuda")
+    t = {"query": rn(b, 128, T, h, w).bfloat16(), "key": rn(b, 128, T, h, w).bfloat16(),
+         "value": rn(b, 128, T, h, w).bfloat16(), "motion_features": rn(b, 128, T, h, w),
+         "uncertainty": torch.rand(b * T, 1, h, w, generator=g, device="cuda").bfloat16(),
+         "sim": torch.rand(b, 1, T, T, generator=g, device="cuda") * 2 - 1,
+         "strive_before": torch.ones(b, 1, T, T, device="cuda")}
+    rows = torch.randperm(h * w, generator=torch.Generator().manual_seed(5))[:256].sort().values
+    rows = torch.cat([torch.tensor([0, 127, 128, h * w - 129, h * w - 128, h * w - 1]), rows]).unique()
+    mem = P.PPMMemory(t["query"], t["key"], None, top_k=5)
+    strive = t["strive_before"].clone()
+    out, mask = mem.read(t["value"], t["motion_features"], t["sim"], strive, t["uncertainty"],
+                         torch.tensor([0.5], device="cuda"))
+    torch.cuda.synchronize()
+    cpu = {k: v.cpu() for k, v in t.items()}
+    want = O.ppm_memory_read(cpu["query"], cpu["key"], O.temporal_pe(T, 128), cpu["value"], cpu["motion_features"],
+                             cpu["sim"], cpu["strive_before"], cpu["uncertainty"], 0.5, rows=rows)
+    assert float((mem.frame_score.cpu() - want["frame_score"]).abs().max()) <= 2e-6
+    assert torch.equal(mask.cpu(), want["mask"])
+    assert torch.equal(mem.picked.cpu().long(), want["picked"])
+    got = out.reshape(b, T, 128, h * w)[..., rows.cuda()].cpu()
+    ref = want["motion_features_global"].reshape(b, T, 128, h * w)[..., rows]
+    hmax = float(want["hidden"][..., rows].abs().max())
+    d = (got - ref).abs()
+    assert float(d.max()) <= 3e-2 * hmax + 1e-6, (float(d.max()), hmax)
+    assert float(d.mean()) <= 3e-3 * hmax + 1e-7
+    # pixels outside `rows` of the oracle output equal motion_features; of ours they must differ (computed)
+    assert torch.isfinite(out).all()
+
+
+def test_headline_shape_one_query_frame_vs_flash_attn(P):
+    """One full query frame (Lq = 58 880, Lk = 294 400) against flash_attn_func, the reference's call at
+    ppmstereo.py:550, fed the SAME packed bf16 operands."""
+    fa = pytest.importorskip("flash_attn")
+    b, T, h, w, K = 1, 20, 184, 320, 5
+    hw = h * w
+    g = torch.Generator(device="cuda").manual_seed(2025)
+    rn = lambda *s: torch.randn(*s, generator=g, device="cuda")
+    q, k, v = rn(b, 128, T, h, w).bfloat16(), rn(b, 128, T, h, w).bfloat16(), rn(b, 128, T, h, w).bfloat16()
+    mf = torch.zeros(b, 128, T, h, w, device="cuda")
+    unc = torch.rand(b * T, 1, h, w, generator=g, device="cuda").bfloat16()
+    sim = torch.rand(b, 1, T, T, generator=g, device="cuda") * 2 - 1
+    mem = P.PPMMemory(q, k, None, top_k=K)
+    mem.pick(sim, torch.ones_like(sim), unc)
+    out = mem.attend(v, mf, torch.tensor([1.0], device="cuda"))            # mf = 0, beta = 1 -> out = hidden
+    for i in (0, 13):
+        qi = mem.q_packed.view(T, hw, 128)[i][None, :, None, :]
+        ki = mem.k_packed.view(T, K, hw, 128)[i].reshape(1, K * hw, 1, 128)
+        picked = mem.picked[0, i].long()
+        vi = v[0][:, picked].permute(1, 2, 3, 0).reshape(1, K * hw, 1, 128).contiguous()
+        ref = fa.flash_attn_func(qi, ki, vi, dropout_p=0.0, softmax_scale=P.softmax_scale(128), causal=False).float()
+        got = out[i].reshape(128, hw).t()
+        d = (got - ref[0, :, 0]).abs()
+        hmax = float(ref.abs().max())
+        assert float(d.max()) <= 2e-2 * hmax, (i, float(d.max()), hmax)     # one bf16 ulp of the output
+        assert float(d.mean()) <= 2e-3 * hmax
