@@ -182,9 +182,10 @@ def test_similarity_vs_oracle_adaptive_windows(P, shape, dtype):
     g = torch.Generator().manual_seed(h * 100 + w)
     q = torch.randn(b, 128, T, h, w, generator=g).to(dtype)
     k = torch.randn(b, 128, T, h, w, generator=g).to(dtype)
-    want = O.qk_similarity(q.float(), k.float())
+    want = O.qk_similarity(q, k)                    # dtype rule: bf16 inputs -> bf16-rounded pooled means
     got = P.PPMMemory(q.cuda(), k.cuda(), None).similarity().cpu()
-    assert float((got - want).abs().max()) <= 1e-5
+    # (bf16: a pooled mean at a rounding boundary may flip by one bf16 ulp between the two fp32 summation orders)
+    assert float((got - want).abs().max()) <= (1e-5 if dtype == torch.float32 else 2e-4)
     again = P.PPMMemory(q.cuda(), k.cuda(), None).similarity().cpu()
     assert torch.equal(got, again)                        # deterministic: it feeds the top-k pick
 
