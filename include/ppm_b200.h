@@ -106,6 +106,21 @@ PPM_API int ppm_qam_pick(const float* sim, float* strive, const void* uncertaint
                  float* score_norm, uint8_t* mask, float* conf_ws, void* stream);
 
 /* ---------------------------------------------------------------------------------------
+ * K3a, allocation-free variant.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc or provide scratch (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid allocation).  Same arithmetic, arguments and results as ppm_qam_pick, minus `conf_ws`: the
+ * frame-confidence scratch is a static device array inside the library (PPM_QAM_STATIC_MAX_FRAMES floats = 16 KB,
+ * held by every GPU that loads the library until the process exits).  Calls no cudaMalloc / cudaFree / allocating
+ * routine.  b*T > PPM_QAM_STATIC_MAX_FRAMES is rejected with PPM_ERR_UNSUPPORTED and a message naming the limit.
+ * All calls on one device share the array (it keeps the last call's contents; nothing in it needs to start at zero:
+ * each call overwrites the b*T entries it then reads).  Calls that OVERLAP on the GPU (different streams without
+ * ordering) race on it -- serialise them, or use ppm_qam_pick with per-caller conf_ws. */
+#define PPM_QAM_STATIC_MAX_FRAMES 4096
+PPM_API int ppm_qam_pick_static(const float* sim, float* strive, const void* uncertainty, int unc_dtype, int b,
+                 int T, int hw, int top_k, float* frame_score, int32_t* picked,
+                 float* score_norm, uint8_t* mask, void* stream);
+
+/* ---------------------------------------------------------------------------------------
  * K3b  operand packing for the memory read (models/core/ppmstereo.py:518-548).
  * Source tensors are indexed src[b*sb + c*sc + t*st + p] (element strides, pixel stride 1),
  * c = 128 channels, dtype src_dtype.

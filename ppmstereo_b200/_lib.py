@@ -27,6 +27,8 @@ SIGNATURES = {
                                   c_void_p, c_void_p, c_void_p]),
     "ppm_qam_pick": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p,
                              c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "ppm_qam_pick_static": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p,
+                                    c_void_p, c_void_p, c_void_p, c_void_p]),
     "ppm_pack_query": (c_int, [c_void_p, c_int, c_int64, c_int64, c_int64, c_void_p, c_int, c_int, c_int,
                                c_void_p, c_void_p]),
     "ppm_pack_key": (c_int, [c_void_p, c_int, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_int,

@@ -3,6 +3,7 @@
 // :518-548 (query + PE, masked_select gather, "play" modulation, flatten/permute/cast).
 // All HBM-bound helper kernels; together ~0.5 % of the memory-read time at 720p.
 #include <math.h>
+#include <mutex>
 
 #include "../../include/ppm_b200.h"
 #include "common.cuh"
@@ -215,6 +216,71 @@ extern "C" int ppm_qam_pick(const float* sim, float* strive, const void* uncerta
   PPM_CUDA(cudaGetLastError());
   qam_pick_kernel<<<1, 256, static_cast<size_t>(b) * T * top_k * 4, st>>>(sim, strive, conf_ws, b, T, top_k,
                                                                             frame_score, picked, score_norm, mask);
+  PPM_CUDA(cudaGetLastError());
+  return PPM_OK;
+}
+
+// ------------------------------------------------------------------ allocation-free variant of ppm_qam_pick
+// No counterpart in the reference: added for callers that cannot provide (or
+// allocate) the `conf_ws` scratch -- code under CUDA graph capture, tight serving loops, harnesses that forbid
+// cudaMalloc.  The frame-confidence scratch lives in a file-scope device array of PPM_QAM_STATIC_MAX_FRAMES floats
+// (16 KB; every GPU that loads the library holds it until exit).  In HOST code the array's name is a host-side
+// stand-in, not a device address: its device address is taken once per device with cudaGetSymbolAddress (that device
+// current) and THAT pointer is handed to the kernels.  Nothing in the array has to start at zero: frame_mean_kernel
+// overwrites conf[0 .. b*T) before qam_pick_kernel reads exactly that range, so the previous call's contents (which
+// the array keeps) are never observed.  Every call shares the one array per device: calls that overlap on the GPU
+// (different streams, no ordering between them) race on it.
+namespace ppm {
+
+static __device__ __align__(256) float g_qam_conf_scratch[PPM_QAM_STATIC_MAX_FRAMES];
+
+constexpr int kQamMaxDevices = 64;
+
+static int qam_static_scratch(float** out) {
+  static std::mutex mu;
+  static float* addr[kQamMaxDevices] = {};
+  int dev = -1;
+  PPM_CUDA(cudaGetDevice(&dev));
+  PPM_CHECK(dev >= 0 && dev < kQamMaxDevices, PPM_ERR_UNSUPPORTED, "ppm_qam_pick_static: device ordinal %d >= %d", dev,
+            kQamMaxDevices);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!addr[dev]) {                                     // set-up, once per device, with that device current
+    void* p = nullptr;
+    PPM_CUDA(cudaGetSymbolAddress(&p, g_qam_conf_scratch));
+    PPM_CHECK(p != nullptr, PPM_ERR_CUDA, "ppm_qam_pick_static: cudaGetSymbolAddress returned a null address");
+    addr[dev] = static_cast<float*>(p);
+  }
+  *out = addr[dev];
+  return PPM_OK;
+}
+
+}  // namespace ppm
+
+extern "C" int ppm_qam_pick_static(const float* sim, float* strive, const void* uncertainty, int unc_dtype, int b,
+                                   int T, int hw, int top_k, float* frame_score, int32_t* picked,
+                                   float* score_norm, uint8_t* mask, void* stream) {
+  PPM_CHECK(sim && strive && uncertainty && frame_score && picked && score_norm, PPM_ERR_ARG,
+            "ppm_qam_pick_static: null pointer");
+  PPM_CHECK(b > 0 && T > 0 && hw > 0 && top_k > 0, PPM_ERR_ARG, "ppm_qam_pick_static: bad shape");
+  PPM_CHECK(static_cast<long long>(b) * T <= PPM_QAM_STATIC_MAX_FRAMES, PPM_ERR_UNSUPPORTED,
+            "ppm_qam_pick_static: b*T = %lld frames exceeds the static scratch of %d frames "
+            "(PPM_QAM_STATIC_MAX_FRAMES); use ppm_qam_pick with a caller-provided conf_ws",
+            static_cast<long long>(b) * T, PPM_QAM_STATIC_MAX_FRAMES);
+  PPM_CHECK(T <= 64, PPM_ERR_UNSUPPORTED, "ppm_qam_pick_static: T = %d > 64", T);
+  PPM_CHECK(top_k <= 16, PPM_ERR_UNSUPPORTED, "ppm_qam_pick_static: top_k = %d > 16", top_k);
+  PPM_CHECK(static_cast<size_t>(b) * T * top_k * 4 <= 48 * 1024, PPM_ERR_UNSUPPORTED,
+            "ppm_qam_pick_static: b*T*top_k too large");
+  PPM_CHECK(unc_dtype == PPM_F32 || unc_dtype == PPM_BF16, PPM_ERR_ARG, "ppm_qam_pick_static: bad dtype");
+  float* conf = nullptr;
+  if (int rc = qam_static_scratch(&conf)) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (unc_dtype == PPM_BF16)
+    frame_mean_kernel<__nv_bfloat16><<<b * T, 512, 0, st>>>(static_cast<const __nv_bfloat16*>(uncertainty), hw, conf);
+  else
+    frame_mean_kernel<float><<<b * T, 512, 0, st>>>(static_cast<const float*>(uncertainty), hw, conf);
+  PPM_CUDA(cudaGetLastError());
+  qam_pick_kernel<<<1, 256, static_cast<size_t>(b) * T * top_k * 4, st>>>(sim, strive, conf, b, T, top_k, frame_score,
+                                                                            picked, score_norm, mask);
   PPM_CUDA(cudaGetLastError());
   return PPM_OK;
 }
