@@ -334,6 +334,10 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="profiling aid: skip the host-buffer pass")
     ap.add_argument("--no-same-box", action="store_true", help="profiling aid: skip the flash_attn comparison")
+    ap.add_argument("--full-model", action="store_true",
+                    help="also run the whole model (PPMStereo.forward_batch_test, BASELINE configs[3]) on this GPU, the "
+                         "reference's own stack vs ppmstereo_b200.install(), with a phase split: extra key `full_model` "
+                         "(adds ~5 min; needs the staged reference under oracle/_ref)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -390,6 +394,73 @@ def main():
     if not args.no_e2e:
         run_clip(P, inputs, beta, True, False, runner)   # warm the pinned-copy path once
         ms_e2e, _ = timed(True, args.steps, False)
+
+    # ---- N >= 2 only: the optional splits of ONE clip; the weak-scaling line above stays the headline
+    multi = None
+    if world > 1:
+        multi = {"rowband_bit_exact": bool(P.rowband.verify_against_full_read(dev))}
+        # (a) strong scaling by temporal windows: the 4 windows of one clip are independent (ppmstereo.py:277-307),
+        #     LPT-assigned to min(N, 4) ranks by attention FLOPs; no exchange; time = max over ranks
+        wins = clip_windows()
+        hw_l = [(PAD_H // ds) * (PAD_W // ds) for ds, _ in LEVELS]
+        costs = [P.shard.window_cost(T, hw_l, [it for _, it in LEVELS]) for T in wins]
+        owned = P.shard.assign_balanced(costs, min(world, len(wins)))
+        mine = owned[rank] if rank < len(owned) else []
+
+        def one_clip_by_windows():
+            for wi in mine:
+                for ds, iters in LEVELS:
+                    run_level(P, inputs[(wins[wi], ds)].dev, iters, beta, False)
+
+        one_clip_by_windows()
+        barrier()
+        a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        one_clip_by_windows()
+        b_.record()
+        barrier()
+        _, ms_w = P.shard.reduce_throughput(0, a.elapsed_time(b_), device=dev)
+        multi["one_clip_window_split"] = {
+            "scaling": "strong", "ranks_used": len(owned), "windows_per_rank": [[wins[i] for i in o] for o in owned],
+            "ms_per_clip": ms_w, "frames_per_s": CLIP_FRAMES / (ms_w * 1e-3),
+            "speedup_vs_1gpu": ms_step / ms_w,
+            "note": "hot path of ONE 40-frame clip, windows [20,20,20,10] LPT-assigned by attention FLOPs; no collective; "
+                    "ceiling 3.5x (the largest share is one 20-frame window of 3.5 window-equivalents)"}
+        # (b) row-band split of one window's memory read at the 1/4 level: per iteration the value + uncertainty bands
+        #     are all-gathered (NCCL), the pick is replicated, every rank aggregates its band's queries
+        x = inputs[(KERNEL_SIZE, 4)].dev
+        h4 = PAD_H // 4
+        r0, r1 = P.row_bands(h4, world)[rank]
+        band = P.RowBandMemory(x["query"], x["key"], None, top_k=TOP_K)
+        vb = x["value"][:, :, :, r0:r1].contiguous()
+        mb = x["mf"][:, :, :, r0:r1].contiguous()
+        ub = x["unc"][:, :, r0:r1].contiguous()
+        strive = torch.ones_like(x["sim"])
+
+        def timed_ms(fn, reps=3):
+            fn()
+            barrier()
+            e = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+            e[0].record()
+            for _ in range(reps):
+                fn()
+            e[1].record()
+            barrier()
+            return P.shard.reduce_throughput(0, e[0].elapsed_time(e[1]) / reps, device=dev)[1]
+
+        ms_band = timed_ms(lambda: band.read(vb, mb, x["sim"], strive, ub, beta))
+        ms_gather = timed_ms(lambda: (P.gather_bands(vb, h4, 3), P.gather_bands(ub, h4, 2)))
+        full = P.PPMMemory(x["query"], x["key"], None, top_k=TOP_K)
+        ms_full = timed_ms(lambda: full.read(x["value"], x["mf"], x["sim"], strive, x["unc"], beta))
+        multi["rowband_memory_read"] = {
+            "scaling": "strong", "level": "1/4 res, T=20, hw=58880, K=5", "ms_per_iteration_1gpu": ms_full,
+            "ms_per_iteration_banded": ms_band, "speedup": ms_full / ms_band, "ideal": float(world),
+            "allgather_ms": ms_gather, "allgather_bytes": int(x["value"].numel() * 2 + x["unc"].numel() * 2),
+            "collective": "NCCL all_gather_into_tensor of the bf16 value bands (+ uncertainty bands) per iteration; "
+                          "it is the only exchange of the split and is not overlapped with the attention",
+            "note": "memory read only: the PyTorch glue convolutions have no halo exchange (out of scope), so a whole "
+                    "clip is split by windows, (a), not by bands"}
+        del band, full, vb, mb, ub
 
     def time_kernel(fn, reps=10, rounds=5):
         """Kernel duration free of the host launch path: `reps` back-to-back launches captured in one CUDA
@@ -492,6 +563,9 @@ def main():
             "roofline_other_kernels": other,
             "same_box_reference_attention": same_box,
         }
+        if multi is not None:
+            out["one_clip_splits"] = multi
+            out["rowband_bit_exact"] = multi["rowband_bit_exact"]
         if not args.no_cpu_baseline and world == 1:           # the CPU arm is timed on rank 0 at N = 1 only
             cores = os.cpu_count() or 1
             torch.set_num_threads(cores)
@@ -501,6 +575,19 @@ def main():
             sec = cpu_sample_step(s, kind)
             out["cpu_baseline"] = {"value": cpu_frames_per_s(sec), "unit": "frames/s", "cores": cores,
                                    "kind": kind, "sample": SAMPLE_DESC[kind], "sample_seconds": sec}
+        if args.full_model and world == 1:
+            # Whole model (BASELINE configs[3]; SURVEY 8d brackets PPMStereoModel.forward): the reference's own network
+            # code is the host application here (encoders, GRU glue, loop shells -- unmodified, staged under oracle/_ref),
+            # run (a) with its own einsum / grid_sample / flash_attn stack and (b) after ppmstereo_b200.install().  The
+            # loader lives in oracle/ because it imports the reference; no arithmetic of the product path comes from it.
+            del inputs
+            torch.cuda.empty_cache()
+            from oracle import full_model, ref_import
+            if ref_import.available():
+                fm = full_model.measure(CLIP_FRAMES, 720, 1280, KERNEL_SIZE, ITERS, reference=True)
+                out["full_model"] = fm
+            else:
+                out["full_model"] = {"unavailable": "reference sources not staged under oracle/_ref (python oracle/stage_ref.py)"}
         print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()

@@ -172,7 +172,8 @@ def synthetic_clip(frames: int, H: int, W: int, seed: int = 3, pinned: bool = Tr
 
 
 def measure(frames: int = 40, H: int = 720, W: int = 1280, kernel_size: int = 20, iters: int = 20,
-            reference: bool = True, warmup: int = 1, split: bool = True, model_and_ppm=None) -> Dict:
+            reference: bool = True, warmup: int = 1, split: bool = True, model_and_ppm=None,
+            reference_warmup: int = 0) -> Dict:
     """BASELINE configs[3]: rand(40,2,3,720,1280)*255, ks 20, iters 20, bf16 autocast, one GPU."""
     model, ppm = model_and_ppm if model_and_ppm is not None else build()
     video = synthetic_clip(frames, H, W)
@@ -181,7 +182,7 @@ def measure(frames: int = 40, H: int = 720, W: int = 1280, kernel_size: int = 20
                                                  "beta=0.5, temporal_fc~N(0,0.02)"}}
     arms = [("installed", True)] + ([("reference", False)] if reference else [])
     for name, inst in arms:
-        for _ in range(warmup):
+        for _ in range(warmup if inst else reference_warmup):
             run_clip(model, ppm, video, kernel_size, iters, installed=inst, split=False)
         plain = run_clip(model, ppm, video, kernel_size, iters, installed=inst, split=False)
         r = run_clip(model, ppm, video, kernel_size, iters, installed=inst, split=split) if split else plain

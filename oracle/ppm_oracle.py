@@ -344,3 +344,59 @@ def convex_upsample(flow: torch.Tensor, mask: torch.Tensor, rate: int = 4) -> to
         nb = fp[:, :, ky:ky + H, kx:kx + W]                                       # (N,2,H,W) neighbour k
         out += w[:, k][:, None] * nb[:, :, None, None]
     return out.permute(0, 1, 4, 2, 5, 3).reshape(N, 2, rate * H, rate * W)
+
+
+# ---------------------------------------------------------------------------------------------
+# SKSepConvGRU3D (models/core/ppmtereo_update.py:254-312) -- SURVEY 8f rank 2
+# ---------------------------------------------------------------------------------------------
+def _sep_conv(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor, axis: int, rnd) -> torch.Tensor:
+    """1-D convolution of a (b, C, T, H, W) tensor along ``axis`` (2 = T, 3 = H, 4 = W), zero padding (k-1)/2, written
+    as a sum of shifted channel contractions: out[p] = bias + sum_d W_d . in[p + d - (k-1)/2]  -- what nn.Conv3d with a
+    (k,1,1) / (1,k,1) / (1,1,k) kernel computes (ppmtereo_update.py:257-289).  weight: (Cout, Cin, kt, kh, kw) with a
+    single non-unit kernel dim.  ``rnd`` rounds operands and the result (identity in fp32 mode, bf16 in autocast mode:
+    conv3d is an autocast-to-bf16 op -- input, weight and bias are cast to bf16, fp32 accumulation, bf16 result)."""
+    k = weight.shape[axis]
+    w = rnd(weight.float()).reshape(weight.shape[0], weight.shape[1], k)            # (Cout, Cin, k)
+    xin = rnd(x.float())
+    pad = (k - 1) // 2
+    n = x.shape[axis]
+    out = torch.zeros(x.shape[0], weight.shape[0], *x.shape[2:])
+    for d in range(k):
+        lo, hi = max(0, pad - d), min(n, n + pad - d)          # output positions whose tap d falls inside the tensor
+        if hi <= lo:
+            continue
+        src = xin.narrow(axis, lo + d - pad, hi - lo)
+        out.narrow(axis, lo, hi - lo).add_(torch.einsum("oc,bcthw->bothw", w[:, :, d], src))
+    return rnd(out + rnd(bias.float()).view(1, -1, 1, 1, 1))
+
+
+def sk_sep_conv_gru3d(h: torch.Tensor, x: torch.Tensor, params: dict, mode: str = "fp32") -> torch.Tensor:
+    """SKSepConvGRU3D.forward(h, x) (ppmtereo_update.py:291-312).  h (b,128,T,H,W), x (b,384,T,H,W); ``params`` maps
+    the module's state-dict names ('convz1.0.weight', ..., 'convq3.bias') to tensors.
+
+    mode "fp32": the reference's CPU arithmetic.
+    mode "bf16": the reference's GPU arithmetic under autocast (ppmstereo.py:568): every conv3d runs in bf16 (operands
+      and result rounded, fp32 accumulation); gelu / sigmoid / tanh of a bf16 tensor return bf16; the products and sums
+      of the gate (r*h, (1-z)*h, z*q, their sum) are bf16 ops when h is bf16 -- each rounds once.  h is rounded to bf16
+      on entry in this mode (the model hands over a bf16 hidden state: tanh under autocast, ppmstereo.py:631)."""
+    rnd = bf16_round if mode == "bf16" else (lambda t: t)
+    gelu = torch.nn.functional.gelu
+    p = params
+    h = rnd(h.float())
+    x = x.float()
+    for stage, axis in ((1, 4), (2, 3), (3, 2)):                                   # horizontal, vertical, time
+        hx = torch.cat([h, x], dim=1)
+        if stage == 1:
+            z = _sep_conv(rnd(gelu(_sep_conv(hx, p["convz1.0.weight"], p["convz1.0.bias"], axis, rnd))),
+                          p["convz1.2.weight"], p["convz1.2.bias"], axis, rnd)
+            r = _sep_conv(rnd(gelu(_sep_conv(hx, p["convr1.0.weight"], p["convr1.0.bias"], axis, rnd))),
+                          p["convr1.2.weight"], p["convr1.2.bias"], axis, rnd)
+        else:
+            z = _sep_conv(hx, p[f"convz{stage}.weight"], p[f"convz{stage}.bias"], axis, rnd)
+            r = _sep_conv(hx, p[f"convr{stage}.weight"], p[f"convr{stage}.bias"], axis, rnd)
+        z, r = rnd(torch.sigmoid(z)), rnd(torch.sigmoid(r))
+        rh = rnd(r * h)
+        q = rnd(torch.tanh(_sep_conv(torch.cat([rh, x], dim=1), p[f"convq{stage}.weight"], p[f"convq{stage}.bias"],
+                                     axis, rnd)))
+        h = rnd(rnd(rnd(1 - z) * h) + rnd(z * q))
+    return h

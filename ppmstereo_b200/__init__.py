@@ -19,6 +19,7 @@ from .upsample import convex_upsample
 from .rowband import RowBandMemory, gather_bands, row_bands
 from .window import FrameFeatureCache, forward_batch_test
 from . import window
+from . import rowband
 
 __all__ = ["CorrBlock1D", "build_pyramid", "lookup", "lookup_l0", "PPMMemory", "ppm_memory_read", "softmax_scale",
            "temporal_pe_table", "install", "uninstall", "forward_update_block", "StagedRunner", "shard", "convex_upsample", "RowBandMemory", "gather_bands", "row_bands",

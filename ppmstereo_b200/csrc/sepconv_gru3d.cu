@@ -1,0 +1,313 @@
+// K5: SKSepConvGRU3D -- the recurrent unit of SequenceUpdateBlock3D.
+// Replaces SKSepConvGRU3D.forward (reference models/core/ppmtereo_update.py:254-312), called once per update iteration
+// from SequenceUpdateBlock3D.forward (:971-1003).  Three gated stages, each a set of 1-D convolutions over ONE axis of a
+// (b, C, T, H, W) tensor (W with 15- and 5-tap kernels, then H and T with 5 taps), C = 128 hidden + 384 input channels:
+//     z = sigmoid(convz(cat[h, x]));  r = sigmoid(convr(cat[h, x]));  q = tanh(convq(cat[r*h, x]));  h = (1-z)*h + z*q
+// 8.85 MFLOP per position (10.4 TFLOP per call at 720p 1/4 res x 20 frames): tensor-core bound.  The reference runs nine
+// cuDNN conv3d calls on NCDHW bf16 tensors plus ~25 elementwise launches (measured: 16 % of the bf16 peak).
+//
+// Formulation: a 1-D convolution is a sum of shifted GEMMs,  out[p, :] = bias + sum_d  A[p + d*e_axis, :] . W_d^T,
+// with A the activations in a CHANNELS-LAST bf16 layout [position][channel] (K-major operand rows) and W_d the
+// [Cout][Cin] slice of the kernel at tap d.  One persistent tcgen05 kernel runs every convolution of the unit:
+//   * M tile = 128 positions = a (bw x bh) patch of one frame (bw * bh = 128, bw in {16, 32, 64} chosen to waste the
+//     fewest columns of W); its operand rows come from a 5-D TMA box [64 channels][bw][bh][1][1] of the activation
+//     tensor (dims C, W, H, T, b).  The shift of tap d is a COORDINATE offset of the box along the convolution's axis and
+//     the zero padding of the convolution is TMA's out-of-bounds zero fill -- W, H and T convolutions are the same code;
+//   * K loop = taps x (Cin / 64) steps; a step stages [128 positions][64 ch] of A (16 KB) and [N][64 ch] of W_d
+//     (N = 256: the z and r convolutions of a stage share their input and run as ONE GEMM with N = 256) through a
+//     4-stage mbarrier ring; 4 tcgen05.mma (K = 16) per step into a 128 x N fp32 accumulator in TMEM, double-buffered
+//     (2 x 256 columns) so that the epilogue of tile i overlaps the MMAs of tile i + 1;
+//   * the gate arithmetic is fused into the epilogues (8 warps: TMEM lane = position, 32 channels per tcgen05.ld), with
+//     the reference's autocast rounding: every conv result, gelu / sigmoid / tanh, r*h, 1-z, (1-z)*h, z*q and their sum
+//     are bf16 tensors in the reference (conv3d is an autocast-to-bf16 op and elementwise ops of bf16 tensors return
+//     bf16) -- each is rounded once here, in the same order.
+// A operand channels come from up to two tensors (h or r*h: 128 channels; x: 384 channels), so x is packed once per call.
+#include <math.h>
+#include <mutex>
+
+#include "../../include/ppm_b200.h"
+#include "common.cuh"
+
+namespace ppm {
+
+constexpr int kGrThreads = 320;                 // TMA warp, MMA warp, 8 epilogue warps
+constexpr int kGrM = 128;
+constexpr int kGrKC = 64;                       // channels per K step (128 B of bf16)
+constexpr int kGrABytes = kGrM * kGrKC * 2;     // 16 KB
+constexpr int kGrStages = 4;
+constexpr int kGrTmemCols = 512;
+constexpr int kGrHidden = 128;
+
+enum GruEpilogue : int {
+  GR_EPI_GELU = 0,     // out[p, n] = bf16(gelu(bf16(acc + bias)))                       -> dst0 [P, N]
+  GR_EPI_Z = 1,        // z = bf16(sigmoid(bf16(acc + bias)))                           -> dst0 [P, 128]
+  GR_EPI_R = 2,        // r likewise; rh = bf16(r * h)                                   -> dst1 [P, 128]
+  GR_EPI_ZR = 3,       // N = 256: columns 0-127 as GR_EPI_Z, 128-255 as GR_EPI_R
+  GR_EPI_Q = 4         // q = bf16(tanh(bf16(acc + bias))); h = bf16(bf16(bf16(1-z)*h) + bf16(z*q)) -> hbuf (+ NCTHW out)
+};
+
+struct GruGemmParams {
+  const float* bias;                 // [N] (bf16-representable values)
+  __nv_bfloat16* dst0;               // GELU: G [P, N]; Z / ZR: Z [P, 128]
+  __nv_bfloat16* dst1;               // R / ZR: RH [P, 128]
+  __nv_bfloat16* hbuf;               // [P, 128] current hidden state (read by R / ZR / Q, rewritten by Q)
+  const __nv_bfloat16* zbuf;         // Q: Z [P, 128]
+  void* out;                         // Q, last stage: (b, 128, T, H, W) contiguous, or nullptr
+  int out_dtype;
+  int N;                             // 128 or 256
+  int taps, axis;                    // axis: 0 = W, 1 = H, 2 = T
+  int seg0_chunks, seg0_c0;          // A channels: seg0_chunks 64-channel chunks of map_a0 starting at channel seg0_c0,
+  int seg1_chunks;                   //             then seg1_chunks chunks of map_a1 starting at channel 0
+  int b, T, H, W, bw, bh;
+  int tiles_x, tiles_y;
+  long long n_tiles;
+  int mode;
+};
+
+__device__ __forceinline__ void tma_load_5d(void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2,
+                                            int c3, int c4) {
+  asm volatile(
+      "cp.async.bulk.tensor.5d.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5, %6, %7}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3),
+      "r"(c4)
+      : "memory");
+}
+
+__device__ __forceinline__ float gr_ld(const float* p) { return __ldg(p); }
+__device__ __forceinline__ float gr_ld(const __nv_bfloat16* p) { return __bfloat162float(__ldg(p)); }
+
+// ------------------------------------------------------------------------------------------------ packing
+// (b, C, T, H, W) strided source (pixels contiguous) -> channels-last bf16 [P][dst_c] at channel offset c_off.
+// CTA = 32 pixels x 64 channels, transposed through shared memory; reads are 128-byte rows of pixels, writes are
+// 128-byte rows of channels.
+template <typename SrcT>
+__global__ void __launch_bounds__(256) gru_pack_kernel(const SrcT* __restrict__ src, long long sb, long long sc,
+                                                       long long st, int T, int HW, int C, int dst_c, int c_off,
+                                                       __nv_bfloat16* __restrict__ dst) {
+  __shared__ float tile[64][33];
+  const int p0 = blockIdx.x * 32, c0 = blockIdx.y * 64, frame = blockIdx.z;
+  const int bb = frame / T, t = frame - bb * T;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const SrcT* base = src + bb * sb + t * st + p0;
+  #pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int c = k * 8 + w;
+    tile[c][lane] = (p0 + lane < HW && c0 + c < C) ? gr_ld(base + static_cast<long long>(c0 + c) * sc + lane) : 0.f;
+  }
+  __syncthreads();
+  const int px = threadIdx.x >> 3, cq = (threadIdx.x & 7) * 8;       // 32 pixels x 8 groups of 8 channels (16 B)
+  if (p0 + px < HW && c0 + cq < C) {
+    uint4 v;
+    v.x = pack_bf16x2(tile[cq + 0][px], tile[cq + 1][px]);
+    v.y = pack_bf16x2(tile[cq + 2][px], tile[cq + 3][px]);
+    v.z = pack_bf16x2(tile[cq + 4][px], tile[cq + 5][px]);
+    v.w = pack_bf16x2(tile[cq + 6][px], tile[cq + 7][px]);
+    __nv_bfloat16* d = dst + (static_cast<long long>(frame) * HW + p0 + px) * dst_c + c_off + c0 + cq;
+    *reinterpret_cast<uint4*>(d) = v;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ epilogue math
+// fp32 evaluation + one rounding, as torch's CUDA elementwise kernels do for bf16 tensors (opmath = float).
+__device__ __forceinline__ float gr_gelu(float x) { return 0.5f * x * (1.f + erff(x * 0.70710678118654752440f)); }
+__device__ __forceinline__ float gr_sigmoid(float x) { return 1.f / (1.f + expf(-x)); }
+
+__device__ __forceinline__ void gr_unpack8(const uint4& v, float (&f)[8]) {
+  f[0] = __uint_as_float(v.x << 16); f[1] = __uint_as_float(v.x & 0xFFFF0000u);
+  f[2] = __uint_as_float(v.y << 16); f[3] = __uint_as_float(v.y & 0xFFFF0000u);
+  f[4] = __uint_as_float(v.z << 16); f[5] = __uint_as_float(v.z & 0xFFFF0000u);
+  f[6] = __uint_as_float(v.w << 16); f[7] = __uint_as_float(v.w & 0xFFFF0000u);
+}
+__device__ __forceinline__ uint4 gr_pack8(const float (&f)[8]) {
+  uint4 v;
+  v.x = pack_bf16x2(f[0], f[1]); v.y = pack_bf16x2(f[2], f[3]);
+  v.z = pack_bf16x2(f[4], f[5]); v.w = pack_bf16x2(f[6], f[7]);
+  return v;
+}
+
+// ------------------------------------------------------------------------------------------------ the GEMM
+__global__ void __launch_bounds__(kGrThreads, 1)
+gru_gemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant__ CUtensorMap map_a1,
+                const __grid_constant__ CUtensorMap map_w, const GruGemmParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  __shared__ uint64_t bar_full[kGrStages], bar_empty[kGrStages], bar_acc_full[2], bar_acc_empty[2];
+  __shared__ uint32_t tmem_slot;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int b_bytes = p.N * 128;
+  const int stage_bytes = kGrABytes + b_bytes;
+  const int n_chunks = p.seg0_chunks + p.seg1_chunks;
+  const int n_steps = p.taps * n_chunks;
+  const int pad = (p.taps - 1) / 2;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kGrStages; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(&bar_acc_full[a], 1); mbar_init(&bar_acc_empty[a], 8); }
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc<kGrTmemCols>(&tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = tmem_slot;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------------------ TMA producer
+    if (elect_one()) {
+      tma_prefetch_desc(&map_a0); tma_prefetch_desc(&map_a1); tma_prefetch_desc(&map_w);
+      int stage = 0;
+      uint32_t ph = 1;                                    // parity to wait for on bar_empty[stage]
+      for (long long tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+        long long r = tile;
+        const int bx = static_cast<int>(r % p.tiles_x); r /= p.tiles_x;
+        const int by = static_cast<int>(r % p.tiles_y); r /= p.tiles_y;
+        const int t = static_cast<int>(r % p.T);
+        const int bb = static_cast<int>(r / p.T);
+        for (int d = 0; d < p.taps; ++d) {
+          const int sh = d - pad;
+          const int cx = bx * p.bw + (p.axis == 0 ? sh : 0);
+          const int cy = by * p.bh + (p.axis == 1 ? sh : 0);
+          const int ct = t + (p.axis == 2 ? sh : 0);
+          for (int kc = 0; kc < n_chunks; ++kc) {
+            mbar_wait(&bar_empty[stage], ph);
+            mbar_expect_tx(&bar_full[stage], stage_bytes);
+            uint8_t* dst = smem + stage * stage_bytes;
+            if (kc < p.seg0_chunks) tma_load_5d(dst, &map_a0, &bar_full[stage], p.seg0_c0 + kc * kGrKC, cx, cy, ct, bb);
+            else tma_load_5d(dst, &map_a1, &bar_full[stage], (kc - p.seg0_chunks) * kGrKC, cx, cy, ct, bb);
+            tma_load_3d(dst + kGrABytes, &map_w, &bar_full[stage], kc * kGrKC, 0, d);
+            if (++stage == kGrStages) { stage = 0; ph ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------------------ MMA issuer
+    const bool leader = elect_one();
+    const uint32_t idesc = umma_idesc(1, 0, 0, kGrM, p.N);
+    const uint32_t desc_hi = static_cast<uint32_t>(umma_desc_sw128(0, 16, 1024) >> 32);
+    const uint32_t desc_lo0 = static_cast<uint32_t>(umma_desc_sw128(0, 16, 1024));
+    const uint32_t base_lo = desc_lo0 + (smem_u32(smem) >> 4);
+    auto mk = [&](uint32_t lo) -> uint64_t {
+      uint64_t d;
+      asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "r"(lo), "r"(desc_hi));
+      return d;
+    };
+    int stage = 0;
+    uint32_t ph = 0;
+    int i = 0;
+    for (long long tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++i) {
+      const int buf = i & 1, use = i >> 1;
+      mbar_wait(&bar_acc_empty[buf], (use & 1) ^ 1);      // epilogue has drained this accumulator
+      tc_fence_after();
+      const uint32_t d_tmem = tmem + buf * 256;
+      for (int step = 0; step < n_steps; ++step) {
+        mbar_wait(&bar_full[stage], ph);
+        tc_fence_after();
+        if (leader) {
+          const uint32_t a_lo = base_lo + ((stage * stage_bytes) >> 4);
+          const uint32_t b_lo = a_lo + (kGrABytes >> 4);
+          #pragma unroll
+          for (int k = 0; k < 4; ++k)
+            umma_f16_ss(d_tmem, mk(a_lo + 2 * k), mk(b_lo + 2 * k), idesc, (step | k) != 0);
+          umma_commit(&bar_empty[stage]);                 // frees the ring stage once these MMAs have read it
+        }
+        __syncwarp();
+        if (++stage == kGrStages) { stage = 0; ph ^= 1; }
+      }
+      if (leader) umma_commit(&bar_acc_full[buf]);
+      __syncwarp();
+    }
+  } else {
+    // ------------------------------------------------------------------------------ epilogue (8 warps)
+    const int quarter = warp & 3;                         // TMEM lanes 32*quarter .. +31 (hardware rule: warp_id % 4)
+    const int half = (warp - 2) >> 2;                     // which half of the N columns
+    const int row = quarter * 32 + lane;
+    const int cols_per_warp = p.N >> 1;
+    const int HW = p.H * p.W;
+    int i = 0;
+    for (long long tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++i) {
+      const int buf = i & 1, use = i >> 1;
+      long long r = tile;
+      const int bx = static_cast<int>(r % p.tiles_x); r /= p.tiles_x;
+      const int by = static_cast<int>(r % p.tiles_y); r /= p.tiles_y;
+      const int t = static_cast<int>(r % p.T);
+      const int bb = static_cast<int>(r / p.T);
+      const int x = bx * p.bw + row % p.bw, y = by * p.bh + row / p.bw;
+      const bool valid = x < p.W && y < p.H;
+      const long long pos = (static_cast<long long>(bb) * p.T + t) * HW + static_cast<long long>(y) * p.W + x;
+      mbar_wait(&bar_acc_full[buf], use & 1);
+      tc_fence_after();
+      const uint32_t t_addr = tmem + (static_cast<uint32_t>(quarter * 32) << 16) + buf * 256 + half * cols_per_warp;
+      const int n_chunks_e = cols_per_warp >> 5;
+      for (int c = 0; c < n_chunks_e; ++c) {
+        uint32_t acc[32];
+        tmem_ld_x32(t_addr + c * 32, acc);
+        tmem_ld_wait();
+        if (c == n_chunks_e - 1) {                        // this warp's last read of the accumulator
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&bar_acc_empty[buf]);
+        }
+        if (!valid) continue;
+        const int col0 = half * cols_per_warp + c * 32;   // column of acc[0] in the GEMM's N
+        int mode = p.mode, ch0 = col0;                    // ch0: channel inside the 128-wide gate tensors
+        if (mode == GR_EPI_ZR) { mode = col0 < kGrHidden ? GR_EPI_Z : GR_EPI_R; ch0 = col0 & (kGrHidden - 1); }
+        #pragma unroll
+        for (int g = 0; g < 4; ++g) {                     // 4 groups of 8 channels = one 16-byte store each
+          float v[8];
+          #pragma unroll
+          for (int e = 0; e < 8; ++e)
+            v[e] = bf16_round_f(__uint_as_float(acc[g * 8 + e]) + __ldg(p.bias + col0 + g * 8 + e));
+          const int ch = ch0 + g * 8;
+          if (mode == GR_EPI_GELU) {
+            #pragma unroll
+            for (int e = 0; e < 8; ++e) v[e] = gr_gelu(v[e]);
+            *reinterpret_cast<uint4*>(p.dst0 + pos * p.N + col0 + g * 8) = gr_pack8(v);
+          } else if (mode == GR_EPI_Z) {
+            #pragma unroll
+            for (int e = 0; e < 8; ++e) v[e] = gr_sigmoid(v[e]);
+            *reinterpret_cast<uint4*>(p.dst0 + pos * kGrHidden + ch) = gr_pack8(v);
+          } else if (mode == GR_EPI_R) {
+            float h[8];
+            gr_unpack8(*reinterpret_cast<const uint4*>(p.hbuf + pos * kGrHidden + ch), h);
+            #pragma unroll
+            for (int e = 0; e < 8; ++e) v[e] = bf16_round_f(gr_sigmoid(v[e])) * h[e];
+            *reinterpret_cast<uint4*>(p.dst1 + pos * kGrHidden + ch) = gr_pack8(v);
+          } else {                                        // GR_EPI_Q
+            float h[8], z[8];
+            gr_unpack8(*reinterpret_cast<const uint4*>(p.hbuf + pos * kGrHidden + ch), h);
+            gr_unpack8(*reinterpret_cast<const uint4*>(p.zbuf + pos * kGrHidden + ch), z);
+            #pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              const float q = bf16_round_f(tanhf(v[e]));
+              const float a = bf16_round_f(bf16_round_f(1.f - z[e]) * h[e]);
+              const float bq = bf16_round_f(z[e] * q);
+              v[e] = bf16_round_f(a + bq);
+            }
+            *reinterpret_cast<uint4*>(p.hbuf + pos * kGrHidden + ch) = gr_pack8(v);
+            if (p.out) {
+              const long long o = ((static_cast<long long>(bb) * kGrHidden + ch) * p.T + t) * HW + static_cast<long long>(y) * p.W + x;
+              const long long cs = static_cast<long long>(p.T) * HW;
+              if (p.out_dtype == PPM_BF16) {
+                __nv_bfloat16* ob = static_cast<__nv_bfloat16*>(p.out) + o;
+                #pragma unroll
+                for (int e = 0; e < 8; ++e) ob[e * cs] = __float2bfloat16_rn(v[e]);
+              } else {
+                float* of = static_cast<float*>(p.out) + o;
+                #pragma unroll
+                for (int e = 0; e < 8; ++e) of[e * cs] = v[e];
+              }
+            }
+          }
+        }
+      }
+    }
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<kGrTmemCols>(tmem);
+  }
+}

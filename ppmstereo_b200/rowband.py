@@ -85,3 +85,40 @@ class RowBandMemory:
         full_mf[:, :, :, self.r0:self.r1] = motion_features_band
         out = m.aggregate(full_mf, beta, scale, band=(self.r0 * self.w, (self.r1 - self.r0) * self.w))
         return out[:, :, self.r0:self.r1], mask
+
+
+def verify_against_full_read(device, shape=(1, 7, 21, 40), iterations: int = 3, seed: int = 5, group=None) -> bool:
+    """Self-check on an initialised process group: every rank computes the full-frame read AND its own row band
+    through ``RowBandMemory`` on the same seeded inputs; True iff, on every rank and iteration, the band equals the
+    matching rows of the full result bit for bit, masks / strive_time agree and all ranks picked the same frames.
+    Used by tests/mgpu_rowband_check.py and by ``bench.py --gpus N`` (key ``rowband_bit_exact``)."""
+    b, T, h, w = shape
+    c = 128
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    g = torch.Generator().manual_seed(seed)                    # same inputs on every rank
+    rn = lambda *s_: torch.randn(*s_, generator=g)
+    q, k, v, mf = rn(b, c, T, h, w), rn(b, c, T, h, w), rn(b, c, T, h, w), rn(b, c, T, h, w)
+    unc = torch.rand(b * T, 1, h, w, generator=g)
+    sim = torch.rand(b, 1, T, T, generator=g) * 2 - 1
+    q, k, v, mf, unc, sim = (t.to(device) for t in (q, k, v, mf, unc, sim))
+    beta = torch.tensor([0.5], device=device)
+    ok = True
+    full = PPMMemory(q, k, None, top_k=5)
+    band = RowBandMemory(q, k, None, top_k=5, group=group)
+    s_full, s_band = torch.ones_like(sim), torch.ones_like(sim)
+    r0, r1 = band.r0, band.r1
+    for it in range(iterations):                               # strive_time evolves: picks change
+        vv = v + 0.1 * it
+        want, mask_f = full.read(vv, mf, sim, s_full, unc, beta)
+        got, mask_b = band.read(vv[:, :, :, r0:r1].contiguous(), mf[:, :, :, r0:r1].contiguous(), sim, s_band,
+                                unc[:, :, r0:r1].contiguous(), beta)
+        ok &= bool(torch.equal(got, want[:, :, r0:r1])) and bool(torch.equal(mask_f, mask_b))
+        ok &= bool(torch.equal(s_full, s_band))
+        if world > 1:
+            picks = [torch.empty_like(band.mem.picked) for _ in range(world)]
+            dist.all_gather(picks, band.mem.picked, group=group)
+            ok &= all(bool(torch.equal(p_, picks[0])) for p_ in picks)
+    flag = torch.tensor([1 if ok else 0], device=device)
+    if world > 1:
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+    return int(flag) == 1
