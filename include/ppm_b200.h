@@ -171,6 +171,28 @@ PPM_API int ppm_memory_attend_band(const void* Q, const void* K, const void* V, 
 PPM_API int ppm_convex_upsample(const float* flow, const void* mask, int mask_dtype, int N, int H, int W,
                         int rate, float* out, void* stream);
 
+/* ---------------------------------------------------------------------------------------
+ * K5  SKSepConvGRU3D (models/core/ppmtereo_update.py:254-312, called from
+ * SequenceUpdateBlock3D.forward :971-1003), in the reference's bf16 autocast regime:
+ *   per stage s = 1 (along W), 2 (along H), 3 (along T):
+ *     z = sigmoid(convz_s(cat[h, x])); r = sigmoid(convr_s(cat[h, x])); q = tanh(convq_s(cat[r*h, x]));
+ *     h = (1 - z) * h + z * q          (stage 1: convz / convr = Conv(15 taps) -> GELU -> Conv(5 taps))
+ *   every elementwise result is rounded to bf16 once and every conv result is bf16(bf16(acc) + bias), as cuDNN's bf16
+ *   conv3d + torch's bias add and the elementwise ops of bf16 tensors do in the reference; fp32 accumulation on
+ *   tcgen05 tensor cores.
+ * h (b,128,T,H,W) and x (b,384,T,H,W) are indexed src[b*sb + c*sc + t*st + y*W + x] (element strides), fp32 or bf16.
+ * weights[8]: bf16, packed [tap][Cout][Cin] (Cin order = cat[h, x]):
+ *   0: convz1.0 | convr1.0 stacked on Cout (15, 256, 512)   1: convz1.2 (5,128,128)   2: convr1.2 (5,128,128)
+ *   3: convq1 (5,128,512)   4: convz2 | convr2 (5,256,512)   5: convq2   6: convz3 | convr3   7: convq3
+ * biases[8]: fp32 arrays of Cout values (the bf16-rounded biases), same order.
+ * workspace: ppm_sepconv_gru3d_workspace bytes, 256-byte aligned (channels-last bf16 copies of x, h, r*h, z and the
+ * stage-1 GELU tensor).  out: (b,128,T,H,W) contiguous, out_dtype. */
+PPM_API int ppm_sepconv_gru3d_workspace(int b, int T, int H, int W, size_t* bytes);
+PPM_API int ppm_sepconv_gru3d(const void* h, int h_dtype, int64_t hsb, int64_t hsc, int64_t hst, const void* x,
+                      int x_dtype, int64_t xsb, int64_t xsc, int64_t xst, const void* const* weights,
+                      const float* const* biases, int b, int T, int H, int W, void* workspace,
+                      size_t workspace_bytes, void* out, int out_dtype, void* stream);
+
 /* Bytes of the packed operands for (b, T, Kp, hw): q, k, v in that order. */
 PPM_API int ppm_pack_bytes(int b, int T, int Kp, int hw, size_t* q_bytes, size_t* k_bytes,
                    size_t* v_bytes);

@@ -354,7 +354,8 @@ def _sep_conv(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor, axis: i
     as a sum of shifted channel contractions: out[p] = bias + sum_d W_d . in[p + d - (k-1)/2]  -- what nn.Conv3d with a
     (k,1,1) / (1,k,1) / (1,1,k) kernel computes (ppmtereo_update.py:257-289).  weight: (Cout, Cin, kt, kh, kw) with a
     single non-unit kernel dim.  ``rnd`` rounds operands and the result (identity in fp32 mode, bf16 in autocast mode:
-    conv3d is an autocast-to-bf16 op -- input, weight and bias are cast to bf16, fp32 accumulation, bf16 result)."""
+    conv3d is an autocast-to-bf16 op -- input, weight and bias are cast to bf16, fp32 accumulation, bf16 result, then the
+    bias added in bf16: identified against torch/cuDNN on the B200, scripts/exp/gru_rounding_probe.py)."""
     k = weight.shape[axis]
     w = rnd(weight.float()).reshape(weight.shape[0], weight.shape[1], k)            # (Cout, Cin, k)
     xin = rnd(x.float())
@@ -367,7 +368,8 @@ def _sep_conv(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor, axis: i
             continue
         src = xin.narrow(axis, lo + d - pad, hi - lo)
         out.narrow(axis, lo, hi - lo).add_(torch.einsum("oc,bcthw->bothw", w[:, :, d], src))
-    return rnd(out + rnd(bias.float()).view(1, -1, 1, 1, 1))
+    # two roundings in bf16 mode: cuDNN stores the bf16 convolution, the (bf16) bias is added as a separate bf16 op
+    return rnd(rnd(out) + rnd(bias.float()).view(1, -1, 1, 1, 1))
 
 
 def sk_sep_conv_gru3d(h: torch.Tensor, x: torch.Tensor, params: dict, mode: str = "fp32") -> torch.Tensor:

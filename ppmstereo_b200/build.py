@@ -9,7 +9,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libppm_sm100.so")
-SOURCES = ["api.cu", "corr_build.cu", "corr_lookup.cu", "ppm_prep.cu", "ppm_attend3.cu", "convex_upsample.cu", "qk_similarity.cu"]
+SOURCES = ["api.cu", "corr_build.cu", "corr_lookup.cu", "ppm_prep.cu", "ppm_attend3.cu", "convex_upsample.cu", "qk_similarity.cu", "sepconv_gru3d.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden", "--use_fast_math=false"]
 

@@ -20,7 +20,10 @@
 //   * the gate arithmetic is fused into the epilogues (8 warps: TMEM lane = position, 32 channels per tcgen05.ld), with
 //     the reference's autocast rounding: every conv result, gelu / sigmoid / tanh, r*h, 1-z, (1-z)*h, z*q and their sum
 //     are bf16 tensors in the reference (conv3d is an autocast-to-bf16 op and elementwise ops of bf16 tensors return
-//     bf16) -- each is rounded once here, in the same order.
+//     bf16) -- each is rounded once here, in the same order.  A conv result is TWO roundings, bf16(bf16(acc) + bias):
+//     cuDNN stores the bf16 convolution and torch adds the (bf16) bias as a separate step -- identified on the box
+//     (scripts/exp/gru_rounding_probe.py: 99.8-99.97 % of cuDNN's outputs reproduced, vs 73 % for a fused fp32 bias add;
+//     the gate chain, sigmoid, gelu (erf form) and tanh reproduce torch's bf16 results 100 %).
 // A operand channels come from up to two tensors (h or r*h: 128 channels; x: 384 channels), so x is packed once per call.
 #include <math.h>
 #include <mutex>
@@ -39,7 +42,7 @@ constexpr int kGrTmemCols = 512;
 constexpr int kGrHidden = 128;
 
 enum GruEpilogue : int {
-  GR_EPI_GELU = 0,     // out[p, n] = bf16(gelu(bf16(acc + bias)))                       -> dst0 [P, N]
+  GR_EPI_GELU = 0,     // out[p, n] = bf16(gelu(c)), c = bf16(bf16(acc) + bias)                     -> dst0 [P, N]
   GR_EPI_Z = 1,        // z = bf16(sigmoid(bf16(acc + bias)))                           -> dst0 [P, 128]
   GR_EPI_R = 2,        // r likewise; rh = bf16(r * h)                                   -> dst1 [P, 128]
   GR_EPI_ZR = 3,       // N = 256: columns 0-127 as GR_EPI_Z, 128-255 as GR_EPI_R
@@ -259,7 +262,7 @@ gru_gemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constan
           float v[8];
           #pragma unroll
           for (int e = 0; e < 8; ++e)
-            v[e] = bf16_round_f(__uint_as_float(acc[g * 8 + e]) + __ldg(p.bias + col0 + g * 8 + e));
+            v[e] = bf16_round_f(bf16_round_f(__uint_as_float(acc[g * 8 + e])) + __ldg(p.bias + col0 + g * 8 + e));
           const int ch = ch0 + g * 8;
           if (mode == GR_EPI_GELU) {
             #pragma unroll
@@ -310,4 +313,155 @@ gru_gemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constan
     tc_fence_after();
     tmem_dealloc<kGrTmemCols>(tmem);
   }
+}
+
+// ------------------------------------------------------------------------------------------------ host
+struct GruShape {
+  int b, T, H, W, bw, bh, tiles_x, tiles_y;
+  long long P, n_tiles;
+};
+
+static GruShape gru_shape(int b, int T, int H, int W) {
+  GruShape s{};
+  s.b = b; s.T = T; s.H = H; s.W = W;
+  int best = 64;
+  long long best_cols = -1;
+  for (int bw = 64; bw >= 16; bw >>= 1) {                 // fewest wasted columns; ties -> the wider box
+    const long long cols = static_cast<long long>((W + bw - 1) / bw) * bw;
+    if (best_cols < 0 || cols < best_cols) { best = bw; best_cols = cols; }
+  }
+  s.bw = best; s.bh = kGrM / best;
+  s.tiles_x = (W + s.bw - 1) / s.bw;
+  s.tiles_y = (H + s.bh - 1) / s.bh;
+  s.P = static_cast<long long>(b) * T * H * W;
+  s.n_tiles = static_cast<long long>(s.tiles_x) * s.tiles_y * T * b;
+  return s;
+}
+
+static int gru_act_map(CUtensorMap* m, const void* base, int C, const GruShape& s) {
+  const uint64_t dims[5] = {(uint64_t)C, (uint64_t)s.W, (uint64_t)s.H, (uint64_t)s.T, (uint64_t)s.b};
+  const uint64_t e = static_cast<uint64_t>(C) * 2;
+  const uint64_t str[4] = {e, e * s.W, e * s.W * s.H, e * s.W * s.H * s.T};
+  const uint32_t box[5] = {(uint32_t)kGrKC, (uint32_t)s.bw, (uint32_t)s.bh, 1, 1};
+  return make_tensor_map(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, base, dims, str, box, CU_TENSOR_MAP_SWIZZLE_128B);
+}
+
+static int gru_w_map(CUtensorMap* m, const void* base, int Cin, int N, int taps) {
+  const uint64_t dims[3] = {(uint64_t)Cin, (uint64_t)N, (uint64_t)taps};
+  const uint64_t str[2] = {(uint64_t)Cin * 2, (uint64_t)Cin * 2 * N};
+  const uint32_t box[3] = {(uint32_t)kGrKC, (uint32_t)N, 1};
+  return make_tensor_map(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, base, dims, str, box, CU_TENSOR_MAP_SWIZZLE_128B);
+}
+
+static int gru_launch(const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap& w, GruGemmParams p,
+                      const GruShape& s, cudaStream_t st) {
+  p.b = s.b; p.T = s.T; p.H = s.H; p.W = s.W; p.bw = s.bw; p.bh = s.bh;
+  p.tiles_x = s.tiles_x; p.tiles_y = s.tiles_y; p.n_tiles = s.n_tiles;
+  const int smem = kGrStages * (kGrABytes + p.N * 128) + 1024;
+  static std::mutex mu;
+  static bool attr_done[64] = {};
+  int dev = 0, n_sm = 148;
+  PPM_CUDA(cudaGetDevice(&dev));
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    if (dev < 0 || dev >= 64 || !attr_done[dev]) {
+      PPM_CUDA(cudaFuncSetAttribute(gru_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    kGrStages * (kGrABytes + 256 * 128) + 1024));
+      if (dev >= 0 && dev < 64) attr_done[dev] = true;
+    }
+  }
+  PPM_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
+  const int grid = static_cast<int>(s.n_tiles < n_sm ? s.n_tiles : n_sm);
+  gru_gemm_kernel<<<grid, kGrThreads, smem, st>>>(a0, a1, w, p);
+  PPM_CUDA(cudaGetLastError());
+  return PPM_OK;
+}
+
+template <typename SrcT>
+static int gru_pack(const void* src, long long sb, long long sc, long long st_, const GruShape& s, int C, int dst_c,
+                    int c_off, __nv_bfloat16* dst, cudaStream_t st) {
+  const int HW = s.H * s.W;
+  dim3 grid((HW + 31) / 32, (C + 63) / 64, s.b * s.T);
+  gru_pack_kernel<SrcT><<<grid, 256, 0, st>>>(static_cast<const SrcT*>(src), sb, sc, st_, s.T, HW, C, dst_c, c_off, dst);
+  PPM_CUDA(cudaGetLastError());
+  return PPM_OK;
+}
+
+}  // namespace ppm
+
+extern "C" int ppm_sepconv_gru3d_workspace(int b, int T, int H, int W, size_t* bytes) {
+  PPM_CHECK(b > 0 && T > 0 && H > 0 && W > 0 && bytes, PPM_ERR_ARG, "ppm_sepconv_gru3d_workspace: bad argument");
+  const size_t P = static_cast<size_t>(b) * T * H * W;
+  *bytes = P * (384 + 128 + 128 + 128 + 256) * 2;       // X, H, RH, Z, G  (bf16, channels-last)
+  return PPM_OK;
+}
+
+extern "C" int ppm_sepconv_gru3d(const void* h, int h_dtype, int64_t hsb, int64_t hsc, int64_t hst, const void* x,
+                                 int x_dtype, int64_t xsb, int64_t xsc, int64_t xst, const void* const* weights,
+                                 const float* const* biases, int b, int T, int H, int W, void* workspace,
+                                 size_t workspace_bytes, void* out, int out_dtype, void* stream) {
+  using namespace ppm;
+  PPM_CHECK(h && x && weights && biases && workspace && out, PPM_ERR_ARG, "ppm_sepconv_gru3d: null pointer");
+  PPM_CHECK(b > 0 && T > 0 && H > 0 && W > 0, PPM_ERR_ARG, "ppm_sepconv_gru3d: bad shape");
+  PPM_CHECK(b <= 65535 && T <= 65535 && static_cast<long long>(b) * T <= 65535, PPM_ERR_UNSUPPORTED,
+            "ppm_sepconv_gru3d: b*T > 65535");
+  PPM_CHECK((h_dtype == PPM_F32 || h_dtype == PPM_BF16) && (x_dtype == PPM_F32 || x_dtype == PPM_BF16) &&
+                (out_dtype == PPM_F32 || out_dtype == PPM_BF16),
+            PPM_ERR_ARG, "ppm_sepconv_gru3d: bad dtype");
+  size_t need = 0;
+  ppm_sepconv_gru3d_workspace(b, T, H, W, &need);
+  PPM_CHECK(workspace_bytes >= need, PPM_ERR_ARG, "ppm_sepconv_gru3d: workspace of %zu bytes < %zu needed", workspace_bytes, need);
+  PPM_CHECK((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, PPM_ERR_ARG, "ppm_sepconv_gru3d: workspace must be 256-byte aligned");
+  for (int i = 0; i < 8; ++i)
+    PPM_CHECK(weights[i] && biases[i] && (reinterpret_cast<uintptr_t>(weights[i]) & 15) == 0, PPM_ERR_ARG,
+              "ppm_sepconv_gru3d: weight / bias %d null or misaligned", i);
+  const GruShape s = gru_shape(b, T, H, W);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  __nv_bfloat16* X = static_cast<__nv_bfloat16*>(workspace);
+  __nv_bfloat16* Hb = X + s.P * 384;
+  __nv_bfloat16* RH = Hb + s.P * 128;
+  __nv_bfloat16* Z = RH + s.P * 128;
+  __nv_bfloat16* G = Z + s.P * 128;
+  int rc;
+  // channels-last bf16 operands (the cast conv3d's autocast performs on its input)
+  if (x_dtype == PPM_BF16) rc = gru_pack<__nv_bfloat16>(x, xsb, xsc, xst, s, 384, 384, 0, X, st);
+  else rc = gru_pack<float>(x, xsb, xsc, xst, s, 384, 384, 0, X, st);
+  if (rc) return rc;
+  if (h_dtype == PPM_BF16) rc = gru_pack<__nv_bfloat16>(h, hsb, hsc, hst, s, 128, 128, 0, Hb, st);
+  else rc = gru_pack<float>(h, hsb, hsc, hst, s, 128, 128, 0, Hb, st);
+  if (rc) return rc;
+  CUtensorMap mX, mH, mRH, mG, mW[8];
+  if ((rc = gru_act_map(&mX, X, 384, s))) return rc;
+  if ((rc = gru_act_map(&mH, Hb, 128, s))) return rc;
+  if ((rc = gru_act_map(&mRH, RH, 128, s))) return rc;
+  if ((rc = gru_act_map(&mG, G, 256, s))) return rc;
+  const int w_cin[8] = {512, 128, 128, 512, 512, 512, 512, 512};
+  const int w_n[8] = {256, 128, 128, 128, 256, 128, 256, 128};
+  const int w_taps[8] = {15, 5, 5, 5, 5, 5, 5, 5};
+  for (int i = 0; i < 8; ++i)
+    if ((rc = gru_w_map(&mW[i], weights[i], w_cin[i], w_n[i], w_taps[i]))) return rc;
+
+  GruGemmParams p{};
+  p.hbuf = Hb; p.zbuf = Z; p.out = nullptr; p.out_dtype = out_dtype;
+  // ---- stage 1: along W.  z / r = Conv(15) -> GELU -> Conv(5) (ppmtereo_update.py:257-266)
+  p.bias = biases[0]; p.N = 256; p.taps = 15; p.axis = 0; p.mode = GR_EPI_GELU;
+  p.seg0_chunks = 2; p.seg0_c0 = 0; p.seg1_chunks = 6; p.dst0 = G; p.dst1 = nullptr;
+  if ((rc = gru_launch(mH, mX, mW[0], p, s, st))) return rc;
+  p.bias = biases[1]; p.N = 128; p.taps = 5; p.mode = GR_EPI_Z; p.seg0_chunks = 2; p.seg0_c0 = 0; p.seg1_chunks = 0; p.dst0 = Z;
+  if ((rc = gru_launch(mG, mG, mW[1], p, s, st))) return rc;
+  p.bias = biases[2]; p.mode = GR_EPI_R; p.seg0_c0 = 128; p.dst0 = nullptr; p.dst1 = RH;
+  if ((rc = gru_launch(mG, mG, mW[2], p, s, st))) return rc;
+  p.bias = biases[3]; p.mode = GR_EPI_Q; p.seg0_c0 = 0; p.seg0_chunks = 2; p.seg1_chunks = 6;
+  if ((rc = gru_launch(mRH, mX, mW[3], p, s, st))) return rc;
+  // ---- stages 2 (along H) and 3 (along T): z | r as one N = 256 GEMM, then q
+  for (int stage = 2; stage <= 3; ++stage) {
+    const int wi = stage == 2 ? 4 : 6;
+    p.axis = stage - 1; p.taps = 5;
+    p.bias = biases[wi]; p.N = 256; p.mode = GR_EPI_ZR; p.seg0_chunks = 2; p.seg0_c0 = 0; p.seg1_chunks = 6;
+    p.dst0 = Z; p.dst1 = RH; p.out = nullptr;
+    if ((rc = gru_launch(mH, mX, mW[wi], p, s, st))) return rc;
+    p.bias = biases[wi + 1]; p.N = 128; p.mode = GR_EPI_Q; p.out = stage == 3 ? out : nullptr;
+    if ((rc = gru_launch(mRH, mX, mW[wi + 1], p, s, st))) return rc;
+  }
+  return PPM_OK;
 }

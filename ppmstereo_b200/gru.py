@@ -1,0 +1,106 @@
+"""SKSepConvGRU3D on the B200: the reference module's ``forward(h, x)``
+(models/core/ppmtereo_update.py:291-312) as one C-ABI call (``ppm_sepconv_gru3d``, csrc/sepconv_gru3d.cu).
+
+``SepConvGRU3D(module)`` reads the nine Conv3d layers of a reference ``SKSepConvGRU3D`` instance (state-dict names
+unchanged), packs their weights once into the kernel's [tap][Cout][Cin] bf16 layout (re-packed when a parameter
+changes) and keeps a workspace per input shape.  bf16 autocast regime only -- the regime ``PPMStereoModel`` hard-codes
+(models/ppm_stereo_model.py:26); ``install()`` leaves the module's own forward in place outside it.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Dict, Tuple
+
+import torch
+
+from . import _lib
+
+HIDDEN, INPUT = 128, 384
+_LAYERS = [("convz1.0", "convr1.0"), ("convz1.2",), ("convr1.2",), ("convq1",), ("convz2", "convr2"), ("convq2",),
+           ("convz3", "convr3"), ("convq3",)]
+
+
+def _layer(module, name):
+    obj = module
+    for part in name.split("."):
+        obj = obj[int(part)] if part.isdigit() else getattr(obj, part)
+    return obj
+
+
+def _pack_weight(conv: torch.nn.Conv3d) -> torch.Tensor:
+    w = conv.weight.detach()
+    co, ci = w.shape[:2]
+    return w.reshape(co, ci, -1).permute(2, 0, 1).to(torch.bfloat16).contiguous()          # (taps, Cout, Cin)
+
+
+def _strides5(t: torch.Tensor, name: str, channels: int) -> Tuple[torch.Tensor, int, int, int]:
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor (ppmstereo_b200 has no CPU path)")
+    if t.dim() != 5 or t.shape[1] != channels:
+        raise RuntimeError(f"{name} must be (b, {channels}, T, H, W), got {tuple(t.shape)}")
+    if t.dtype not in (torch.float32, torch.bfloat16):
+        t = t.float()
+    if t.stride(4) != 1 or t.stride(3) != t.shape[4]:
+        t = t.contiguous()
+    return t, t.stride(0), t.stride(1), t.stride(2)
+
+
+class SepConvGRU3D:
+    def __init__(self, module):
+        self.module = module
+        self.lib = _lib.load()
+        self._versions = None
+        self._weights = self._biases = None
+        self._ws: Dict[Tuple, torch.Tensor] = {}
+
+    def _params(self):
+        convs = [[_layer(self.module, n) for n in names] for names in _LAYERS]
+        versions = tuple((c.weight._version, c.weight.data_ptr(), c.bias._version, c.bias.data_ptr())
+                         for group in convs for c in group)
+        if versions != self._versions:
+            self._weights = [torch.cat([_pack_weight(c) for c in group], dim=1).contiguous() for group in convs]
+            # conv3d under autocast casts the bias to bf16 as well
+            self._biases = [torch.cat([c.bias.detach().to(torch.bfloat16).float() for c in group]).contiguous()
+                            for group in convs]
+            self._wptr = _lib.ptr_array(self._weights)
+            self._bptr = _lib.ptr_array(self._biases)
+            self._versions = versions
+        return self._wptr, self._bptr
+
+    def __call__(self, h: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
+        h, hsb, hsc, hst = _strides5(h, "h", HIDDEN)
+        x, xsb, xsc, xst = _strides5(x, "x", INPUT)
+        b, _, T, H, W = h.shape
+        if tuple(x.shape) != (b, INPUT, T, H, W):
+            raise RuntimeError(f"x must be ({b}, {INPUT}, {T}, {H}, {W}), got {tuple(x.shape)}")
+        wptr, bptr = self._params()
+        key = (b, T, H, W, h.device)
+        ws = self._ws.get(key)
+        if ws is None:
+            n = ctypes.c_size_t()
+            _lib.check(self.lib.ppm_sepconv_gru3d_workspace(b, T, H, W, ctypes.byref(n)), "ppm_sepconv_gru3d_workspace")
+            self._ws.clear()                                     # one shape at a time (levels alternate rarely)
+            ws = self._ws[key] = torch.empty(n.value, dtype=torch.uint8, device=h.device)
+        out = torch.empty(b, HIDDEN, T, H, W, dtype=torch.bfloat16, device=h.device)
+        _lib.check(self.lib.ppm_sepconv_gru3d(h.data_ptr(), _lib.dtype_code(h), hsb, hsc, hst, x.data_ptr(),
+                                              _lib.dtype_code(x), xsb, xsc, xst, wptr, bptr, b, T, H, W, ws.data_ptr(),
+                                              ws.numel(), out.data_ptr(), _lib.PPM_BF16, _lib.stream_ptr()),
+                   "ppm_sepconv_gru3d")
+        return out
+
+
+_ATTR = "_ppmstereo_b200_gru"
+
+
+def gru_forward(self, h: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
+    """Replacement for ``SKSepConvGRU3D.forward`` installed by ``ppmstereo_b200.install``: the sm_100a kernel in the
+    reference's bf16 autocast regime with a bf16 hidden state on a CUDA device (what PPMStereoModel runs); the module's
+    own forward otherwise (fp32 models, training)."""
+    if (h.is_cuda and h.dtype == torch.bfloat16 and torch.is_autocast_enabled()
+            and torch.get_autocast_gpu_dtype() == torch.bfloat16 and not torch.is_grad_enabled()):
+        impl = self.__dict__.get(_ATTR)
+        if impl is None:
+            impl = SepConvGRU3D(self)
+            self.__dict__[_ATTR] = impl
+        return impl(h, x)
+    return type(self)._ppm_reference_forward(self, h, x)

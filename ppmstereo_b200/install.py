@@ -14,7 +14,10 @@ from __future__ import annotations
 import torch
 import torch.nn.functional as F
 
+import sys
+
 from .corr import CorrBlock1D
+from .gru import gru_forward
 from .memory import C, PPMMemory, softmax_scale
 from .upsample import convex_upsample
 from .window import forward_batch_test
@@ -73,8 +76,24 @@ def forward_update_block(self, image1, update_block, corr_fn, flow, net, inp, mo
 _ORIGINALS = "_ppmstereo_b200_originals"
 
 
-def install(ppmstereo_module):
-    """Patch the reference module in place; returns it.  Idempotent; ``uninstall`` restores the originals."""
+def _gru_class(ppmstereo_module):
+    """The reference's SKSepConvGRU3D class (models/core/ppmtereo_update.py:254), found through the module that
+    defines SequenceUpdateBlock3D (imported by name at models/core/ppmstereo.py:17-24)."""
+    upd = sys.modules.get(ppmstereo_module.SequenceUpdateBlock3D.__module__)
+    return getattr(upd, "SKSepConvGRU3D", None)
+
+
+def install(ppmstereo_module, gru: bool = True):
+    """Patch the reference module in place; returns it.  Idempotent; ``uninstall`` restores the originals.
+    ``gru=False`` leaves SKSepConvGRU3D on the reference's cuDNN path (SURVEY 8a rows only)."""
+    cls_gru = _gru_class(ppmstereo_module)
+    if cls_gru is not None:
+        if gru and not hasattr(cls_gru, "_ppm_reference_forward"):
+            cls_gru._ppm_reference_forward = cls_gru.forward
+            cls_gru.forward = gru_forward                                   # K5 (ppmtereo_update.py:291-312)
+        elif not gru and hasattr(cls_gru, "_ppm_reference_forward"):
+            cls_gru.forward = cls_gru._ppm_reference_forward
+            del cls_gru._ppm_reference_forward
     if not hasattr(ppmstereo_module, _ORIGINALS):
         cls = ppmstereo_module.PPMStereo
         setattr(ppmstereo_module, _ORIGINALS, {
@@ -90,6 +109,10 @@ def install(ppmstereo_module):
 
 def uninstall(ppmstereo_module):
     """Put the reference's own CorrBlock1D / forward_update_block / forward_batch_test back."""
+    cls_gru = _gru_class(ppmstereo_module)
+    if cls_gru is not None and hasattr(cls_gru, "_ppm_reference_forward"):
+        cls_gru.forward = cls_gru._ppm_reference_forward
+        del cls_gru._ppm_reference_forward
     orig = getattr(ppmstereo_module, _ORIGINALS, None)
     if orig is not None:
         ppmstereo_module.CorrBlock1D = orig["CorrBlock1D"]

@@ -1,0 +1,102 @@
+"""K5 SKSepConvGRU3D: the sm_100a kernel against (i) the reference's own module run by torch /
+cuDNN on the same GPU under bf16 autocast (staged reference sources, oracle/stage_ref.py) and (ii) the CPU oracle's
+bf16-mode restatement (oracle/ppm_oracle.py::sk_sep_conv_gru3d, pinned on the reference module in
+tests/test_oracle_golden.py).
+
+Bar: the unit is three chained gated stages whose every intermediate is a bf16 tensor.  Two correct evaluations that
+differ only in fp32 accumulation order flip a bf16 rounding of a conv output here and there (one ulp = 2^-8 relative);
+a flip in stage 1 propagates through stages 2-3 with gains < 1 (sigmoid / tanh gates, |h| <= 1).  So: max |diff| <= 4
+bf16 ulps of the unit range (2^-6), mean |diff| <= 2e-4 -- and cuDNN-vs-oracle is reported next to ours for scale."""
+import importlib
+
+import pytest
+import torch
+
+from oracle import ppm_oracle as O
+from oracle import ref_import
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def env():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    if not ref_import.available():
+        pytest.skip("reference sources not staged")
+    import ppmstereo_b200 as P
+    ref_import.load_reference()
+    upd = importlib.import_module("models.core.ppmtereo_update")
+    torch.manual_seed(0)
+    gru = upd.SKSepConvGRU3D(hidden_dim=128, input_dim=384).cuda().eval()
+    return P, gru
+
+
+def make(b, T, H, W, seed):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    h = torch.tanh(torch.randn(b, 128, T, H, W, generator=g, device="cuda")).bfloat16()
+    x = torch.randn(b, 384, T, H, W, generator=g, device="cuda")
+    return h, x
+
+
+@pytest.mark.parametrize("shape", [(1, 4, 6, 9), (1, 5, 20, 32), (2, 3, 23, 40), (1, 6, 16, 64), (1, 20, 46, 80)])
+def test_vs_reference_module_under_autocast(env, shape):
+    P, gru = env
+    h, x = make(*shape, seed=sum(shape))
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        want = gru(h, x)
+    assert want.dtype == torch.bfloat16
+    got = P.SepConvGRU3D(gru)(h, x)
+    torch.cuda.synchronize()
+    assert got.shape == want.shape and got.dtype == torch.bfloat16
+    d = (got.float() - want.float()).abs()
+    same = float((got == want).float().mean())
+    print(f"GRU {shape}: {same * 100:.2f} % bit-identical to torch/cuDNN, max |diff| {float(d.max()):.4f}, mean {float(d.mean()):.2e}")
+    assert float(d.max()) <= 2.0 ** -6
+    assert float(d.mean()) <= 2e-4
+    assert same >= 0.97
+
+
+@pytest.mark.parametrize("shape", [(1, 4, 6, 9), (2, 3, 5, 17)])
+def test_vs_cpu_oracle_bf16_mode(env, shape):
+    P, gru = env
+    h, x = make(*shape, seed=7 + sum(shape))
+    params = {k: v.detach().float().cpu() for k, v in gru.state_dict().items()}
+    want = O.sk_sep_conv_gru3d(h.float().cpu(), x.cpu(), params, mode="bf16")
+    got = P.SepConvGRU3D(gru)(h, x).float().cpu()
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        cudnn = gru(h, x).float().cpu()
+    d = (got - want).abs()
+    print(f"GRU {shape} vs oracle: max {float(d.max()):.4f} mean {float(d.mean()):.2e}; cuDNN vs oracle: max "
+          f"{float((cudnn - want).abs().max()):.4f} mean {float((cudnn - want).abs().mean()):.2e}")
+    assert float(d.max()) <= 2.0 ** -6
+    assert float(d.mean()) <= 2e-4
+
+
+def test_strided_frame_major_inputs_and_fp32_hidden(env):
+    """The model hands over views: h / x are (b, C, T, H, W) views of frame-major (b*T, C, H, W) tensors."""
+    P, gru = env
+    b, T, H, W = 1, 5, 12, 20
+    h, x = make(b, T, H, W, seed=3)
+    hv = h.permute(0, 2, 1, 3, 4).contiguous().permute(0, 2, 1, 3, 4)             # frame-major storage
+    xv = x.permute(0, 2, 1, 3, 4).contiguous().permute(0, 2, 1, 3, 4)
+    assert not hv.is_contiguous()
+    k = P.SepConvGRU3D(gru)
+    assert torch.equal(k(hv, xv), k(h, x))
+    assert torch.equal(k(h, x.bfloat16()), k(h, x))                                # the cast the conv would do anyway
+
+
+def test_weights_are_repacked_when_parameters_change(env):
+    P, gru = env
+    h, x = make(1, 3, 6, 16, seed=5)
+    k = P.SepConvGRU3D(gru)
+    a = k(h, x)
+    with torch.no_grad():
+        gru.convq3.bias.add_(0.5)
+    try:
+        b_ = k(h, x)
+        assert not torch.equal(a, b_)
+    finally:
+        with torch.no_grad():
+            gru.convq3.bias.sub_(0.5)
+    assert torch.equal(k(h, x), a)
