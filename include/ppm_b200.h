@@ -185,8 +185,11 @@ PPM_API int ppm_convex_upsample(const float* flow, const void* mask, int mask_dt
  *   0: convz1.0 | convr1.0 stacked on Cout (15, 256, 512)   1: convz1.2 (5,128,128)   2: convr1.2 (5,128,128)
  *   3: convq1 (5,128,512)   4: convz2 | convr2 (5,256,512)   5: convq2   6: convz3 | convr3   7: convq3
  * biases[8]: fp32 arrays of Cout values (the bf16-rounded biases), same order.
+ *   h_dtype selects the reference's type promotion: a bf16 h makes r*h, (1-z)*h and the final sum bf16 ops; an fp32 h
+ *   (what PPMStereo hands over: its SST blocks return fp32) makes (1-z)*h and the sum fp32 ops, so the state keeps fp32
+ *   precision from iteration to iteration (the convs still see bf16(h)).  Pass out_dtype = h_dtype for the reference's result.
  * workspace: ppm_sepconv_gru3d_workspace bytes, 256-byte aligned (channels-last bf16 copies of x, h, r*h, z and the
- * stage-1 GELU tensor).  out: (b,128,T,H,W) contiguous, out_dtype. */
+ * stage-1 GELU tensor, plus the fp32 state).  out: (b,128,T,H,W) contiguous, out_dtype. */
 PPM_API int ppm_sepconv_gru3d_workspace(int b, int T, int H, int W, size_t* bytes);
 PPM_API int ppm_sepconv_gru3d(const void* h, int h_dtype, int64_t hsb, int64_t hsc, int64_t hst, const void* x,
                       int x_dtype, int64_t xsb, int64_t xsc, int64_t xst, const void* const* weights,

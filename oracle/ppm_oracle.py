@@ -372,19 +372,24 @@ def _sep_conv(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor, axis: i
     return rnd(rnd(out) + rnd(bias.float()).view(1, -1, 1, 1, 1))
 
 
-def sk_sep_conv_gru3d(h: torch.Tensor, x: torch.Tensor, params: dict, mode: str = "fp32") -> torch.Tensor:
+def sk_sep_conv_gru3d(h: torch.Tensor, x: torch.Tensor, params: dict, mode: str = "fp32",
+                      hidden: str = "bf16") -> torch.Tensor:
     """SKSepConvGRU3D.forward(h, x) (ppmtereo_update.py:291-312).  h (b,128,T,H,W), x (b,384,T,H,W); ``params`` maps
     the module's state-dict names ('convz1.0.weight', ..., 'convq3.bias') to tensors.
 
     mode "fp32": the reference's CPU arithmetic.
     mode "bf16": the reference's GPU arithmetic under autocast (ppmstereo.py:568): every conv3d runs in bf16 (operands
       and result rounded, fp32 accumulation); gelu / sigmoid / tanh of a bf16 tensor return bf16; the products and sums
-      of the gate (r*h, (1-z)*h, z*q, their sum) are bf16 ops when h is bf16 -- each rounds once.  h is rounded to bf16
-      on entry in this mode (the model hands over a bf16 hidden state: tanh under autocast, ppmstereo.py:631)."""
+      of the gate (r*h, (1-z)*h, z*q, their sum) are bf16 ops when h is bf16 (``hidden="bf16"``; h rounded on entry)
+      -- each rounds once.  ``hidden="fp32"`` is what PPMStereo actually hands over (its SST blocks return fp32, so
+      tanh(net) is fp32, ppmstereo.py:631, 661): torch's type promotion then makes (1-z)*h and the final sum fp32 ops
+      (the state keeps fp32 precision), r*h is an fp32 product that the next conv's autocast cast rounds to bf16, and
+      the convs see bf16(h)."""
     rnd = bf16_round if mode == "bf16" else (lambda t: t)
+    hrnd = rnd if hidden == "bf16" else (lambda t: t)
     gelu = torch.nn.functional.gelu
     p = params
-    h = rnd(h.float())
+    h = hrnd(h.float())
     x = x.float()
     for stage, axis in ((1, 4), (2, 3), (3, 2)):                                   # horizontal, vertical, time
         hx = torch.cat([h, x], dim=1)
@@ -400,5 +405,5 @@ def sk_sep_conv_gru3d(h: torch.Tensor, x: torch.Tensor, params: dict, mode: str 
         rh = rnd(r * h)
         q = rnd(torch.tanh(_sep_conv(torch.cat([rh, x], dim=1), p[f"convq{stage}.weight"], p[f"convq{stage}.bias"],
                                      axis, rnd)))
-        h = rnd(rnd(rnd(1 - z) * h) + rnd(z * q))
+        h = hrnd(hrnd(rnd(1 - z) * h) + rnd(z * q))
     return h

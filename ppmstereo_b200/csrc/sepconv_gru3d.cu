@@ -53,7 +53,9 @@ struct GruGemmParams {
   const float* bias;                 // [N] (bf16-representable values)
   __nv_bfloat16* dst0;               // GELU: G [P, N]; Z / ZR: Z [P, 128]
   __nv_bfloat16* dst1;               // R / ZR: RH [P, 128]
-  __nv_bfloat16* hbuf;               // [P, 128] current hidden state (read by R / ZR / Q, rewritten by Q)
+  __nv_bfloat16* hbuf;               // [P, 128] bf16(hidden state): the conv operand (rewritten by Q)
+  float* hstate;                     // [P, 128] the hidden state itself, fp32 storage (read by R / ZR / Q, rewritten by Q)
+  int h_fp32;                        // 1: the caller's h is fp32 -> products / sums with h are fp32 ops (see below)
   const __nv_bfloat16* zbuf;         // Q: Z [P, 128]
   void* out;                         // Q, last stage: (b, 128, T, H, W) contiguous, or nullptr
   int out_dtype;
@@ -87,7 +89,7 @@ __device__ __forceinline__ float gr_ld(const __nv_bfloat16* p) { return __bfloat
 template <typename SrcT>
 __global__ void __launch_bounds__(256) gru_pack_kernel(const SrcT* __restrict__ src, long long sb, long long sc,
                                                        long long st, int T, int HW, int C, int dst_c, int c_off,
-                                                       __nv_bfloat16* __restrict__ dst) {
+                                                       __nv_bfloat16* __restrict__ dst, float* __restrict__ dst32) {
   __shared__ float tile[64][33];
   const int p0 = blockIdx.x * 32, c0 = blockIdx.y * 64, frame = blockIdx.z;
   const int bb = frame / T, t = frame - bb * T;
@@ -108,6 +110,11 @@ __global__ void __launch_bounds__(256) gru_pack_kernel(const SrcT* __restrict__ 
     v.w = pack_bf16x2(tile[cq + 6][px], tile[cq + 7][px]);
     __nv_bfloat16* d = dst + (static_cast<long long>(frame) * HW + p0 + px) * dst_c + c_off + c0 + cq;
     *reinterpret_cast<uint4*>(d) = v;
+    if (dst32) {                                           // unrounded copy (the fp32 hidden state)
+      float* d32 = dst32 + (static_cast<long long>(frame) * HW + p0 + px) * dst_c + c_off + c0 + cq;
+      *reinterpret_cast<float4*>(d32) = make_float4(tile[cq + 0][px], tile[cq + 1][px], tile[cq + 2][px], tile[cq + 3][px]);
+      *reinterpret_cast<float4*>(d32 + 4) = make_float4(tile[cq + 4][px], tile[cq + 5][px], tile[cq + 6][px], tile[cq + 7][px]);
+    }
   }
 }
 
@@ -273,22 +280,35 @@ gru_gemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constan
             for (int e = 0; e < 8; ++e) v[e] = gr_sigmoid(v[e]);
             *reinterpret_cast<uint4*>(p.dst0 + pos * kGrHidden + ch) = gr_pack8(v);
           } else if (mode == GR_EPI_R) {
-            float h[8];
-            gr_unpack8(*reinterpret_cast<const uint4*>(p.hbuf + pos * kGrHidden + ch), h);
+            // r * h: a bf16 op for a bf16 h; for an fp32 h an fp32 product that the next conv's autocast cast rounds to
+            // bf16 -- fp32(r*h) then bf16 in both cases (the fp32 product of two bf16 values is exact)
+            const float4 h0 = *reinterpret_cast<const float4*>(p.hstate + pos * kGrHidden + ch);
+            const float4 h1 = *reinterpret_cast<const float4*>(p.hstate + pos * kGrHidden + ch + 4);
+            const float h[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
             #pragma unroll
-            for (int e = 0; e < 8; ++e) v[e] = bf16_round_f(gr_sigmoid(v[e])) * h[e];
+            for (int e = 0; e < 8; ++e) v[e] = __fmul_rn(bf16_round_f(gr_sigmoid(v[e])), h[e]);
             *reinterpret_cast<uint4*>(p.dst1 + pos * kGrHidden + ch) = gr_pack8(v);
           } else {                                        // GR_EPI_Q
-            float h[8], z[8];
-            gr_unpack8(*reinterpret_cast<const uint4*>(p.hbuf + pos * kGrHidden + ch), h);
+            float z[8];
+            float* hs = p.hstate + pos * kGrHidden + ch;
+            const float4 h0 = *reinterpret_cast<const float4*>(hs);
+            const float4 h1 = *reinterpret_cast<const float4*>(hs + 4);
+            const float h[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
             gr_unpack8(*reinterpret_cast<const uint4*>(p.zbuf + pos * kGrHidden + ch), z);
             #pragma unroll
             for (int e = 0; e < 8; ++e) {
+              // (1 - z) * h + z * q: 1 - z and z * q are bf16 ops (z, q bf16).  bf16 h: the product and the sum are bf16
+              // ops too.  fp32 h (what the model hands over: the SST blocks return fp32): type promotion makes both fp32.
               const float q = bf16_round_f(tanhf(v[e]));
-              const float a = bf16_round_f(bf16_round_f(1.f - z[e]) * h[e]);
+              float a = __fmul_rn(bf16_round_f(1.f - z[e]), h[e]);
               const float bq = bf16_round_f(z[e] * q);
-              v[e] = bf16_round_f(a + bq);
+              if (!p.h_fp32) a = bf16_round_f(a);
+              float hn = __fadd_rn(a, bq);
+              if (!p.h_fp32) hn = bf16_round_f(hn);
+              v[e] = hn;
             }
+            *reinterpret_cast<float4*>(hs) = make_float4(v[0], v[1], v[2], v[3]);
+            *reinterpret_cast<float4*>(hs + 4) = make_float4(v[4], v[5], v[6], v[7]);
             *reinterpret_cast<uint4*>(p.hbuf + pos * kGrHidden + ch) = gr_pack8(v);
             if (p.out) {
               const long long o = ((static_cast<long long>(bb) * kGrHidden + ch) * p.T + t) * HW + static_cast<long long>(y) * p.W + x;
@@ -379,10 +399,10 @@ static int gru_launch(const CUtensorMap& a0, const CUtensorMap& a1, const CUtens
 
 template <typename SrcT>
 static int gru_pack(const void* src, long long sb, long long sc, long long st_, const GruShape& s, int C, int dst_c,
-                    int c_off, __nv_bfloat16* dst, cudaStream_t st) {
+                    int c_off, __nv_bfloat16* dst, float* dst32, cudaStream_t st) {
   const int HW = s.H * s.W;
   dim3 grid((HW + 31) / 32, (C + 63) / 64, s.b * s.T);
-  gru_pack_kernel<SrcT><<<grid, 256, 0, st>>>(static_cast<const SrcT*>(src), sb, sc, st_, s.T, HW, C, dst_c, c_off, dst);
+  gru_pack_kernel<SrcT><<<grid, 256, 0, st>>>(static_cast<const SrcT*>(src), sb, sc, st_, s.T, HW, C, dst_c, c_off, dst, dst32);
   PPM_CUDA(cudaGetLastError());
   return PPM_OK;
 }
@@ -392,7 +412,7 @@ static int gru_pack(const void* src, long long sb, long long sc, long long st_, 
 extern "C" int ppm_sepconv_gru3d_workspace(int b, int T, int H, int W, size_t* bytes) {
   PPM_CHECK(b > 0 && T > 0 && H > 0 && W > 0 && bytes, PPM_ERR_ARG, "ppm_sepconv_gru3d_workspace: bad argument");
   const size_t P = static_cast<size_t>(b) * T * H * W;
-  *bytes = P * (384 + 128 + 128 + 128 + 256) * 2;       // X, H, RH, Z, G  (bf16, channels-last)
+  *bytes = P * ((384 + 128 + 128 + 128 + 256) * 2 + 128 * 4);   // X, H, RH, Z, G (bf16) + hidden state (fp32), channels-last
   return PPM_OK;
 }
 
@@ -422,13 +442,14 @@ extern "C" int ppm_sepconv_gru3d(const void* h, int h_dtype, int64_t hsb, int64_
   __nv_bfloat16* RH = Hb + s.P * 128;
   __nv_bfloat16* Z = RH + s.P * 128;
   __nv_bfloat16* G = Z + s.P * 128;
+  float* Hs = reinterpret_cast<float*>(G + s.P * 256);
   int rc;
   // channels-last bf16 operands (the cast conv3d's autocast performs on its input)
-  if (x_dtype == PPM_BF16) rc = gru_pack<__nv_bfloat16>(x, xsb, xsc, xst, s, 384, 384, 0, X, st);
-  else rc = gru_pack<float>(x, xsb, xsc, xst, s, 384, 384, 0, X, st);
+  if (x_dtype == PPM_BF16) rc = gru_pack<__nv_bfloat16>(x, xsb, xsc, xst, s, 384, 384, 0, X, nullptr, st);
+  else rc = gru_pack<float>(x, xsb, xsc, xst, s, 384, 384, 0, X, nullptr, st);
   if (rc) return rc;
-  if (h_dtype == PPM_BF16) rc = gru_pack<__nv_bfloat16>(h, hsb, hsc, hst, s, 128, 128, 0, Hb, st);
-  else rc = gru_pack<float>(h, hsb, hsc, hst, s, 128, 128, 0, Hb, st);
+  if (h_dtype == PPM_BF16) rc = gru_pack<__nv_bfloat16>(h, hsb, hsc, hst, s, 128, 128, 0, Hb, Hs, st);
+  else rc = gru_pack<float>(h, hsb, hsc, hst, s, 128, 128, 0, Hb, Hs, st);
   if (rc) return rc;
   CUtensorMap mX, mH, mRH, mG, mW[8];
   if ((rc = gru_act_map(&mX, X, 384, s))) return rc;
@@ -442,7 +463,7 @@ extern "C" int ppm_sepconv_gru3d(const void* h, int h_dtype, int64_t hsb, int64_
     if ((rc = gru_w_map(&mW[i], weights[i], w_cin[i], w_n[i], w_taps[i]))) return rc;
 
   GruGemmParams p{};
-  p.hbuf = Hb; p.zbuf = Z; p.out = nullptr; p.out_dtype = out_dtype;
+  p.hbuf = Hb; p.hstate = Hs; p.h_fp32 = h_dtype == PPM_F32 ? 1 : 0; p.zbuf = Z; p.out = nullptr; p.out_dtype = out_dtype;
   // ---- stage 1: along W.  z / r = Conv(15) -> GELU -> Conv(5) (ppmtereo_update.py:257-266)
   p.bias = biases[0]; p.N = 256; p.taps = 15; p.axis = 0; p.mode = GR_EPI_GELU;
   p.seg0_chunks = 2; p.seg0_c0 = 0; p.seg1_chunks = 6; p.dst0 = G; p.dst1 = nullptr;

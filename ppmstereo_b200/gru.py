@@ -81,10 +81,10 @@ class SepConvGRU3D:
             _lib.check(self.lib.ppm_sepconv_gru3d_workspace(b, T, H, W, ctypes.byref(n)), "ppm_sepconv_gru3d_workspace")
             self._ws.clear()                                     # one shape at a time (levels alternate rarely)
             ws = self._ws[key] = torch.empty(n.value, dtype=torch.uint8, device=h.device)
-        out = torch.empty(b, HIDDEN, T, H, W, dtype=torch.bfloat16, device=h.device)
+        out = torch.empty(b, HIDDEN, T, H, W, dtype=h.dtype, device=h.device)     # the reference's type promotion
         _lib.check(self.lib.ppm_sepconv_gru3d(h.data_ptr(), _lib.dtype_code(h), hsb, hsc, hst, x.data_ptr(),
                                               _lib.dtype_code(x), xsb, xsc, xst, wptr, bptr, b, T, H, W, ws.data_ptr(),
-                                              ws.numel(), out.data_ptr(), _lib.PPM_BF16, _lib.stream_ptr()),
+                                              ws.numel(), out.data_ptr(), _lib.dtype_code(out), _lib.stream_ptr()),
                    "ppm_sepconv_gru3d")
         return out
 
@@ -94,9 +94,9 @@ _ATTR = "_ppmstereo_b200_gru"
 
 def gru_forward(self, h: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
     """Replacement for ``SKSepConvGRU3D.forward`` installed by ``ppmstereo_b200.install``: the sm_100a kernel in the
-    reference's bf16 autocast regime with a bf16 hidden state on a CUDA device (what PPMStereoModel runs); the module's
-    own forward otherwise (fp32 models, training)."""
-    if (h.is_cuda and h.dtype == torch.bfloat16 and torch.is_autocast_enabled()
+    reference's bf16 autocast regime on a CUDA device (what PPMStereoModel runs; hidden state fp32 or bf16); the
+    module's own forward otherwise (fp32 models, training)."""
+    if (h.is_cuda and h.dtype in (torch.bfloat16, torch.float32) and torch.is_autocast_enabled()
             and torch.get_autocast_gpu_dtype() == torch.bfloat16 and not torch.is_grad_enabled()):
         impl = self.__dict__.get(_ATTR)
         if impl is None:

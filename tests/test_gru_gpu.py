@@ -32,37 +32,42 @@ def env():
     return P, gru
 
 
-def make(b, T, H, W, seed):
+def make(b, T, H, W, seed, hdtype=torch.bfloat16):
     g = torch.Generator(device="cuda").manual_seed(seed)
-    h = torch.tanh(torch.randn(b, 128, T, H, W, generator=g, device="cuda")).bfloat16()
+    h = torch.tanh(torch.randn(b, 128, T, H, W, generator=g, device="cuda")).to(hdtype)
     x = torch.randn(b, 384, T, H, W, generator=g, device="cuda")
     return h, x
 
 
+@pytest.mark.parametrize("hdtype", [torch.float32, torch.bfloat16])
 @pytest.mark.parametrize("shape", [(1, 4, 6, 9), (1, 5, 20, 32), (2, 3, 23, 40), (1, 6, 16, 64), (1, 20, 46, 80)])
-def test_vs_reference_module_under_autocast(env, shape):
+def test_vs_reference_module_under_autocast(env, shape, hdtype):
+    """hdtype fp32 is what the model hands over (type promotion keeps the state in fp32); bf16 the other promotion."""
     P, gru = env
-    h, x = make(*shape, seed=sum(shape))
+    h, x = make(*shape, seed=sum(shape), hdtype=hdtype)
     with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
         want = gru(h, x)
-    assert want.dtype == torch.bfloat16
+    assert want.dtype == hdtype
     got = P.SepConvGRU3D(gru)(h, x)
     torch.cuda.synchronize()
-    assert got.shape == want.shape and got.dtype == torch.bfloat16
+    assert got.shape == want.shape and got.dtype == hdtype
     d = (got.float() - want.float()).abs()
-    same = float((got == want).float().mean())
-    print(f"GRU {shape}: {same * 100:.2f} % bit-identical to torch/cuDNN, max |diff| {float(d.max()):.4f}, mean {float(d.mean()):.2e}")
+    same = float(((got.float() - want.float()).abs() <= 1e-6).float().mean()) if hdtype == torch.float32 else float((got == want).float().mean())
+    print(f"GRU {shape} h {hdtype}: {same * 100:.2f} % bit-identical to torch/cuDNN, max |diff| {float(d.max()):.4f}, mean {float(d.mean()):.2e}")
     assert float(d.max()) <= 2.0 ** -6
     assert float(d.mean()) <= 2e-4
-    assert same >= 0.97
+    # (an fp32 state shows EVERY bf16 flip of a conv output as a different fp32 value; a bf16 state rounds most away)
+    assert same >= (0.97 if hdtype == torch.bfloat16 else 0.93)
 
 
+@pytest.mark.parametrize("hdtype", [torch.float32, torch.bfloat16])
 @pytest.mark.parametrize("shape", [(1, 4, 6, 9), (2, 3, 5, 17)])
-def test_vs_cpu_oracle_bf16_mode(env, shape):
+def test_vs_cpu_oracle_bf16_mode(env, shape, hdtype):
     P, gru = env
-    h, x = make(*shape, seed=7 + sum(shape))
+    h, x = make(*shape, seed=7 + sum(shape), hdtype=hdtype)
     params = {k: v.detach().float().cpu() for k, v in gru.state_dict().items()}
-    want = O.sk_sep_conv_gru3d(h.float().cpu(), x.cpu(), params, mode="bf16")
+    want = O.sk_sep_conv_gru3d(h.float().cpu(), x.cpu(), params, mode="bf16",
+                               hidden="fp32" if hdtype == torch.float32 else "bf16")
     got = P.SepConvGRU3D(gru)(h, x).float().cpu()
     with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
         cudnn = gru(h, x).float().cpu()

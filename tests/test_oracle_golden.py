@@ -96,3 +96,28 @@ def test_convex_upsample_matches_reference(golden_dir, kind):
     assert out.shape == ref.shape
     # bf16 mask = storage only: under the reference's CUDA autocast the softmax runs (and stays) in fp32
     assert (out - ref).abs().max() <= 1e-5 * ref.abs().max()   # fp32 summation order only
+
+
+def test_gru_oracle_matches_reference_module():
+    """SKSepConvGRU3D restated as shifted channel contractions (oracle) == the reference module (fp32, CPU)."""
+    import importlib
+    from oracle import ref_import
+    if not ref_import.available():
+        pytest.skip("reference tree not present")
+    ref_import.load_reference()
+    upd = importlib.import_module("models.core.ppmtereo_update")
+    torch.manual_seed(0)
+    gru = upd.SKSepConvGRU3D(hidden_dim=128, input_dim=384).eval()
+    g = torch.Generator().manual_seed(1)
+    for shape in ((1, 4, 6, 9), (2, 2, 3, 17)):
+        b, T, H, W = shape
+        h = torch.tanh(torch.randn(b, 128, T, H, W, generator=g))
+        x = torch.randn(b, 384, T, H, W, generator=g)
+        with torch.no_grad():
+            want = gru(h, x)
+        got = O.sk_sep_conv_gru3d(h, x, dict(gru.state_dict()))
+        assert float((got - want).abs().max()) <= 2e-6
+        # the bf16-autocast restatements stay within bf16 rounding of the fp32 result
+        for hidden in ("bf16", "fp32"):
+            lo = O.sk_sep_conv_gru3d(h, x, dict(gru.state_dict()), mode="bf16", hidden=hidden)
+            assert float((lo - want).abs().max()) <= 3e-2
