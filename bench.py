@@ -516,6 +516,36 @@ def main():
                                   "path in the number), CUDA events on the replay stream; traffic = dram bytes of "
                                   "one ncu --set full capture (profiles/)"})
         del blk
+        # K5: SKSepConvGRU3D at the same level, tensor-core bound.  The layer container below only
+        # states the unit's Conv3d shapes (include/ppm_b200.h, K5) with random-init weights; no reference code involved.
+        import torch.nn as nn
+
+        def _c(ci, k):
+            return nn.Conv3d(ci, 128, k, padding=tuple(x // 2 for x in k))
+
+        class _GruLayers(nn.Module):
+            def __init__(self):
+                super().__init__()
+                self.convz1 = nn.Sequential(_c(512, (1, 1, 15)), nn.GELU(), _c(128, (1, 1, 5)))
+                self.convr1 = nn.Sequential(_c(512, (1, 1, 15)), nn.GELU(), _c(128, (1, 1, 5)))
+                self.convq1 = _c(512, (1, 1, 5))
+                self.convz2, self.convr2, self.convq2 = _c(512, (1, 5, 1)), _c(512, (1, 5, 1)), _c(512, (1, 5, 1))
+                self.convz3, self.convr3, self.convq3 = _c(512, (5, 1, 1)), _c(512, (5, 1, 1)), _c(512, (5, 1, 1))
+
+        torch.manual_seed(11)
+        k5 = P.SepConvGRU3D(_GruLayers().to(dev))
+        gh = torch.tanh(torch.randn(1, 128, T4, h4, w4, generator=gk, device=dev))
+        gx = torch.randn(1, 384, T4, h4, w4, generator=gk, device=dev)
+        ms5 = time_kernel(lambda: k5(gh, gx), reps=3)
+        f5 = 2.0 * T4 * h4 * w4 * (512 * 128 * 35 + 2 * 128 * 128 * 5 + 6 * 512 * 128 * 5)
+        tpk = float(peaks()[0].get("bf16_tflops_sustained", 1400.0))
+        other.append({"kernel": "gru_gemm_kernel x 8 + packs (K5 SKSepConvGRU3D, SURVEY 8f rank 2, 1/4-res, T=20; the unit the "
+                                "installed model calls once per iteration; not part of the timed hot-path step)",
+                      "bound": "tensor", "achieved": f5 / (ms5 * 1e-3) / 1e12, "peak": tpk, "unit": "TFLOP/s",
+                      "frac": f5 / (ms5 * 1e-3) / 1e12 / tpk, "flops_per_call": f5, "avg_call_ms": ms5, "traffic": None,
+                      "note": "one whole unit (2 pack launches + 8 GEMM launches) replayed from a CUDA graph; FLOPs = 8.85 MFLOP "
+                              "per position (SURVEY 8f / DESIGN K5); ncu per-GEMM breakdown in profiles/r02_k5_gru.md"})
+        del k5, gh, gx
         same_box = None
         try:                                            # the library the reference calls at ppmstereo.py:550, same box
             if args.no_same_box:

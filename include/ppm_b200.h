@@ -195,6 +195,22 @@ PPM_API int ppm_sepconv_gru3d(const void* h, int h_dtype, int64_t hsb, int64_t h
                       int x_dtype, int64_t xsb, int64_t xsc, int64_t xst, const void* const* weights,
                       const float* const* biases, int b, int T, int H, int W, void* workspace,
                       size_t workspace_bytes, void* out, int out_dtype, void* stream);
+/* Byte offset, inside a ppm_sepconv_gru3d workspace, of the bf16 channels-last copy [b*T*H*W][128] of the unit's RESULT
+ * (valid after the call): ppm_flow_head3d can take it as `x_cl` instead of re-packing the (b,128,T,H,W) tensor. */
+PPM_API int ppm_sepconv_gru3d_state_offset(int b, int T, int H, int W, size_t* offset);
+
+/* ---------------------------------------------------------------------------------------
+ * K5b  FlowHead3D (models/core/ppmtereo_update.py:670-678): conv2(relu(conv1(x))), two 3x3x3
+ * Conv3d (128 -> 256 -> 2) in the bf16 autocast regime (each conv = bf16(bf16(acc) + bias), relu in bf16), on the K5
+ * shifted-GEMM kernel.  x (b,128,T,H,W) indexed x[b*sb + c*sc + t*st + y*W + x], fp32 or bf16 -- or x_cl != NULL: the same
+ * tensor already as bf16 channels-last [b*T*H*W][128] (then x may be NULL).  w1: bf16 [27][256][128]; b1: fp32 [256];
+ * w2: bf16 [27][64][256] with rows 2..63 zero; b2: fp32 [64] (entries 2..63 ignored).  Tap order (it*3 + ih)*3 + iw.
+ * workspace: ppm_flow_head3d_workspace bytes, 256-byte aligned.  out: (b,2,T,H,W) contiguous, out_dtype. */
+PPM_API int ppm_flow_head3d_workspace(int b, int T, int H, int W, size_t* bytes);
+PPM_API int ppm_flow_head3d(const void* x, int x_dtype, int64_t xsb, int64_t xsc, int64_t xst, const void* x_cl,
+                    const void* w1, const float* b1, const void* w2, const float* b2, int b, int T, int H, int W,
+                    void* workspace, size_t workspace_bytes, void* out, int out_dtype, void* stream);
+
 
 /* Bytes of the packed operands for (b, T, Kp, hw): q, k, v in that order. */
 PPM_API int ppm_pack_bytes(int b, int T, int Kp, int hw, size_t* q_bytes, size_t* k_bytes,

@@ -407,3 +407,27 @@ def sk_sep_conv_gru3d(h: torch.Tensor, x: torch.Tensor, params: dict, mode: str 
                                      axis, rnd)))
         h = hrnd(hrnd(rnd(1 - z) * h) + rnd(z * q))
     return h
+
+
+def conv3d_shifted(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor, rnd) -> torch.Tensor:
+    """nn.Conv3d(kernel (kt,kh,kw), padding (k-1)/2, stride 1) as a sum over taps of shifted channel contractions:
+    out[p] = bias + sum_{it,ih,iw} W[:, :, it, ih, iw] . in[p + (it,ih,iw) - pad], zeros outside.  ``rnd`` as in _sep_conv."""
+    co, ci, kt, kh, kw = weight.shape
+    w = rnd(weight.float())
+    xin = rnd(x.float())
+    b, _, T, H, W = x.shape
+    xp = torch.nn.functional.pad(xin, ((kw - 1) // 2,) * 2 + ((kh - 1) // 2,) * 2 + ((kt - 1) // 2,) * 2)
+    out = torch.zeros(b, co, T, H, W)
+    for it in range(kt):
+        for ih in range(kh):
+            for iw in range(kw):
+                out += torch.einsum("oc,bcthw->bothw", w[:, :, it, ih, iw], xp[:, :, it:it + T, ih:ih + H, iw:iw + W])
+    return rnd(rnd(out) + rnd(bias.float()).view(1, -1, 1, 1, 1))
+
+
+def flow_head3d(x: torch.Tensor, params: dict, mode: str = "fp32") -> torch.Tensor:
+    """FlowHead3D.forward (models/core/ppmtereo_update.py:670-678): conv2(relu(conv1(x))), two 3x3x3 Conv3d.
+    mode as in sk_sep_conv_gru3d (bf16: the autocast regime; each conv = bf16(bf16(acc) + bias))."""
+    rnd = bf16_round if mode == "bf16" else (lambda t: t)
+    y = torch.relu(conv3d_shifted(x, params["conv1.weight"], params["conv1.bias"], rnd))
+    return conv3d_shifted(y, params["conv2.weight"], params["conv2.bias"], rnd)

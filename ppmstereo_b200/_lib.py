@@ -45,6 +45,10 @@ SIGNATURES = {
     "ppm_sepconv_gru3d": (c_int, [c_void_p, c_int, c_int64, c_int64, c_int64, c_void_p, c_int, c_int64, c_int64, c_int64,
                                   POINTER(c_void_p), POINTER(c_void_p), c_int, c_int, c_int, c_int, c_void_p, c_size_t,
                                   c_void_p, c_int, c_void_p]),
+    "ppm_sepconv_gru3d_state_offset": (c_int, [c_int, c_int, c_int, c_int, POINTER(c_size_t)]),
+    "ppm_flow_head3d_workspace": (c_int, [c_int, c_int, c_int, c_int, POINTER(c_size_t)]),
+    "ppm_flow_head3d": (c_int, [c_void_p, c_int, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                c_int, c_int, c_int, c_int, c_void_p, c_size_t, c_void_p, c_int, c_void_p]),
     "ppm_pack_bytes": (c_int, [c_int, c_int, c_int, c_int, POINTER(c_size_t), POINTER(c_size_t),
                                POINTER(c_size_t)]),
 }

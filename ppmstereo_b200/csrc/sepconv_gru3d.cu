@@ -46,7 +46,9 @@ enum GruEpilogue : int {
   GR_EPI_Z = 1,        // z = bf16(sigmoid(bf16(acc + bias)))                           -> dst0 [P, 128]
   GR_EPI_R = 2,        // r likewise; rh = bf16(r * h)                                   -> dst1 [P, 128]
   GR_EPI_ZR = 3,       // N = 256: columns 0-127 as GR_EPI_Z, 128-255 as GR_EPI_R
-  GR_EPI_Q = 4         // q = bf16(tanh(bf16(acc + bias))); h = bf16(bf16(bf16(1-z)*h) + bf16(z*q)) -> hbuf (+ NCTHW out)
+  GR_EPI_Q = 4,        // q = bf16(tanh(bf16(acc + bias))); h = bf16(bf16(bf16(1-z)*h) + bf16(z*q)) -> hbuf (+ NCTHW out)
+  GR_EPI_RELU = 5,     // out = relu(c)   -> dst0 [P, dst_ld] at channel dst_c0 (channels-last bf16) and / or NCTHW `out`
+  GR_EPI_LINEAR = 6    // out = c         -> likewise          (c = bf16(bf16(acc) + bias) in every mode)
 };
 
 struct GruGemmParams {
@@ -59,8 +61,10 @@ struct GruGemmParams {
   const __nv_bfloat16* zbuf;         // Q: Z [P, 128]
   void* out;                         // Q, last stage: (b, 128, T, H, W) contiguous, or nullptr
   int out_dtype;
-  int N;                             // 128 or 256
-  int taps, axis;                    // axis: 0 = W, 1 = H, 2 = T
+  int N;                             // GEMM N: 64, 128, 192 or 256 (output channels padded with zero weights)
+  int n_valid;                       // RELU / LINEAR: output channels actually stored (<= N)
+  int dst_ld, dst_c0;                // RELU / LINEAR: row pitch (channels) and channel offset of dst0 (free concatenation)
+  int kw, kh, kt;                    // kernel footprint; tap d = (it*kh + ih)*kw + iw, offsets centred ((k-1)/2 padding)
   int seg0_chunks, seg0_c0;          // A channels: seg0_chunks 64-channel chunks of map_a0 starting at channel seg0_c0,
   int seg1_chunks;                   //             then seg1_chunks chunks of map_a1 starting at channel 0
   int b, T, H, W, bw, bh;
@@ -144,13 +148,15 @@ gru_gemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constan
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   __shared__ uint64_t bar_full[kGrStages], bar_empty[kGrStages], bar_acc_full[2], bar_acc_empty[2];
   __shared__ uint32_t tmem_slot;
+  __shared__ float s_bias[256];
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x < p.N) s_bias[threadIdx.x] = __ldg(p.bias + threadIdx.x);
   const int b_bytes = p.N * 128;
   const int stage_bytes = kGrABytes + b_bytes;
   const int n_chunks = p.seg0_chunks + p.seg1_chunks;
-  const int n_steps = p.taps * n_chunks;
-  const int pad = (p.taps - 1) / 2;
+  const int taps = p.kw * p.kh * p.kt;
+  const int n_steps = taps * n_chunks;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kGrStages; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 1); }
@@ -175,11 +181,11 @@ gru_gemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constan
         const int by = static_cast<int>(r % p.tiles_y); r /= p.tiles_y;
         const int t = static_cast<int>(r % p.T);
         const int bb = static_cast<int>(r / p.T);
-        for (int d = 0; d < p.taps; ++d) {
-          const int sh = d - pad;
-          const int cx = bx * p.bw + (p.axis == 0 ? sh : 0);
-          const int cy = by * p.bh + (p.axis == 1 ? sh : 0);
-          const int ct = t + (p.axis == 2 ? sh : 0);
+        for (int d = 0; d < taps; ++d) {
+          const int iw = d % p.kw, ih = (d / p.kw) % p.kh, it = d / (p.kw * p.kh);
+          const int cx = bx * p.bw + iw - (p.kw - 1) / 2;
+          const int cy = by * p.bh + ih - (p.kh - 1) / 2;
+          const int ct = t + it - (p.kt - 1) / 2;
           for (int kc = 0; kc < n_chunks; ++kc) {
             mbar_wait(&bar_empty[stage], ph);
             mbar_expect_tx(&bar_full[stage], stage_bytes);
@@ -254,6 +260,23 @@ gru_gemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constan
       for (int c = 0; c < n_chunks_e; ++c) {
         uint32_t acc[32];
         tmem_ld_x32(t_addr + c * 32, acc);
+        const int col0 = half * cols_per_warp + c * 32;   // column of acc[0] in the GEMM's N
+        int mode = p.mode, ch0 = col0;                    // ch0: channel inside the 128-wide gate tensors
+        if (mode == GR_EPI_ZR) { mode = col0 < kGrHidden ? GR_EPI_Z : GR_EPI_R; ch0 = col0 & (kGrHidden - 1); }
+        // the chunk's state / gate operands are requested before the accumulator wait: with two epilogue warps per
+        // scheduler nothing else hides their latency (ncu: the epilogue, not the MMAs, paced the K = 2560 GEMMs)
+        float4 hreg[8];
+        uint4 zreg[4];
+        if (valid && (mode == GR_EPI_R || mode == GR_EPI_Q)) {
+          const float4* hp = reinterpret_cast<const float4*>(p.hstate + pos * kGrHidden + ch0);
+          #pragma unroll
+          for (int e = 0; e < 8; ++e) hreg[e] = hp[e];
+          if (mode == GR_EPI_Q) {
+            const uint4* zp = reinterpret_cast<const uint4*>(p.zbuf + pos * kGrHidden + ch0);
+            #pragma unroll
+            for (int e = 0; e < 4; ++e) zreg[e] = zp[e];
+          }
+        }
         tmem_ld_wait();
         if (c == n_chunks_e - 1) {                        // this warp's last read of the accumulator
           tc_fence_before();
@@ -261,15 +284,12 @@ gru_gemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constan
           if (lane == 0) mbar_arrive(&bar_acc_empty[buf]);
         }
         if (!valid) continue;
-        const int col0 = half * cols_per_warp + c * 32;   // column of acc[0] in the GEMM's N
-        int mode = p.mode, ch0 = col0;                    // ch0: channel inside the 128-wide gate tensors
-        if (mode == GR_EPI_ZR) { mode = col0 < kGrHidden ? GR_EPI_Z : GR_EPI_R; ch0 = col0 & (kGrHidden - 1); }
         #pragma unroll
         for (int g = 0; g < 4; ++g) {                     // 4 groups of 8 channels = one 16-byte store each
           float v[8];
           #pragma unroll
           for (int e = 0; e < 8; ++e)
-            v[e] = bf16_round_f(bf16_round_f(__uint_as_float(acc[g * 8 + e])) + __ldg(p.bias + col0 + g * 8 + e));
+            v[e] = bf16_round_f(bf16_round_f(__uint_as_float(acc[g * 8 + e])) + s_bias[col0 + g * 8 + e]);
           const int ch = ch0 + g * 8;
           if (mode == GR_EPI_GELU) {
             #pragma unroll
@@ -282,19 +302,46 @@ gru_gemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constan
           } else if (mode == GR_EPI_R) {
             // r * h: a bf16 op for a bf16 h; for an fp32 h an fp32 product that the next conv's autocast cast rounds to
             // bf16 -- fp32(r*h) then bf16 in both cases (the fp32 product of two bf16 values is exact)
-            const float4 h0 = *reinterpret_cast<const float4*>(p.hstate + pos * kGrHidden + ch);
-            const float4 h1 = *reinterpret_cast<const float4*>(p.hstate + pos * kGrHidden + ch + 4);
+            const float4 h0 = hreg[2 * g], h1 = hreg[2 * g + 1];
             const float h[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
             #pragma unroll
             for (int e = 0; e < 8; ++e) v[e] = __fmul_rn(bf16_round_f(gr_sigmoid(v[e])), h[e]);
             *reinterpret_cast<uint4*>(p.dst1 + pos * kGrHidden + ch) = gr_pack8(v);
+          } else if (mode == GR_EPI_RELU || mode == GR_EPI_LINEAR) {
+            if (col0 + g * 8 < p.n_valid) {
+              if (mode == GR_EPI_RELU) {
+                #pragma unroll
+                for (int e = 0; e < 8; ++e) v[e] = fmaxf(v[e], 0.f);
+              }
+              if (p.dst0) {
+                if (col0 + g * 8 + 8 <= p.n_valid) {
+                  *reinterpret_cast<uint4*>(p.dst0 + pos * p.dst_ld + p.dst_c0 + col0 + g * 8) = gr_pack8(v);
+                } else {
+                  #pragma unroll
+                  for (int e = 0; e < 8; ++e)
+                    if (col0 + g * 8 + e < p.n_valid)
+                      p.dst0[pos * p.dst_ld + p.dst_c0 + col0 + g * 8 + e] = __float2bfloat16_rn(v[e]);
+                }
+              }
+              if (p.out) {
+                const long long cs = static_cast<long long>(p.T) * HW;
+                const long long o = ((static_cast<long long>(bb) * p.n_valid + col0 + g * 8) * p.T + t) * HW +
+                                    static_cast<long long>(y) * p.W + x;
+                #pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                  if (col0 + g * 8 + e < p.n_valid) {
+                    if (p.out_dtype == PPM_BF16) static_cast<__nv_bfloat16*>(p.out)[o + e * cs] = __float2bfloat16_rn(v[e]);
+                    else static_cast<float*>(p.out)[o + e * cs] = v[e];
+                  }
+                }
+              }
+            }
           } else {                                        // GR_EPI_Q
             float z[8];
             float* hs = p.hstate + pos * kGrHidden + ch;
-            const float4 h0 = *reinterpret_cast<const float4*>(hs);
-            const float4 h1 = *reinterpret_cast<const float4*>(hs + 4);
+            const float4 h0 = hreg[2 * g], h1 = hreg[2 * g + 1];
             const float h[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
-            gr_unpack8(*reinterpret_cast<const uint4*>(p.zbuf + pos * kGrHidden + ch), z);
+            gr_unpack8(zreg[g], z);
             #pragma unroll
             for (int e = 0; e < 8; ++e) {
               // (1 - z) * h + z * q: 1 - z and z * q are bf16 ops (z, q bf16).  bf16 h: the product and the sum are bf16
@@ -465,10 +512,10 @@ extern "C" int ppm_sepconv_gru3d(const void* h, int h_dtype, int64_t hsb, int64_
   GruGemmParams p{};
   p.hbuf = Hb; p.hstate = Hs; p.h_fp32 = h_dtype == PPM_F32 ? 1 : 0; p.zbuf = Z; p.out = nullptr; p.out_dtype = out_dtype;
   // ---- stage 1: along W.  z / r = Conv(15) -> GELU -> Conv(5) (ppmtereo_update.py:257-266)
-  p.bias = biases[0]; p.N = 256; p.taps = 15; p.axis = 0; p.mode = GR_EPI_GELU;
+  p.bias = biases[0]; p.N = 256; p.kw = 15; p.kh = 1; p.kt = 1; p.mode = GR_EPI_GELU;
   p.seg0_chunks = 2; p.seg0_c0 = 0; p.seg1_chunks = 6; p.dst0 = G; p.dst1 = nullptr;
   if ((rc = gru_launch(mH, mX, mW[0], p, s, st))) return rc;
-  p.bias = biases[1]; p.N = 128; p.taps = 5; p.mode = GR_EPI_Z; p.seg0_chunks = 2; p.seg0_c0 = 0; p.seg1_chunks = 0; p.dst0 = Z;
+  p.bias = biases[1]; p.N = 128; p.kw = 5; p.mode = GR_EPI_Z; p.seg0_chunks = 2; p.seg0_c0 = 0; p.seg1_chunks = 0; p.dst0 = Z;
   if ((rc = gru_launch(mG, mG, mW[1], p, s, st))) return rc;
   p.bias = biases[2]; p.mode = GR_EPI_R; p.seg0_c0 = 128; p.dst0 = nullptr; p.dst1 = RH;
   if ((rc = gru_launch(mG, mG, mW[2], p, s, st))) return rc;
@@ -477,12 +524,69 @@ extern "C" int ppm_sepconv_gru3d(const void* h, int h_dtype, int64_t hsb, int64_
   // ---- stages 2 (along H) and 3 (along T): z | r as one N = 256 GEMM, then q
   for (int stage = 2; stage <= 3; ++stage) {
     const int wi = stage == 2 ? 4 : 6;
-    p.axis = stage - 1; p.taps = 5;
+    p.kw = 1; p.kh = stage == 2 ? 5 : 1; p.kt = stage == 3 ? 5 : 1;
     p.bias = biases[wi]; p.N = 256; p.mode = GR_EPI_ZR; p.seg0_chunks = 2; p.seg0_c0 = 0; p.seg1_chunks = 6;
     p.dst0 = Z; p.dst1 = RH; p.out = nullptr;
     if ((rc = gru_launch(mH, mX, mW[wi], p, s, st))) return rc;
     p.bias = biases[wi + 1]; p.N = 128; p.mode = GR_EPI_Q; p.out = stage == 3 ? out : nullptr;
     if ((rc = gru_launch(mRH, mX, mW[wi + 1], p, s, st))) return rc;
   }
+  return PPM_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ FlowHead3D
+// FlowHead3D.forward (reference models/core/ppmtereo_update.py:670-678): conv2(relu(conv1(x))), two 3x3x3 Conv3d
+// (128 -> 256 -> 2), on the SAME shifted-GEMM kernel: a 3x3x3 footprint is 27 coordinate offsets of the TMA box.
+// conv2's two output channels are padded to N = 64 with zero weight rows (the GEMM is bound by its A traffic, not by MMA).
+extern "C" int ppm_sepconv_gru3d_state_offset(int b, int T, int H, int W, size_t* offset) {
+  PPM_CHECK(b > 0 && T > 0 && H > 0 && W > 0 && offset, PPM_ERR_ARG, "ppm_sepconv_gru3d_state_offset: bad argument");
+  *offset = static_cast<size_t>(b) * T * H * W * 384 * 2;       // the bf16 channels-last state [P, 128] follows X
+  return PPM_OK;
+}
+
+extern "C" int ppm_flow_head3d_workspace(int b, int T, int H, int W, size_t* bytes) {
+  PPM_CHECK(b > 0 && T > 0 && H > 0 && W > 0 && bytes, PPM_ERR_ARG, "ppm_flow_head3d_workspace: bad argument");
+  *bytes = static_cast<size_t>(b) * T * H * W * (128 + 256) * 2;
+  return PPM_OK;
+}
+
+extern "C" int ppm_flow_head3d(const void* x, int x_dtype, int64_t xsb, int64_t xsc, int64_t xst, const void* x_cl,
+                               const void* w1, const float* b1, const void* w2, const float* b2, int b, int T, int H,
+                               int W, void* workspace, size_t workspace_bytes, void* out, int out_dtype, void* stream) {
+  using namespace ppm;
+  PPM_CHECK((x || x_cl) && w1 && b1 && w2 && b2 && workspace && out, PPM_ERR_ARG, "ppm_flow_head3d: null pointer");
+  PPM_CHECK(b > 0 && T > 0 && H > 0 && W > 0 && static_cast<long long>(b) * T <= 65535, PPM_ERR_ARG, "ppm_flow_head3d: bad shape");
+  PPM_CHECK((x_cl || x_dtype == PPM_F32 || x_dtype == PPM_BF16) && (out_dtype == PPM_F32 || out_dtype == PPM_BF16), PPM_ERR_ARG,
+            "ppm_flow_head3d: bad dtype");
+  size_t need = 0;
+  ppm_flow_head3d_workspace(b, T, H, W, &need);
+  PPM_CHECK(workspace_bytes >= need, PPM_ERR_ARG, "ppm_flow_head3d: workspace of %zu bytes < %zu needed", workspace_bytes, need);
+  PPM_CHECK((reinterpret_cast<uintptr_t>(workspace) & 255) == 0 && (reinterpret_cast<uintptr_t>(x_cl) & 15) == 0 &&
+                (reinterpret_cast<uintptr_t>(w1) & 15) == 0 && (reinterpret_cast<uintptr_t>(w2) & 15) == 0,
+            PPM_ERR_ARG, "ppm_flow_head3d: misaligned pointer");
+  const GruShape s = gru_shape(b, T, H, W);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  __nv_bfloat16* Xc = static_cast<__nv_bfloat16*>(workspace);
+  __nv_bfloat16* Hd = Xc + s.P * 128;
+  int rc;
+  const __nv_bfloat16* a_in = static_cast<const __nv_bfloat16*>(x_cl);
+  if (!a_in) {
+    if (x_dtype == PPM_BF16) rc = gru_pack<__nv_bfloat16>(x, xsb, xsc, xst, s, 128, 128, 0, Xc, nullptr, st);
+    else rc = gru_pack<float>(x, xsb, xsc, xst, s, 128, 128, 0, Xc, nullptr, st);
+    if (rc) return rc;
+    a_in = Xc;
+  }
+  CUtensorMap mA, mH, mW1, mW2;
+  if ((rc = gru_act_map(&mA, a_in, 128, s))) return rc;
+  if ((rc = gru_act_map(&mH, Hd, 256, s))) return rc;
+  if ((rc = gru_w_map(&mW1, w1, 128, 256, 27))) return rc;
+  if ((rc = gru_w_map(&mW2, w2, 256, 64, 27))) return rc;
+  GruGemmParams p{};
+  p.kw = 3; p.kh = 3; p.kt = 3; p.out_dtype = out_dtype;
+  p.bias = b1; p.N = 256; p.n_valid = 256; p.mode = GR_EPI_RELU; p.seg0_chunks = 2; p.seg0_c0 = 0; p.seg1_chunks = 0;
+  p.dst0 = Hd; p.dst_ld = 256; p.dst_c0 = 0; p.out = nullptr;
+  if ((rc = gru_launch(mA, mA, mW1, p, s, st))) return rc;
+  p.bias = b2; p.N = 64; p.n_valid = 2; p.mode = GR_EPI_LINEAR; p.seg0_chunks = 4; p.dst0 = nullptr; p.out = out;
+  if ((rc = gru_launch(mH, mH, mW2, p, s, st))) return rc;
   return PPM_OK;
 }

@@ -86,6 +86,7 @@ class SepConvGRU3D:
                                               _lib.dtype_code(x), xsb, xsc, xst, wptr, bptr, b, T, H, W, ws.data_ptr(),
                                               ws.numel(), out.data_ptr(), _lib.dtype_code(out), _lib.stream_ptr()),
                    "ppm_sepconv_gru3d")
+        _remember_state(out, ws, self.lib)
         return out
 
 
@@ -104,3 +105,82 @@ def gru_forward(self, h: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
             self.__dict__[_ATTR] = impl
         return impl(h, x)
     return type(self)._ppm_reference_forward(self, h, x)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# FlowHead3D (models/core/ppmtereo_update.py:670-678) on the same kernel
+# ---------------------------------------------------------------------------------------------------------------
+_LAST_STATE = {}          # set by SepConvGRU3D.__call__: the result tensor and where its channels-last bf16 copy lives
+
+
+def _remember_state(out: torch.Tensor, ws: torch.Tensor, lib) -> None:
+    b, _, T, H, W = out.shape
+    off = ctypes.c_size_t()
+    _lib.check(lib.ppm_sepconv_gru3d_state_offset(b, T, H, W, ctypes.byref(off)), "ppm_sepconv_gru3d_state_offset")
+    _LAST_STATE.update(ptr=out.data_ptr(), version=out._version, shape=tuple(out.shape), device=out.device,
+                       cl_ptr=ws.data_ptr() + off.value, ws=ws, stream=_lib.stream_ptr())
+
+
+def _state_channels_last(x: torch.Tensor) -> int:
+    """Device address of the bf16 channels-last copy of ``x`` when ``x`` IS the tensor K5 just returned (same storage,
+    unmodified, same stream), else 0."""
+    s = _LAST_STATE
+    if (s and s["ptr"] == x.data_ptr() and s["version"] == x._version and s["shape"] == tuple(x.shape)
+            and s["device"] == x.device and x.is_contiguous() and s["stream"] == _lib.stream_ptr()):
+        return s["cl_ptr"]
+    return 0
+
+
+class FlowHead3D:
+    def __init__(self, module):
+        self.module = module
+        self.lib = _lib.load()
+        self._versions = None
+        self._ws: Dict[Tuple, torch.Tensor] = {}
+
+    def _params(self):
+        c1, c2 = self.module.conv1, self.module.conv2
+        versions = tuple((c.weight._version, c.weight.data_ptr(), c.bias._version, c.bias.data_ptr()) for c in (c1, c2))
+        if versions != self._versions:
+            self.w1 = _pack_weight(c1)                                                   # (27, 256, 128)
+            w2 = _pack_weight(c2)                                                        # (27, 2, 256)
+            self.w2 = torch.zeros(w2.shape[0], 64, w2.shape[2], dtype=torch.bfloat16, device=w2.device)
+            self.w2[:, :w2.shape[1]] = w2
+            self.b1 = c1.bias.detach().to(torch.bfloat16).float().contiguous()
+            self.b2 = torch.zeros(64, device=w2.device)
+            self.b2[:w2.shape[1]] = c2.bias.detach().to(torch.bfloat16).float()
+            self.n_out = w2.shape[1]
+            self._versions = versions
+
+    def __call__(self, x: torch.Tensor) -> torch.Tensor:
+        self._params()
+        if self.n_out != 2 or tuple(self.w1.shape) != (27, 256, HIDDEN):
+            raise RuntimeError("FlowHead3D kernel: expects Conv3d(128, 256, 3) -> Conv3d(256, 2, 3)")
+        cl = _state_channels_last(x)
+        x, sb, sc, st = _strides5(x, "x", HIDDEN)
+        b, _, T, H, W = x.shape
+        key = (b, T, H, W, x.device)
+        ws = self._ws.get(key)
+        if ws is None:
+            n = ctypes.c_size_t()
+            _lib.check(self.lib.ppm_flow_head3d_workspace(b, T, H, W, ctypes.byref(n)), "ppm_flow_head3d_workspace")
+            self._ws.clear()
+            ws = self._ws[key] = torch.empty(n.value, dtype=torch.uint8, device=x.device)
+        out = torch.empty(b, 2, T, H, W, dtype=torch.bfloat16, device=x.device)      # conv3d is an autocast-to-bf16 op
+        _lib.check(self.lib.ppm_flow_head3d(x.data_ptr(), _lib.dtype_code(x), sb, sc, st, cl or None, self.w1.data_ptr(),
+                                            self.b1.data_ptr(), self.w2.data_ptr(), self.b2.data_ptr(), b, T, H, W,
+                                            ws.data_ptr(), ws.numel(), out.data_ptr(), _lib.PPM_BF16, _lib.stream_ptr()),
+                   "ppm_flow_head3d")
+        return out
+
+
+def flow_head_forward(self, x: torch.Tensor) -> torch.Tensor:
+    """Replacement for ``FlowHead3D.forward`` installed by ``ppmstereo_b200.install`` (same regime rule as the GRU)."""
+    if (x.is_cuda and x.dim() == 5 and x.dtype in (torch.bfloat16, torch.float32) and torch.is_autocast_enabled()
+            and torch.get_autocast_gpu_dtype() == torch.bfloat16 and not torch.is_grad_enabled()):
+        impl = self.__dict__.get(_ATTR)
+        if impl is None:
+            impl = FlowHead3D(self)
+            self.__dict__[_ATTR] = impl
+        return impl(x)
+    return type(self)._ppm_reference_forward(self, x)

@@ -17,7 +17,7 @@ import torch.nn.functional as F
 import sys
 
 from .corr import CorrBlock1D
-from .gru import gru_forward
+from .gru import flow_head_forward, gru_forward
 from .memory import C, PPMMemory, softmax_scale
 from .upsample import convex_upsample
 from .window import forward_batch_test
@@ -76,24 +76,25 @@ def forward_update_block(self, image1, update_block, corr_fn, flow, net, inp, mo
 _ORIGINALS = "_ppmstereo_b200_originals"
 
 
-def _gru_class(ppmstereo_module):
-    """The reference's SKSepConvGRU3D class (models/core/ppmtereo_update.py:254), found through the module that
-    defines SequenceUpdateBlock3D (imported by name at models/core/ppmstereo.py:17-24)."""
+def _update_classes(ppmstereo_module):
+    """The reference's SKSepConvGRU3D (models/core/ppmtereo_update.py:254) and FlowHead3D (:670) classes with their
+    replacement forwards, found through the module that defines SequenceUpdateBlock3D (imported by name at
+    models/core/ppmstereo.py:17-24)."""
     upd = sys.modules.get(ppmstereo_module.SequenceUpdateBlock3D.__module__)
-    return getattr(upd, "SKSepConvGRU3D", None)
+    pairs = [(getattr(upd, "SKSepConvGRU3D", None), gru_forward), (getattr(upd, "FlowHead3D", None), flow_head_forward)]
+    return [(c, f) for c, f in pairs if c is not None]
 
 
 def install(ppmstereo_module, gru: bool = True):
     """Patch the reference module in place; returns it.  Idempotent; ``uninstall`` restores the originals.
-    ``gru=False`` leaves SKSepConvGRU3D on the reference's cuDNN path (SURVEY 8a rows only)."""
-    cls_gru = _gru_class(ppmstereo_module)
-    if cls_gru is not None:
-        if gru and not hasattr(cls_gru, "_ppm_reference_forward"):
-            cls_gru._ppm_reference_forward = cls_gru.forward
-            cls_gru.forward = gru_forward                                   # K5 (ppmtereo_update.py:291-312)
-        elif not gru and hasattr(cls_gru, "_ppm_reference_forward"):
-            cls_gru.forward = cls_gru._ppm_reference_forward
-            del cls_gru._ppm_reference_forward
+    ``gru=False`` leaves SKSepConvGRU3D and FlowHead3D on the reference's cuDNN path (SURVEY 8a rows only)."""
+    for cls, fwd in _update_classes(ppmstereo_module):                      # K5 / K5b (ppmtereo_update.py:291-312, :677)
+        if gru and not hasattr(cls, "_ppm_reference_forward"):
+            cls._ppm_reference_forward = cls.forward
+            cls.forward = fwd
+        elif not gru and hasattr(cls, "_ppm_reference_forward"):
+            cls.forward = cls._ppm_reference_forward
+            del cls._ppm_reference_forward
     if not hasattr(ppmstereo_module, _ORIGINALS):
         cls = ppmstereo_module.PPMStereo
         setattr(ppmstereo_module, _ORIGINALS, {
@@ -109,10 +110,10 @@ def install(ppmstereo_module, gru: bool = True):
 
 def uninstall(ppmstereo_module):
     """Put the reference's own CorrBlock1D / forward_update_block / forward_batch_test back."""
-    cls_gru = _gru_class(ppmstereo_module)
-    if cls_gru is not None and hasattr(cls_gru, "_ppm_reference_forward"):
-        cls_gru.forward = cls_gru._ppm_reference_forward
-        del cls_gru._ppm_reference_forward
+    for cls, _ in _update_classes(ppmstereo_module):
+        if hasattr(cls, "_ppm_reference_forward"):
+            cls.forward = cls._ppm_reference_forward
+            del cls._ppm_reference_forward
     orig = getattr(ppmstereo_module, _ORIGINALS, None)
     if orig is not None:
         ppmstereo_module.CorrBlock1D = orig["CorrBlock1D"]

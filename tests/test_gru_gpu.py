@@ -105,3 +105,51 @@ def test_weights_are_repacked_when_parameters_change(env):
         with torch.no_grad():
             gru.convq3.bias.sub_(0.5)
     assert torch.equal(k(h, x), a)
+
+
+# ------------------------------------------------------------------------------------------------ FlowHead3D (K5b)
+@pytest.fixture(scope="module")
+def flow_head(env):
+    upd = importlib.import_module("models.core.ppmtereo_update")
+    torch.manual_seed(3)
+    return upd.FlowHead3D(128, hidden_dim=256).cuda().eval()
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("shape", [(1, 4, 6, 9), (2, 3, 23, 40), (1, 1, 16, 64), (1, 20, 46, 80)])
+def test_flow_head_vs_reference_module_under_autocast(env, flow_head, shape, dtype):
+    P, _ = env
+    b, T, H, W = shape
+    x = torch.tanh(torch.randn(b, 128, T, H, W, generator=torch.Generator(device="cuda").manual_seed(sum(shape)),
+                               device="cuda")).to(dtype)
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        want = flow_head(x)
+    assert want.dtype == torch.bfloat16 and want.shape == (b, 2, T, H, W)
+    got = P.FlowHead3D(flow_head)(x)
+    assert got.shape == want.shape and got.dtype == torch.bfloat16
+    d = (got.float() - want.float()).abs()
+    same = float((got == want).float().mean())
+    scale = float(want.float().abs().max())
+    print(f"FlowHead3D {shape} {dtype}: {same * 100:.2f} % bit-identical to torch/cuDNN, max |diff| {float(d.max()):.4f} of {scale:.3f}")
+    assert float(d.max()) <= 2.0 ** -6 * max(scale, 1.0)
+    assert same >= 0.93          # (differences are single bf16 ulps of small values: see the max |diff| bound)
+
+
+def test_flow_head_vs_cpu_oracle_and_state_reuse(env, flow_head):
+    """(i) the CPU oracle's bf16-mode restatement; (ii) fed the tensor K5 just returned, the head reads K5's channels-last
+    state instead of re-packing -- same result as with a fresh copy of that tensor."""
+    P, gru = env
+    h, x = make(1, 4, 10, 24, seed=11, hdtype=torch.float32)
+    k = P.SepConvGRU3D(gru)
+    head = P.FlowHead3D(flow_head)
+    net = k(h, x)
+    from ppmstereo_b200 import gru as G
+    assert G._state_channels_last(net) != 0 and G._state_channels_last(net.clone()) == 0
+    a = head(net)                     # channels-last state of K5
+    b_ = head(net.clone())            # packed from the (b, c, T, H, W) tensor
+    assert torch.equal(a, b_)
+    params = {n: v.detach().float().cpu() for n, v in flow_head.state_dict().items()}
+    want = O.flow_head3d(net.float().cpu(), params, mode="bf16")
+    d = (a.float().cpu() - want).abs()
+    assert float(d.max()) <= 2.0 ** -6 * max(float(want.abs().max()), 1.0)
+    assert float(d.mean()) <= 2e-4

@@ -121,3 +121,20 @@ def test_gru_oracle_matches_reference_module():
         for hidden in ("bf16", "fp32"):
             lo = O.sk_sep_conv_gru3d(h, x, dict(gru.state_dict()), mode="bf16", hidden=hidden)
             assert float((lo - want).abs().max()) <= 3e-2
+
+
+def test_flow_head_oracle_matches_reference_module():
+    import importlib
+    from oracle import ref_import
+    if not ref_import.available():
+        pytest.skip("reference tree not present")
+    ref_import.load_reference()
+    upd = importlib.import_module("models.core.ppmtereo_update")
+    torch.manual_seed(1)
+    fh = upd.FlowHead3D(128, hidden_dim=256).eval()
+    x = torch.randn(2, 128, 3, 5, 7, generator=torch.Generator().manual_seed(2))
+    with torch.no_grad():
+        want = fh(x)
+    got = O.flow_head3d(x, dict(fh.state_dict()))
+    assert got.shape == want.shape == (2, 2, 3, 5, 7)
+    assert float((got - want).abs().max()) <= 1e-5
