@@ -224,7 +224,6 @@ def _reference_shell():
     from oracle import ref_import
     ref_import.load_reference()
     ppm = importlib.import_module("models.core.ppmstereo")
-    ppm.flash_attn_func = ref_import._flash_attn_cpu          # the CPU arm always uses the CPU stand-in for flash_attn
 
     class Shell:                                         # borrows the reference's unbound methods; no parameters needed
         mixed_precision = False
@@ -269,13 +268,20 @@ def cpu_sample_step(s, kind: str) -> float:
         T, _, h, w = s["f1"].shape
         inp = torch.zeros(T, C_QKV, h, w)
         net = torch.zeros(T, C_QKV, h, w)
-        t0 = time.perf_counter()
-        with torch.no_grad():
-            blk = r["ppm"].CorrBlock1D(s["f1"], s["f2"])
-            r["shell"].forward_update_block(image1=None, update_block=glue, corr_fn=blk, flow=s["flow"], net=net, inp=inp,
-                                            motion_hidden_state=None, attn_block=glue, predictions=[], uncertainties=[],
-                                            iters=SAMPLE_ITERS, interp_scale=4, t=T)
-        return time.perf_counter() - t0
+        from oracle import ref_import
+        saved = r["ppm"].flash_attn_func
+        r["ppm"].flash_attn_func = ref_import._flash_attn_cpu    # CUDA-only library -> CPU stand-in, for this call only
+        import contextlib
+        try:
+            t0 = time.perf_counter()
+            with torch.no_grad(), contextlib.redirect_stdout(sys.stderr):     # stdout carries the one JSON line only
+                blk = r["ppm"].CorrBlock1D(s["f1"], s["f2"])
+                r["shell"].forward_update_block(image1=None, update_block=glue, corr_fn=blk, flow=s["flow"], net=net,
+                                                inp=inp, motion_hidden_state=None, attn_block=glue, predictions=[],
+                                                uncertainties=[], iters=SAMPLE_ITERS, interp_scale=4, t=T)
+            return time.perf_counter() - t0
+        finally:
+            r["ppm"].flash_attn_func = saved
     from oracle import ppm_oracle as O          # the CPU baseline is the one place bench.py runs the oracle
     t0 = time.perf_counter()
     lv = O.corr_pyramid(s["f1"], s["f2"], mode="bf16")
@@ -614,7 +620,9 @@ def main():
             torch.cuda.empty_cache()
             from oracle import full_model, ref_import
             if ref_import.available():
-                fm = full_model.measure(CLIP_FRAMES, 720, 1280, KERNEL_SIZE, ITERS, reference=True)
+                import contextlib
+                with contextlib.redirect_stdout(sys.stderr):        # the reference prints ("iters 20"); stdout = one JSON line
+                    fm = full_model.measure(CLIP_FRAMES, 720, 1280, KERNEL_SIZE, ITERS, reference=True)
                 out["full_model"] = fm
             else:
                 out["full_model"] = {"unavailable": "reference sources not staged under oracle/_ref (python oracle/stage_ref.py)"}
