@@ -117,7 +117,7 @@ def run_clip(model, ppm, video, kernel_size: int, iters: int, installed: bool, s
     inst = importlib.import_module("ppmstereo_b200.install")       # (the package attribute `install` is the function)
     mem_mod = importlib.import_module("ppmstereo_b200.memory")
     if installed:
-        P.install(ppm)
+        P.install(ppm)                                   # defaults: K5 on, eager iterations
     else:
         P.uninstall(ppm)
     tm = PhaseTimer()

@@ -30,6 +30,27 @@ def _inference_only(inp, *params):
                            "installed model under torch.no_grad(), or ppmstereo_b200.uninstall() for training")
 
 
+# Replay of the update iteration from a CUDA graph -- built, measured, and left OFF by default.
+# Every kernel of the library launches on the caller's stream, allocates nothing and never synchronises, and the
+# reference's glue is plain torch modules, so one iteration can be captured per (window, level) and replayed: iteration 0
+# runs eagerly (it warms up cuDNN plans, function attributes, weight packs, and takes the `motion_hidden_state is None`
+# branch), iteration 1 is captured on static input buffers, iterations 1..n-1 are replays.  Measured on the B200
+# (scripts/small_clip_probe.py, BASELINE configs[0] size, 5 x 320 x 512, iters 10): eager 76 ms per forward, graph 91 ms
+# (12 frames: 130 vs 157 ms), with spikes to 2x when the allocator recycles the capture pools -- capturing and
+# instantiating a ~400-node graph per (window, level) costs more than 4-19 replays save, and at 720p the device is the
+# bound anyway (device time = wall time).  cuDNN may also pick another convolution algorithm under capture, so replayed
+# results equal the eager ones only to rounding (bit-identical at 320 x 512, 1e-4 px apart at 64 x 256).
+GRAPH = {"mode": "never"}           # "never" (default) | "auto" | "always"   (ppmstereo_b200.install(..., graph=...))
+GRAPH_MAX_POSITIONS = 400_000
+GRAPH_STATS = {"captured": 0, "replayed": 0, "eager": 0}
+
+
+def _use_graph(iters: int, positions: int, device) -> bool:
+    if device.type != "cuda" or GRAPH["mode"] == "never" or iters < 3 or torch.cuda.is_current_stream_capturing():
+        return False
+    return GRAPH["mode"] == "always" or (iters >= 4 and positions <= GRAPH_MAX_POSITIONS)
+
+
 def forward_update_block(self, image1, update_block, corr_fn, flow, net, inp, motion_hidden_state,
                          attn_block, predictions, uncertainties, iters, interp_scale, t):
     _inference_only(inp, attn_block.to_qk.weight, update_block.aggregator.beta)
@@ -46,8 +67,10 @@ def forward_update_block(self, image1, update_block, corr_fn, flow, net, inp, mo
     strive_time = torch.ones_like(sim_score)
     scale = softmax_scale(c)
     autocast = torch.autocast("cuda", dtype=torch.bfloat16, enabled=bool(self.mixed_precision))
-    flow_out = flow
-    for _ in range(iters):
+    beta = update_block.aggregator.beta
+
+    def step(flow, net, motion_hidden_state):
+        """One update iteration (ppmstereo.py:482-591)."""
         flow = flow.detach()
         out_corrs = corr_fn(flow)
         motion_features, motion_hidden_state, value = update_block.get_motion_and_value(
@@ -55,8 +78,7 @@ def forward_update_block(self, image1, update_block, corr_fn, flow, net, inp, mo
         uncertainty_score = update_block.get_uncertainty(torch.cat([net, value], dim=1))
         mf5 = motion_features.reshape(b, t, c, h, w).permute(0, 2, 1, 3, 4)
         v5 = value.reshape(b, t, c, h, w).permute(0, 2, 1, 3, 4)
-        motion_features_global, _ = memory.read(v5, mf5, sim_score, strive_time, uncertainty_score,
-                                                update_block.aggregator.beta, scale)
+        motion_features_global, _ = memory.read(v5, mf5, sim_score, strive_time, uncertainty_score, beta, scale)
         with autocast:
             net, up_mask, delta_flow = update_block(net, inp, motion_features, motion_features_global, t=t)
         flow = flow + delta_flow
@@ -68,8 +90,36 @@ def forward_update_block(self, image1, update_block, corr_fn, flow, net, inp, mo
         if interp_scale > 1:
             size = (interp_scale * flow_out.shape[2], interp_scale * flow_out.shape[3])
             flow_up = interp_scale * F.interpolate(flow_out, size=size, mode="bilinear", align_corners=True)
-        predictions.append(flow_up[:, :1])
-        uncertainties.append(uncertainty_up)
+        return flow, net, motion_hidden_state, flow_out, flow_up[:, :1], uncertainty_up
+
+    flow, net, motion_hidden_state, flow_out, pred, unc_up = step(flow, net, motion_hidden_state)    # iteration 0
+    predictions.append(pred)
+    uncertainties.append(unc_up)
+    done = 1
+    if _use_graph(iters, bt * h * w, inp.device):
+        static_in = [flow.clone(), net.clone(), motion_hidden_state.clone()]
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            outs = step(*static_in)
+        if all(o.shape == i.shape and o.dtype == i.dtype for o, i in zip(outs[:3], static_in)):
+            GRAPH_STATS["captured"] += 1
+            while done < iters:
+                graph.replay()
+                GRAPH_STATS["replayed"] += 1
+                predictions.append(outs[4].clone())
+                uncertainties.append(outs[5].clone())
+                done += 1
+                if done < iters:
+                    for dst, src in zip(static_in, outs[:3]):
+                        dst.copy_(src)
+            flow, net, motion_hidden_state, flow_out = (o.clone() for o in outs[:4])
+        del graph, outs, static_in                        # returns the capture's private pool
+    while done < iters:
+        flow, net, motion_hidden_state, flow_out, pred, unc_up = step(flow, net, motion_hidden_state)
+        GRAPH_STATS["eager"] += 1
+        predictions.append(pred)
+        uncertainties.append(unc_up)
+        done += 1
     return flow_out, net, motion_hidden_state
 
 
@@ -85,9 +135,14 @@ def _update_classes(ppmstereo_module):
     return [(c, f) for c, f in pairs if c is not None]
 
 
-def install(ppmstereo_module, gru: bool = True):
+def install(ppmstereo_module, gru: bool = True, graph: str = "never"):
     """Patch the reference module in place; returns it.  Idempotent; ``uninstall`` restores the originals.
-    ``gru=False`` leaves SKSepConvGRU3D and FlowHead3D on the reference's cuDNN path (SURVEY 8a rows only)."""
+    ``gru=False`` leaves SKSepConvGRU3D and FlowHead3D on the reference's cuDNN path (SURVEY 8a rows only).
+    ``graph``: "never" (default: eager iterations, measured faster -- see GRAPH above); "always" replays the update
+    iteration of every level from a CUDA graph, "auto" only on levels of <= GRAPH_MAX_POSITIONS pixels x frames."""
+    if graph not in ("auto", "always", "never"):
+        raise ValueError("graph must be 'auto', 'always' or 'never'")
+    GRAPH["mode"] = graph
     for cls, fwd in _update_classes(ppmstereo_module):                      # K5 / K5b (ppmtereo_update.py:291-312, :677)
         if gru and not hasattr(cls, "_ppm_reference_forward"):
             cls._ppm_reference_forward = cls.forward

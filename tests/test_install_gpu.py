@@ -116,7 +116,7 @@ def test_installed_model_matches_reference_disparity(env, T, H, W, iters):
     finally:
         ppm.flash_attn_func = real_fa
     floor = float((d_flip - d_ref).abs().mean())
-    P.install(ppm)
+    P.install(ppm, graph="never")                 # eager iterations: the Python-level pick hook below must see every one
     got_masks = []
     orig_pick = P.PPMMemory.pick
 
@@ -187,6 +187,34 @@ def test_forward_batch_test_window_scheduler_vs_reference_loop(env):
     print(f"forward_batch_test 13 frames: mean |d disparity| {mad:.5f} px, uncertainty MAD {umad:.2e}")
     assert mad <= 0.015                     # (three windows' worth of the rounding noise quantified in the test above)
     assert umad <= 1e-3
+
+
+@pytest.mark.parametrize("T,H,W,iters", [(6, 64, 256, 6), (5, 320, 512, 10)])
+def test_graph_replayed_iterations_equal_eager(env, T, H, W, iters):
+    """install(graph="always"): iteration 0 eager, one iteration captured per level, the rest replayed from the CUDA
+    graph.  Our kernels are the same launches on the same data; cuDNN may choose another convolution algorithm under
+    capture, so the results equal the eager loop's to rounding (well inside the 0.01 px bar), replay-to-replay exactly."""
+    import importlib
+    inst = importlib.import_module("ppmstereo_b200.install")
+    P, model, ppm = env
+    video = clip(T, H, W, 17)
+    try:
+        P.install(ppm, graph="never")
+        d0, u0 = run_forward(model, video, iters)
+        before = dict(inst.GRAPH_STATS)
+        P.install(ppm, graph="always")
+        d1, u1 = run_forward(model, video, iters)
+        after = dict(inst.GRAPH_STATS)
+        d2, u2 = run_forward(model, video, iters)           # fresh captures, same answer
+    finally:
+        P.uninstall(ppm)
+    assert inst.GRAPH["mode"] == "always"
+    assert after["captured"] - before["captured"] == 3                      # one capture per cascade level
+    assert after["replayed"] - before["replayed"] == 2 * (iters // 2 - 1) + (iters - 1)
+    mad = float((d1 - d0).abs().mean())
+    print(f"graph vs eager T={T} {H}x{W}: mean |d disparity| {mad:.2e} px, identical: {bool(torch.equal(d0, d1))}")
+    assert mad <= 5e-3 and float((u1 - u0).abs().mean()) <= 1e-3
+    assert torch.equal(d1, d2) and torch.equal(u1, u2)
 
 
 def test_installed_model_refuses_autograd(env):
