@@ -153,3 +153,54 @@ def test_flow_head_vs_cpu_oracle_and_state_reuse(env, flow_head):
     d = (a.float().cpu() - want).abs()
     assert float(d.max()) <= 2.0 ** -6 * max(float(want.abs().max()), 1.0)
     assert float(d.mean()) <= 2e-4
+
+
+@pytest.mark.parametrize("shape", [(1, 3, 6, 9), (2, 2, 5, 17), (1, 4, 7, 70)])
+def test_no_write_outside_output_and_workspace(env, flow_head, shape):
+    """Guard bands instead of compute-sanitizer (closed on this pool): K5 / K5b called through the C ABI with the output
+    and the workspace placed INSIDE larger sentinel-filled buffers, at shapes with partial tiles in x and y (masked
+    epilogue stores, TMA boxes hanging over the tensor edge).  Nothing outside the declared regions may change, every
+    output element must be written."""
+    import ctypes
+    from ppmstereo_b200 import _lib
+    P, gru = env
+    lib = _lib.load()
+    b, T, H, W = shape
+    h, x = make(b, T, H, W, seed=19, hdtype=torch.float32)
+    k = P.SepConvGRU3D(gru)
+    want = k(h, x)                                             # also packs the weights
+    wptr, bptr = k._params()
+    n = ctypes.c_size_t()
+    _lib.check(lib.ppm_sepconv_gru3d_workspace(b, T, H, W, ctypes.byref(n)), "ws")
+    guard = 4096
+    ws = torch.full((n.value + 2 * guard,), 0x5A, dtype=torch.uint8, device="cuda")
+    n_out = b * 128 * T * H * W
+    outbuf = torch.full((n_out + 2 * 1024,), float("nan"), device="cuda")
+    base = (ws.data_ptr() + guard + 255) // 256 * 256
+    lo = base - ws.data_ptr()
+    out_ptr = outbuf.data_ptr() + 1024 * 4
+    _lib.check(lib.ppm_sepconv_gru3d(h.data_ptr(), _lib.dtype_code(h), h.stride(0), h.stride(1), h.stride(2), x.data_ptr(),
+                                     _lib.dtype_code(x), x.stride(0), x.stride(1), x.stride(2), wptr, bptr, b, T, H, W,
+                                     base, n.value, out_ptr, _lib.PPM_F32, _lib.stream_ptr()), "ppm_sepconv_gru3d")
+    torch.cuda.synchronize()
+    assert bool((ws[:lo] == 0x5A).all()) and bool((ws[lo + n.value:] == 0x5A).all())
+    assert bool(torch.isnan(outbuf[:1024]).all()) and bool(torch.isnan(outbuf[1024 + n_out:]).all())
+    got = outbuf[1024:1024 + n_out].view(b, 128, T, H, W)
+    assert bool(torch.isfinite(got).all()) and torch.equal(got, want)
+    # flow head, same scheme
+    head = P.FlowHead3D(flow_head)
+    want_f = head(want.clone())
+    _lib.check(lib.ppm_flow_head3d_workspace(b, T, H, W, ctypes.byref(n)), "ws")
+    ws = torch.full((n.value + 2 * guard,), 0x5A, dtype=torch.uint8, device="cuda")
+    base = (ws.data_ptr() + guard + 255) // 256 * 256
+    lo = base - ws.data_ptr()
+    n_out = b * 2 * T * H * W
+    outbuf = torch.full((n_out + 2 * 1024,), -7.0, dtype=torch.bfloat16, device="cuda")
+    _lib.check(lib.ppm_flow_head3d(want.data_ptr(), _lib.dtype_code(want), want.stride(0), want.stride(1), want.stride(2),
+                                   None, head.w1.data_ptr(), head.b1.data_ptr(), head.w2.data_ptr(), head.b2.data_ptr(),
+                                   b, T, H, W, base, n.value, outbuf.data_ptr() + 1024 * 2, _lib.PPM_BF16,
+                                   _lib.stream_ptr()), "ppm_flow_head3d")
+    torch.cuda.synchronize()
+    assert bool((ws[:lo] == 0x5A).all()) and bool((ws[lo + n.value:] == 0x5A).all())
+    assert bool((outbuf[:1024] == -7.0).all()) and bool((outbuf[1024 + n_out:] == -7.0).all())
+    assert torch.equal(outbuf[1024:1024 + n_out].view(b, 2, T, H, W), want_f)
