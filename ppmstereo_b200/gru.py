@@ -114,19 +114,19 @@ _LAST_STATE = {}          # set by SepConvGRU3D.__call__: the result tensor and 
 
 
 def _remember_state(out: torch.Tensor, ws: torch.Tensor, lib) -> None:
+    import weakref
     b, _, T, H, W = out.shape
     off = ctypes.c_size_t()
     _lib.check(lib.ppm_sepconv_gru3d_state_offset(b, T, H, W, ctypes.byref(off)), "ppm_sepconv_gru3d_state_offset")
-    _LAST_STATE.update(ptr=out.data_ptr(), version=out._version, shape=tuple(out.shape), device=out.device,
-                       cl_ptr=ws.data_ptr() + off.value, ws=ws, stream=_lib.stream_ptr())
+    _LAST_STATE.update(ref=weakref.ref(out), version=out._version, cl_ptr=ws.data_ptr() + off.value, ws=ws,
+                       stream=_lib.stream_ptr())
 
 
 def _state_channels_last(x: torch.Tensor) -> int:
-    """Device address of the bf16 channels-last copy of ``x`` when ``x`` IS the tensor K5 just returned (same storage,
-    unmodified, same stream), else 0."""
+    """Device address of the bf16 channels-last copy of ``x`` when ``x`` IS the tensor object K5 just returned
+    (identity, not address: a later tensor may reuse the address), unmodified since, on the same stream; else 0."""
     s = _LAST_STATE
-    if (s and s["ptr"] == x.data_ptr() and s["version"] == x._version and s["shape"] == tuple(x.shape)
-            and s["device"] == x.device and x.is_contiguous() and s["stream"] == _lib.stream_ptr()):
+    if s and s["ref"]() is x and s["version"] == x._version and s["stream"] == _lib.stream_ptr():
         return s["cl_ptr"]
     return 0
 
