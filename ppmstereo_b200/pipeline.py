@@ -26,15 +26,16 @@ class StagedRunner:
         self.depth = max(1, int(depth))
         self.h2d = torch.cuda.Stream(self.device)
         self.d2h = torch.cuda.Stream(self.device)
-        self._host_out: Dict[Tuple, List[torch.Tensor]] = {}
+        self._host_out: Dict[Tuple, torch.Tensor] = {}
 
-    # -- pinned result buffers per distinct (result index, shape, dtype): `slots` of them, reused across run() calls
-    def _out_buffer(self, t: torch.Tensor, slot: int, slots: int, idx: int) -> torch.Tensor:
-        key = (idx, tuple(t.shape), t.dtype)
-        pool = self._host_out.setdefault(key, [])
-        while len(pool) < slots:
-            pool.append(torch.empty(t.shape, dtype=t.dtype, pin_memory=True))
-        return pool[slot]
+    # -- pinned result buffers, one per (result index, shape, dtype, slot), allocated when a slot is first used and
+    #    reused by later run() calls
+    def _out_buffer(self, t: torch.Tensor, slot: int, idx: int) -> torch.Tensor:
+        key = (idx, tuple(t.shape), t.dtype, slot)
+        buf = self._host_out.get(key)
+        if buf is None:
+            buf = self._host_out[key] = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+        return buf
 
     def _upload(self, job: Dict[str, torch.Tensor], after=None):
         with torch.cuda.stream(self.h2d):
@@ -92,7 +93,7 @@ class StagedRunner:
                 host = []
                 for n, t in enumerate(outs):
                     t.record_stream(self.d2h)
-                    hb = self._out_buffer(t, i % slots, slots, n)
+                    hb = self._out_buffer(t, i % slots, n)
                     hb.copy_(t, non_blocking=True)
                     host.append(hb)
                 ev = torch.cuda.Event()

@@ -62,3 +62,24 @@ def test_staged_cached_windows_equal_the_synchronous_path(T, ks, hw):
         assert got[k].shape == want[k].shape == (T, 1, *hw)
         assert not got[k].is_cuda
         assert float((got[k] - want[k]).abs().max()) <= 1e-4 * float(want[k].abs().max())
+
+
+@pytest.mark.gpu
+def test_staged_runner_results_do_not_alias():
+    """More jobs than the ring depth, all of one shape: every returned result must be its own job's (the advisor's
+    round-1 finding: results[i] and results[i + depth] were the same pinned tensor); the callback form streams the
+    same values through `depth` buffers and hands each one over before it is reused."""
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import ppmstereo_b200 as P
+    runner = P.StagedRunner(depth=2)
+    jobs = [{"x": torch.full((64, 1024), float(i)).pin_memory()} for i in range(7)]
+    fn = lambda dev, i: (dev["x"] * 2 + 1, dev["x"].sum(dim=1))
+    res = runner.run(jobs, fn)
+    assert len(res) == 7
+    for i, (a, b) in enumerate(res):
+        assert a.is_pinned() and float(a[0, 0]) == 2 * i + 1 and float(b[0]) == 1024 * i
+    assert len({a.data_ptr() for a, _ in res}) == 7
+    seen = []
+    out = runner.run(jobs, fn, on_result=lambda i, host: seen.append((i, float(host[0][0, 0]), float(host[1][3]))))
+    assert out == [] and seen == [(i, 2.0 * i + 1, 1024.0 * i) for i in range(7)]
