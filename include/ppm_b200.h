@@ -172,6 +172,25 @@ PPM_API int ppm_convex_upsample(const float* flow, const void* mask, int mask_dt
                         int rate, float* out, void* stream);
 
 /* ---------------------------------------------------------------------------------------
+ * K6  lookup fused into the motion encoder's front end.
+ * Replaces `cor = F.gelu(self.convc1(corr))` of BasicMotionEncoder_v2.forward (models/core/ppmtereo_update.py:466),
+ * convc1 = PCBlock4_Deep_nopool_res(36, 256, k_conv=[1, 7]) (:91-116), together with the CorrBlock1D.__call__ that
+ * produced `corr` (models/core/corr.py:74-94), in the bf16 autocast regime: the (B,36,H,W1) fp32 lookup result is
+ * never written.  Rounding: 1x1 conv = bf16(bf16(acc) + bias), depthwise conv = bf16(acc + bias), GELU of a bf16
+ * tensor = bf16, residual stream fp32 (torch / cuDNN's flow, identified on the B200).
+ * level0 / flow / W2: as ppm_corr_lookup_l0 -- or corr != NULL: start from a materialised (B,36,H,W1) fp32 lookup.
+ * weights_a: PPM_MF_A_FLOATS fp32 (bf16-representable values): ffn1.0 W[54][36], b[54] (+2 pad), ffn1.2 W[36][56]
+ *   (rows padded from 54), b[36], conv_list.0 w[36], b[36].
+ * weights_b: PPM_MF_B_FLOATS fp32: conv_list.1 w[36][49], b[36], pw W[36][36], b[36], ffn2.0 W[54][36], b[54] (+2 pad),
+ *   ffn2.2 W TRANSPOSED [54][256], b[256].
+ * x2_ws: B*36*H*W1 floats of scratch.  cor: (B,256,H,W1) bf16 = gelu(convc1(corr)). */
+#define PPM_MF_A_FLOATS 4124
+#define PPM_MF_B_FLOATS 19212
+PPM_API int ppm_motion_corr_front(const void* level0, const float* flow, const float* corr, const float* weights_a,
+                          const float* weights_b, int B, int H, int W1, int W2, float* x2_ws, void* cor,
+                          void* stream);
+
+/* ---------------------------------------------------------------------------------------
  * K5  SKSepConvGRU3D (models/core/ppmtereo_update.py:254-312, called from
  * SequenceUpdateBlock3D.forward :971-1003), in the reference's bf16 autocast regime:
  *   per stage s = 1 (along W), 2 (along H), 3 (along T):

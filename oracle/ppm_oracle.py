@@ -431,3 +431,50 @@ def flow_head3d(x: torch.Tensor, params: dict, mode: str = "fp32") -> torch.Tens
     rnd = bf16_round if mode == "bf16" else (lambda t: t)
     y = torch.relu(conv3d_shifted(x, params["conv1.weight"], params["conv1.bias"], rnd))
     return conv3d_shifted(y, params["conv2.weight"], params["conv2.bias"], rnd)
+
+
+# ---------------------------------------------------------------------------------------------
+# BasicMotionEncoder_v2.convc1 = PCBlock4_Deep_nopool_res(36, 256, k_conv=[1, 7]) + the encoder's outer GELU
+# (models/core/ppmtereo_update.py:91-116, :466) -- SURVEY 8f rank 1 (lookup -> convc1 fusion)
+# ---------------------------------------------------------------------------------------------
+def _conv1x1(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor, rnd) -> torch.Tensor:
+    """1x1 Conv2d as a channel contraction.  bf16 mode: bf16(bf16(acc) + bf16 bias) -- what cuDNN + torch produce
+    (identified on the B200, scripts/exp/pcblock_rounding_probe.py: 99.999 %)."""
+    w = rnd(weight.float()).reshape(weight.shape[0], weight.shape[1])
+    acc = torch.einsum("oc,bchw->bohw", w, rnd(x.float()))
+    return rnd(rnd(acc) + rnd(bias.float()).view(1, -1, 1, 1))
+
+
+def _depthwise(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor, rnd) -> torch.Tensor:
+    """Depthwise k x k Conv2d (groups = C, zero padding k//2) as a sum of shifted per-channel products.  bf16 mode:
+    ONE rounding, bf16(acc + bf16 bias) (cuDNN's depthwise path fuses the bias; probe: 99.995-100 %)."""
+    C, _, k, _ = weight.shape
+    w = rnd(weight.float())
+    xin = torch.nn.functional.pad(rnd(x.float()), (k // 2,) * 4)
+    H, W = x.shape[-2:]
+    acc = torch.zeros_like(x, dtype=torch.float32)
+    for ky in range(k):
+        for kx in range(k):
+            acc += w[:, 0, ky, kx].view(1, C, 1, 1) * xin[:, :, ky:ky + H, kx:kx + W]
+    return rnd(acc + rnd(bias.float()).view(1, -1, 1, 1))
+
+
+def motion_corr_front(corr: torch.Tensor, params: dict, mode: str = "fp32") -> torch.Tensor:
+    """gelu(PCBlock4_Deep_nopool_res(corr)): the ``cor = F.gelu(self.convc1(corr))`` line of
+    BasicMotionEncoder_v2.forward (ppmtereo_update.py:466) with the block's forward (:110-116) written out.
+    corr (B, 36, h, w) fp32 (the lookup's output); params: the block's state dict ('ffn1.0.weight', 'conv_list.1.bias',
+    'pw.weight', 'ffn2.2.weight', ...).  mode "bf16" = the autocast regime: every conv output is a bf16 tensor (rounding
+    rules above), the residual stream ``x + branch`` and its GELUs stay fp32 (fp32 + bf16 promotes to fp32), GELU of a
+    bf16 tensor is bf16."""
+    rnd = bf16_round if mode == "bf16" else (lambda t: t)
+    gelu = torch.nn.functional.gelu
+    p = params
+    x = corr.float()
+    t = _conv1x1(rnd(gelu(_conv1x1(x, p["ffn1.0.weight"], p["ffn1.0.bias"], rnd))), p["ffn1.2.weight"], p["ffn1.2.bias"], rnd)
+    x = gelu(x + t)
+    for i in range(2):                                           # conv_list: depthwise k = 1, then k = 7
+        x = gelu(x + _depthwise(x, p[f"conv_list.{i}.weight"], p[f"conv_list.{i}.bias"], rnd))
+    x = gelu(x + _conv1x1(x, p["pw.weight"], p["pw.bias"], rnd))
+    u = rnd(gelu(_conv1x1(x, p["ffn2.0.weight"], p["ffn2.0.bias"], rnd)))
+    out = _conv1x1(u, p["ffn2.2.weight"], p["ffn2.2.bias"], rnd)
+    return rnd(gelu(out))

@@ -49,6 +49,8 @@ SIGNATURES = {
     "ppm_flow_head3d_workspace": (c_int, [c_int, c_int, c_int, c_int, POINTER(c_size_t)]),
     "ppm_flow_head3d": (c_int, [c_void_p, c_int, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                 c_int, c_int, c_int, c_int, c_void_p, c_size_t, c_void_p, c_int, c_void_p]),
+    "ppm_motion_corr_front": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int,
+                                      c_void_p, c_void_p, c_void_p]),
     "ppm_pack_bytes": (c_int, [c_int, c_int, c_int, c_int, POINTER(c_size_t), POINTER(c_size_t),
                                POINTER(c_size_t)]),
 }

@@ -18,6 +18,8 @@
 // them the interpolation weights -- are bit-identical to the reference's, tap by tap.  (Round 1 used the closed form
 // out_k = (1-a) V[f+k] + a V[f+k+1]; the reference's normalise / un-normalise round trip moves each tap's position
 // by up to an ulp of x, 2e-5 of |out|, and the recurrent update amplifies that to ~0.01 px of final disparity.)
+#include <atomic>
+
 #include "../../include/ppm_b200.h"
 #include "common.cuh"
 
@@ -245,20 +247,19 @@ struct LookupL0Params {
   int HW, W1, W2;
 };
 
-__global__ void __launch_bounds__(kLookupThreads)
-corr_lookup_l0_kernel(const LookupL0Params p) {
-  const int b = blockIdx.y;
-  const int q = blockIdx.x * kLookupThreads + threadIdx.x;
-  if (q >= p.HW) return;
+// The 36 outputs of pixel (b, q), delivered level by level to `sink.put(level, o[9])` (K2b stores them, the fused
+// motion-encoder front end K6a keeps them in registers).
+template <typename Sink>
+__device__ __forceinline__ void lookup_l0_pixel(const LookupL0Params& p, int b, int q, Sink& sink) {
   const float x = __fadd_rn(static_cast<float>(q % p.W1), __ldg(p.flow + static_cast<long long>(b) * 2 * p.HW + q));
   float fl = fminf(fmaxf(floorf(x), -1048576.f), 1048576.f);
   fl = (fl == fl) ? fl : 0.f;
   const int f = static_cast<int>(fl);
   const int s0 = 8 * ((f >> 3) - 4);                      // in-row level-0 index of span element 0
-  float* dst = p.out + static_cast<long long>(b) * 36 * p.HW + q;
   if (s0 >= p.W2 || s0 + 80 <= 0) {                      // every tap of every level is outside the row
+    const float zero[kMaxTaps] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     #pragma unroll
-    for (int c = 0; c < 36; ++c) dst[static_cast<long long>(c) * p.HW] = 0.f;
+    for (int l = 0; l < kMaxLevels; ++l) sink.put(l, zero);
     return;
   }
   const long long g0 = (static_cast<long long>(b) * p.HW + q) * p.W2 + s0;      // multiple of 8
@@ -331,15 +332,233 @@ corr_lookup_l0_kernel(const LookupL0Params p) {
     }
     const float cl = x * (1.f / static_cast<float>(1 << l));
     const float wm1 = static_cast<float>(Wl - 1), inv = __frcp_rn(wm1);
-    float* d = dst + static_cast<long long>(l) * 9 * p.HW;
     float o[kMaxTaps];
     o[0] = lk_sample<0>(v[l], first, cl, 4, inv, wm1); o[1] = lk_sample<1>(v[l], first, cl, 4, inv, wm1);
     o[2] = lk_sample<2>(v[l], first, cl, 4, inv, wm1); o[3] = lk_sample<3>(v[l], first, cl, 4, inv, wm1);
     o[4] = lk_sample<4>(v[l], first, cl, 4, inv, wm1); o[5] = lk_sample<5>(v[l], first, cl, 4, inv, wm1);
     o[6] = lk_sample<6>(v[l], first, cl, 4, inv, wm1); o[7] = lk_sample<7>(v[l], first, cl, 4, inv, wm1);
     o[8] = lk_sample<8>(v[l], first, cl, 4, inv, wm1);
+    sink.put(l, o);
+  }
+}
+
+struct LookupStoreSink {
+  float* dst;
+  long long HW;
+  __device__ __forceinline__ void put(int l, const float (&o)[kMaxTaps]) {
+    float* d = dst + static_cast<long long>(l) * 9 * HW;
     #pragma unroll
-    for (int k = 0; k < kMaxTaps; ++k) d[static_cast<long long>(k) * p.HW] = o[k];
+    for (int k = 0; k < kMaxTaps; ++k) d[static_cast<long long>(k) * HW] = o[k];
+  }
+};
+
+__global__ void __launch_bounds__(kLookupThreads)
+corr_lookup_l0_kernel(const LookupL0Params p) {
+  const int b = blockIdx.y;
+  const int q = blockIdx.x * kLookupThreads + threadIdx.x;
+  if (q >= p.HW) return;
+  LookupStoreSink sink{p.out + static_cast<long long>(b) * 36 * p.HW + q, p.HW};
+  lookup_l0_pixel(p, b, q, sink);
+}
+
+
+
+// ================================================================================================================
+// K6: lookup fused into the motion encoder's front end.
+// Replaces `cor = F.gelu(self.convc1(corr))` of BasicMotionEncoder_v2.forward (reference
+// models/core/ppmtereo_update.py:466) with convc1 = PCBlock4_Deep_nopool_res(36, 256, k_conv=[1, 7]) (:91-116), and the
+// lookup that produced `corr` (corr.py:74-94): the (B, 36, h, w) fp32 lookup result never reaches HBM.
+//   K6a (this kernel), per pixel:  x = lookup;  x = gelu(x + ffn1(x));  x = gelu(x + dw1(x))           -> x2 (B,36,h,w) fp32
+//   K6b, 32 x 16 pixel tiles:      x = gelu(x + dw7(x));  x = gelu(x + pw(x));  cor = gelu(ffn2(x))    -> (B,256,h,w) bf16
+// Rounding flow = torch / cuDNN under bf16 autocast, identified on the box (scripts/exp/pcblock_rounding_probe.py):
+// a 1x1 conv is bf16(bf16(acc) + bias) (99.999 % reproduced), a depthwise conv bf16(acc + bias) (99.995-100 %), GELU of a
+// bf16 tensor is bf16, and the residual stream x + branch with its GELUs stays fp32 (fp32 + bf16 promotes to fp32).
+// Weights arrive as one fp32 array of bf16-representable values (layout: MfA / MfB offsets below).
+namespace mf {
+constexpr int kC = 36, kHid = 54, kOut = 256;
+// K6a block
+constexpr int kWa = 0;                      // ffn1.0 weight [54][36]
+constexpr int kBa = kWa + kHid * kC;        // ffn1.0 bias [54] (+2 pad)
+constexpr int kWb = kBa + 56;               // ffn1.2 weight [36][56] (rows padded from 54)
+constexpr int kBb = kWb + kC * 56;          // ffn1.2 bias [36]
+constexpr int kW1 = kBb + kC;               // conv_list.0 (depthwise k = 1) weight [36]
+constexpr int kB1 = kW1 + kC;               // conv_list.0 bias [36]
+constexpr int kASize = kB1 + kC;            // 4124 floats
+// K6b block
+constexpr int kW7 = 0;                      // conv_list.1 (depthwise 7x7) weight [36][49]
+constexpr int kB7 = kW7 + kC * 49;          // bias [36]
+constexpr int kWp = kB7 + kC;               // pw weight [36][36]
+constexpr int kBp = kWp + kC * kC;          // pw bias [36]
+constexpr int kWc = kBp + kC;               // ffn2.0 weight [54][36]
+constexpr int kBc = kWc + kHid * kC;        // ffn2.0 bias [54] (+2 pad)
+constexpr int kWd = kBc + 56;               // ffn2.2 weight TRANSPOSED [54][256]
+constexpr int kBd = kWd + kHid * kOut;      // ffn2.2 bias [256]
+constexpr int kBSize = kBd + kOut;          // 19212 floats
+}  // namespace mf
+
+__device__ __forceinline__ float mf_gelu(float x) { return 0.5f * x * (1.f + erff(x * 0.70710678118654752440f)); }
+__device__ __forceinline__ float mf_r(float x) { return bf16_round_f(x); }
+
+struct LookupRegSink {
+  float* x;                                                // 36 registers
+  __device__ __forceinline__ void put(int l, const float (&o)[kMaxTaps]) {
+    #pragma unroll
+    for (int k = 0; k < kMaxTaps; ++k) x[l * kMaxTaps + k] = o[k];
+  }
+};
+
+struct MotionFrontAParams {
+  LookupL0Params lk;               // fused lookup (lk.out unused), or
+  const float* corr_in;            // a materialised (B, 36, h, w) fp32 lookup result (foreign pyramids); nullptr = fused
+  const float* wts;                // mf::kASize floats
+  float* x2;                       // (B, 36, h, w) fp32
+};
+
+__global__ void __launch_bounds__(kLookupThreads)
+motion_front_a_kernel(const MotionFrontAParams p) {
+  __shared__ __align__(16) float sw[mf::kASize];
+  for (int i = threadIdx.x; i < mf::kASize; i += kLookupThreads) sw[i] = __ldg(p.wts + i);
+  __syncthreads();
+  const int b = blockIdx.y, HW = p.lk.HW;
+  const int q = blockIdx.x * kLookupThreads + threadIdx.x;
+  if (q >= HW) return;
+  float x[mf::kC];
+  if (p.corr_in) {
+    #pragma unroll
+    for (int c = 0; c < mf::kC; ++c) x[c] = __ldg(p.corr_in + (static_cast<long long>(b) * mf::kC + c) * HW + q);
+  } else {
+    LookupRegSink sink{x};
+    lookup_l0_pixel(p.lk, b, q, sink);
+  }
+  float xr[mf::kC];
+  #pragma unroll
+  for (int c = 0; c < mf::kC; ++c) xr[c] = mf_r(x[c]);                   // the conv's autocast cast of its input
+  // ffn1: 36 -> 54 -> GELU -> 36
+  float hid[mf::kHid];
+  #pragma unroll
+  for (int o = 0; o < mf::kHid; ++o) {
+    const float4* w = reinterpret_cast<const float4*>(sw + mf::kWa + o * mf::kC);
+    float acc = 0.f;
+    #pragma unroll
+    for (int c4 = 0; c4 < mf::kC / 4; ++c4) {
+      const float4 w4 = w[c4];
+      acc = fmaf(w4.x, xr[4 * c4], acc); acc = fmaf(w4.y, xr[4 * c4 + 1], acc);
+      acc = fmaf(w4.z, xr[4 * c4 + 2], acc); acc = fmaf(w4.w, xr[4 * c4 + 3], acc);
+    }
+    hid[o] = mf_r(mf_gelu(mf_r(mf_r(acc) + sw[mf::kBa + o])));
+  }
+  float* dst = p.x2 + static_cast<long long>(b) * mf::kC * HW + q;
+  #pragma unroll
+  for (int o = 0; o < mf::kC; ++o) {
+    const float2* w = reinterpret_cast<const float2*>(sw + mf::kWb + o * 56);
+    float acc = 0.f;
+    #pragma unroll
+    for (int c2 = 0; c2 < mf::kHid / 2; ++c2) {
+      const float2 w2 = w[c2];
+      acc = fmaf(w2.x, hid[2 * c2], acc); acc = fmaf(w2.y, hid[2 * c2 + 1], acc);
+    }
+    const float x1 = mf_gelu(x[o] + mf_r(mf_r(acc) + sw[mf::kBb + o]));          // fp32 residual stream
+    const float d1 = mf_r(fmaf(sw[mf::kW1 + o], mf_r(x1), sw[mf::kB1 + o]));     // depthwise k = 1: bf16(w * x + b)
+    dst[static_cast<long long>(o) * HW] = mf_gelu(x1 + d1);
+  }
+}
+
+// K6b: CTA = 32 x 16 pixels of one frame, thread = pixel.  The bf16 copy of x2 the depthwise conv reads (its autocast
+// cast) is staged with a 3-pixel halo in shared memory, zero outside the image (the conv's zero padding); all weights of
+// the tail sit in shared memory as fp32 (77 KB) and are read as warp-wide broadcasts.
+constexpr int kMfTileW = 32, kMfTileH = 16, kMfHalo = 3;
+constexpr int kMfTW = kMfTileW + 2 * kMfHalo + 2;            // 40: row pitch of the tile (38 used)
+constexpr int kMfTH = kMfTileH + 2 * kMfHalo;                // 22
+constexpr int kMfBThreads = kMfTileW * kMfTileH;             // 512
+constexpr int kMfBSmem = mf::kBSize * 4 + mf::kC * kMfTH * kMfTW * 2;
+
+__global__ void __launch_bounds__(kMfBThreads, 1)
+motion_front_b_kernel(const float* __restrict__ x2, const float* __restrict__ wts, __nv_bfloat16* __restrict__ cor,
+                      int H, int W) {
+  extern __shared__ __align__(16) uint8_t mf_smem[];
+  float* sw = reinterpret_cast<float*>(mf_smem);
+  __nv_bfloat16* tile = reinterpret_cast<__nv_bfloat16*>(mf_smem + mf::kBSize * 4);
+  const int HW = H * W;
+  const int x0 = blockIdx.x * kMfTileW, y0 = blockIdx.y * kMfTileH, frame = blockIdx.z;
+  const float* src = x2 + static_cast<long long>(frame) * mf::kC * HW;
+  for (int i = threadIdx.x; i < mf::kBSize; i += kMfBThreads) sw[i] = __ldg(wts + i);
+  for (int i = threadIdx.x; i < mf::kC * kMfTH * kMfTW; i += kMfBThreads) {
+    const int tx = i % kMfTW, ty = (i / kMfTW) % kMfTH, c = i / (kMfTW * kMfTH);
+    const int gx = x0 + tx - kMfHalo, gy = y0 + ty - kMfHalo;
+    float v = 0.f;
+    if (tx < kMfTileW + 2 * kMfHalo && gx >= 0 && gx < W && gy >= 0 && gy < H) v = __ldg(src + static_cast<long long>(c) * HW + gy * W + gx);
+    tile[i] = __float2bfloat16_rn(v);
+  }
+  __syncthreads();
+  const int tx = threadIdx.x & (kMfTileW - 1), ty = threadIdx.x / kMfTileW;
+  const int gx = x0 + tx, gy = y0 + ty;
+  if (gx >= W || gy >= H) return;
+  const long long pix = static_cast<long long>(gy) * W + gx;
+  // ---- x3 = gelu(x2 + dw7(x2))
+  float x3[mf::kC];
+  #pragma unroll
+  for (int c = 0; c < mf::kC; ++c) {
+    const __nv_bfloat16* t = tile + (c * kMfTH + ty) * kMfTW + tx;
+    const float* w = sw + mf::kW7 + c * 49;
+    float acc = 0.f;
+    #pragma unroll
+    for (int ky = 0; ky < 7; ++ky)
+      #pragma unroll
+      for (int kx = 0; kx < 7; ++kx) acc = fmaf(w[ky * 7 + kx], __bfloat162float(t[ky * kMfTW + kx]), acc);
+    const float d7 = mf_r(acc + sw[mf::kB7 + c]);                          // depthwise: bf16(acc + b)
+    x3[c] = mf_gelu(__ldg(src + static_cast<long long>(c) * HW + pix) + d7);
+  }
+  // ---- x4 = gelu(x3 + pw(x3))
+  float xr[mf::kC], x4r[mf::kC];
+  #pragma unroll
+  for (int c = 0; c < mf::kC; ++c) xr[c] = mf_r(x3[c]);
+  #pragma unroll
+  for (int o = 0; o < mf::kC; ++o) {
+    const float4* w = reinterpret_cast<const float4*>(sw + mf::kWp + o * mf::kC);
+    float acc = 0.f;
+    #pragma unroll
+    for (int c4 = 0; c4 < mf::kC / 4; ++c4) {
+      const float4 w4 = w[c4];
+      acc = fmaf(w4.x, xr[4 * c4], acc); acc = fmaf(w4.y, xr[4 * c4 + 1], acc);
+      acc = fmaf(w4.z, xr[4 * c4 + 2], acc); acc = fmaf(w4.w, xr[4 * c4 + 3], acc);
+    }
+    x4r[o] = mf_r(mf_gelu(x3[o] + mf_r(mf_r(acc) + sw[mf::kBp + o])));    // bf16(x4): ffn2.0's input cast
+  }
+  // ---- u = bf16(gelu(ffn2.0(x4)))
+  float u[mf::kHid];
+  #pragma unroll
+  for (int o = 0; o < mf::kHid; ++o) {
+    const float4* w = reinterpret_cast<const float4*>(sw + mf::kWc + o * mf::kC);
+    float acc = 0.f;
+    #pragma unroll
+    for (int c4 = 0; c4 < mf::kC / 4; ++c4) {
+      const float4 w4 = w[c4];
+      acc = fmaf(w4.x, x4r[4 * c4], acc); acc = fmaf(w4.y, x4r[4 * c4 + 1], acc);
+      acc = fmaf(w4.z, x4r[4 * c4 + 2], acc); acc = fmaf(w4.w, x4r[4 * c4 + 3], acc);
+    }
+    u[o] = mf_r(mf_gelu(mf_r(mf_r(acc) + sw[mf::kBc + o])));
+  }
+  // ---- cor = bf16(gelu(ffn2.2(u))), 16 output channels at a time (weights transposed: [c][o])
+  __nv_bfloat16* dst = cor + static_cast<long long>(frame) * mf::kOut * HW + pix;
+  for (int o0 = 0; o0 < mf::kOut; o0 += 16) {
+    float acc[16];
+    #pragma unroll
+    for (int j = 0; j < 16; ++j) acc[j] = 0.f;
+    #pragma unroll
+    for (int c = 0; c < mf::kHid; ++c) {
+      const float4* w = reinterpret_cast<const float4*>(sw + mf::kWd + c * mf::kOut + o0);
+      #pragma unroll
+      for (int j4 = 0; j4 < 4; ++j4) {
+        const float4 w4 = w[j4];
+        acc[4 * j4] = fmaf(w4.x, u[c], acc[4 * j4]); acc[4 * j4 + 1] = fmaf(w4.y, u[c], acc[4 * j4 + 1]);
+        acc[4 * j4 + 2] = fmaf(w4.z, u[c], acc[4 * j4 + 2]); acc[4 * j4 + 3] = fmaf(w4.w, u[c], acc[4 * j4 + 3]);
+      }
+    }
+    #pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      const float v = mf_r(mf_r(acc[j]) + sw[mf::kBd + o0 + j]);
+      dst[static_cast<long long>(o0 + j) * HW] = __float2bfloat16_rn(mf_gelu(v));   // the encoder's outer F.gelu
+    }
   }
 }
 
@@ -392,6 +611,44 @@ extern "C" int ppm_corr_lookup_l0(const void* level0, const float* flow, int B, 
   p.flow = flow; p.out = out;
   dim3 grid((p.HW + kLookupThreads - 1) / kLookupThreads, B);
   corr_lookup_l0_kernel<<<grid, kLookupThreads, 0, static_cast<cudaStream_t>(stream)>>>(p);
+  PPM_CUDA(cudaGetLastError());
+  return PPM_OK;
+}
+
+
+// K6 entry: see the section header above.  level0 / flow as ppm_corr_lookup_l0 (fused lookup), or corr != NULL to start
+// from a materialised (B, 36, H, W1) fp32 lookup result.  weights_a / weights_b: fp32 arrays (bf16-representable values)
+// in the MfA / MfB layouts; x2_ws: B*36*H*W1 floats of scratch; cor: (B, 256, H, W1) bf16.
+extern "C" int ppm_motion_corr_front(const void* level0, const float* flow, const float* corr, const float* weights_a,
+                                     const float* weights_b, int B, int H, int W1, int W2, float* x2_ws, void* cor,
+                                     void* stream) {
+  using namespace ppm;
+  PPM_CHECK((corr || (level0 && flow)) && weights_a && weights_b && x2_ws && cor, PPM_ERR_ARG,
+            "ppm_motion_corr_front: null pointer");
+  PPM_CHECK(B > 0 && H > 0 && W1 > 0 && B <= 65535, PPM_ERR_ARG, "ppm_motion_corr_front: bad shape");
+  MotionFrontAParams a{};
+  a.lk.HW = H * W1; a.lk.W1 = W1; a.lk.W2 = W2;
+  if (!corr) {
+    PPM_CHECK(W2 > 0 && W2 % 8 == 0, PPM_ERR_UNSUPPORTED, "ppm_motion_corr_front: W2 = %d must be a multiple of 8", W2);
+    PPM_CHECK((reinterpret_cast<uintptr_t>(level0) & 31) == 0, PPM_ERR_ARG, "ppm_motion_corr_front: level 0 must be 32-byte aligned");
+    a.lk.level0 = static_cast<const __nv_bfloat16*>(level0);
+    a.lk.total = static_cast<long long>(B) * H * W1 * W2;
+    a.lk.flow = flow;
+  }
+  a.corr_in = corr; a.wts = weights_a; a.x2 = x2_ws;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  motion_front_a_kernel<<<dim3((a.lk.HW + kLookupThreads - 1) / kLookupThreads, B), kLookupThreads, 0, st>>>(a);
+  PPM_CUDA(cudaGetLastError());
+  static std::atomic<uint64_t> attr_done{0};
+  int dev = 0;
+  PPM_CUDA(cudaGetDevice(&dev));
+  if (dev >= 64 || !((attr_done.load(std::memory_order_acquire) >> dev) & 1)) {
+    PPM_CUDA(cudaFuncSetAttribute(motion_front_b_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMfBSmem));
+    if (dev < 64) attr_done.fetch_or(1ull << dev, std::memory_order_release);
+  }
+  PPM_CHECK((H + kMfTileH - 1) / kMfTileH <= 65535, PPM_ERR_UNSUPPORTED, "ppm_motion_corr_front: H too large");
+  dim3 grid((W1 + kMfTileW - 1) / kMfTileW, (H + kMfTileH - 1) / kMfTileH, B);
+  motion_front_b_kernel<<<grid, kMfBThreads, kMfBSmem, st>>>(x2_ws, weights_b, static_cast<__nv_bfloat16*>(cor), H, W1);
   PPM_CUDA(cudaGetLastError());
   return PPM_OK;
 }

@@ -18,6 +18,7 @@ import sys
 
 from .corr import CorrBlock1D
 from .gru import flow_head_forward, gru_forward
+from .motion import LookupRequest, encoder_forward
 from .memory import C, PPMMemory, softmax_scale
 from .upsample import convex_upsample
 from .window import forward_batch_test
@@ -72,7 +73,9 @@ def forward_update_block(self, image1, update_block, corr_fn, flow, net, inp, mo
     def step(flow, net, motion_hidden_state):
         """One update iteration (ppmstereo.py:482-591)."""
         flow = flow.detach()
-        out_corrs = corr_fn(flow)
+        # K6: when the encoder's front end is fused, the lookup runs inside it (the (B,36,h,w) tensor is never written)
+        fused = hasattr(type(update_block.encoder), "_ppm_reference_forward") and getattr(corr_fn, "_l0_only", False)
+        out_corrs = LookupRequest(corr_fn, flow) if fused else corr_fn(flow)
         motion_features, motion_hidden_state, value = update_block.get_motion_and_value(
             flow, out_corrs, motion_hidden_state, inp)
         uncertainty_score = update_block.get_uncertainty(torch.cat([net, value], dim=1))
@@ -127,23 +130,25 @@ _ORIGINALS = "_ppmstereo_b200_originals"
 
 
 def _update_classes(ppmstereo_module):
-    """The reference's SKSepConvGRU3D (models/core/ppmtereo_update.py:254) and FlowHead3D (:670) classes with their
-    replacement forwards, found through the module that defines SequenceUpdateBlock3D (imported by name at
+    """The reference's SKSepConvGRU3D (models/core/ppmtereo_update.py:254), FlowHead3D (:670) and BasicMotionEncoder_v2
+    (:445) classes with their replacement forwards, found through the module that defines SequenceUpdateBlock3D (imported by name at
     models/core/ppmstereo.py:17-24)."""
     upd = sys.modules.get(ppmstereo_module.SequenceUpdateBlock3D.__module__)
-    pairs = [(getattr(upd, "SKSepConvGRU3D", None), gru_forward), (getattr(upd, "FlowHead3D", None), flow_head_forward)]
+    pairs = [(getattr(upd, "SKSepConvGRU3D", None), gru_forward), (getattr(upd, "FlowHead3D", None), flow_head_forward),
+             (getattr(upd, "BasicMotionEncoder_v2", None), encoder_forward)]
     return [(c, f) for c, f in pairs if c is not None]
 
 
 def install(ppmstereo_module, gru: bool = True, graph: str = "never"):
     """Patch the reference module in place; returns it.  Idempotent; ``uninstall`` restores the originals.
-    ``gru=False`` leaves SKSepConvGRU3D and FlowHead3D on the reference's cuDNN path (SURVEY 8a rows only).
+    ``gru=False`` leaves the SURVEY 8f kernels off: SKSepConvGRU3D, FlowHead3D and the motion encoder's front end stay
+    on the reference's cuDNN path (SURVEY 8a rows only).
     ``graph``: "never" (default: eager iterations, measured faster -- see GRAPH above); "always" replays the update
     iteration of every level from a CUDA graph, "auto" only on levels of <= GRAPH_MAX_POSITIONS pixels x frames."""
     if graph not in ("auto", "always", "never"):
         raise ValueError("graph must be 'auto', 'always' or 'never'")
     GRAPH["mode"] = graph
-    for cls, fwd in _update_classes(ppmstereo_module):                      # K5 / K5b (ppmtereo_update.py:291-312, :677)
+    for cls, fwd in _update_classes(ppmstereo_module):          # K5 / K5b / K6 (ppmtereo_update.py:291-312, :677, :458-482)
         if gru and not hasattr(cls, "_ppm_reference_forward"):
             cls._ppm_reference_forward = cls.forward
             cls.forward = fwd

@@ -1,0 +1,135 @@
+"""Lookup fused into the motion encoder's front end (csrc/corr_lookup.cu, K6).
+
+``MotionCorrFront(pcblock)`` computes ``F.gelu(pcblock(corr))`` -- the first line of the correlation branch of the
+reference's ``BasicMotionEncoder_v2.forward`` (models/core/ppmtereo_update.py:466) -- in one C-ABI call, either from a
+materialised lookup tensor or, fused, from a ``LookupRequest`` (the correlation block + the flow), in which case the
+(B, 36, h, w) lookup result is never written.  ``encoder_forward`` is the replacement ``install()`` puts on the encoder
+class: the reference's forward with that one line exchanged.
+"""
+from __future__ import annotations
+
+from typing import Dict, Tuple
+
+import torch
+import torch.nn.functional as F
+
+from . import _lib
+
+A_FLOATS, B_FLOATS = 4124, 19212          # PPM_MF_A_FLOATS / PPM_MF_B_FLOATS (include/ppm_b200.h)
+_ATTR = "_ppmstereo_b200_front"
+
+
+class LookupRequest:
+    """What ``forward_update_block`` hands to the encoder instead of ``corr_fn(flow)`` when the front end is fused."""
+
+    def __init__(self, block, flow: torch.Tensor):
+        self.block, self.flow = block, flow
+
+    def materialise(self) -> torch.Tensor:
+        return self.block(self.flow)
+
+
+def _b16(t: torch.Tensor) -> torch.Tensor:
+    return t.detach().to(torch.bfloat16).float()
+
+
+class MotionCorrFront:
+    def __init__(self, pcblock):
+        self.m = pcblock
+        self.lib = _lib.load()
+        self._versions = None
+        self._ws: Dict[Tuple, torch.Tensor] = {}
+
+    def supported(self) -> bool:
+        m = self.m
+        try:
+            return (tuple(m.ffn1[0].weight.shape) == (54, 36, 1, 1) and tuple(m.ffn2[2].weight.shape) == (256, 54, 1, 1)
+                    and [tuple(c.weight.shape) for c in m.conv_list] == [(36, 1, 1, 1), (36, 1, 7, 7)]
+                    and tuple(m.pw.weight.shape) == (36, 36, 1, 1))
+        except (AttributeError, IndexError):
+            return False
+
+    def _params(self):
+        m = self.m
+        convs = [m.ffn1[0], m.ffn1[2], m.conv_list[0], m.conv_list[1], m.pw, m.ffn2[0], m.ffn2[2]]
+        versions = tuple((c.weight._version, c.weight.data_ptr(), c.bias._version, c.bias.data_ptr()) for c in convs)
+        if versions != self._versions:
+            dev = m.pw.weight.device
+            a = torch.zeros(A_FLOATS, device=dev)
+            a[0:1944] = _b16(m.ffn1[0].weight).reshape(-1)
+            a[1944:1998] = _b16(m.ffn1[0].bias)
+            a[2000:4016].view(36, 56)[:, :54] = _b16(m.ffn1[2].weight).reshape(36, 54)
+            a[4016:4052] = _b16(m.ffn1[2].bias)
+            a[4052:4088] = _b16(m.conv_list[0].weight).reshape(-1)
+            a[4088:4124] = _b16(m.conv_list[0].bias)
+            b = torch.zeros(B_FLOATS, device=dev)
+            b[0:1764] = _b16(m.conv_list[1].weight).reshape(-1)
+            b[1764:1800] = _b16(m.conv_list[1].bias)
+            b[1800:3096] = _b16(m.pw.weight).reshape(-1)
+            b[3096:3132] = _b16(m.pw.bias)
+            b[3132:5076] = _b16(m.ffn2[0].weight).reshape(-1)
+            b[5076:5130] = _b16(m.ffn2[0].bias)
+            b[5132:18956] = _b16(m.ffn2[2].weight).reshape(256, 54).t().contiguous().reshape(-1)
+            b[18956:19212] = _b16(m.ffn2[2].bias)
+            self.wa, self.wb, self._versions = a, b, versions
+        return self.wa, self.wb
+
+    def __call__(self, corr) -> torch.Tensor:
+        wa, wb = self._params()
+        level0 = flow = corr_ptr = None
+        keep = None
+        if isinstance(corr, LookupRequest):
+            blk = corr.block
+            if getattr(blk, "_l0_only", False):
+                keep = (blk._level0, corr.flow.detach().float().contiguous())
+                level0, flow = keep[0].data_ptr(), keep[1].data_ptr()
+                B, _, H, W1 = keep[1].shape
+                W2 = blk._w2
+            else:
+                corr = corr.materialise()
+        if level0 is None:
+            if not corr.is_cuda or corr.dim() != 4 or corr.shape[1] != 36:
+                raise RuntimeError(f"corr must be a CUDA tensor (B, 36, h, w), got {tuple(corr.shape)}")
+            keep = corr.float().contiguous()
+            corr_ptr = keep.data_ptr()
+            B, _, H, W1 = keep.shape
+            W2 = 0
+        dev = wa.device
+        key = (B, H, W1)
+        ws = self._ws.get(key)
+        if ws is None:
+            self._ws.clear()
+            ws = self._ws[key] = torch.empty(B * 36 * H * W1, dtype=torch.float32, device=dev)
+        out = torch.empty(B, 256, H, W1, dtype=torch.bfloat16, device=dev)
+        _lib.check(self.lib.ppm_motion_corr_front(level0, flow, corr_ptr, wa.data_ptr(), wb.data_ptr(), B, H, W1, W2,
+                                                  ws.data_ptr(), out.data_ptr(), _lib.stream_ptr()),
+                   "ppm_motion_corr_front")
+        return out
+
+
+def _kernel_regime(t: torch.Tensor) -> bool:
+    return (t.is_cuda and torch.is_autocast_enabled() and torch.get_autocast_gpu_dtype() == torch.bfloat16
+            and not torch.is_grad_enabled())
+
+
+def encoder_forward(self, flow, corr, motion_hidden_state, inp):
+    """Replacement for ``BasicMotionEncoder_v2.forward`` (models/core/ppmtereo_update.py:458-482): identical, except that
+    ``F.gelu(self.convc1(corr))`` is one fused call in the bf16 autocast regime; ``corr`` may be a LookupRequest."""
+    if motion_hidden_state is None:
+        motion_hidden_state = self.init_conv(inp)
+    front = self.__dict__.get(_ATTR)
+    if front is None:
+        front = self.__dict__[_ATTR] = MotionCorrFront(self.convc1)
+    if _kernel_regime(flow) and front.supported():
+        cor = front(corr)
+    else:
+        if isinstance(corr, LookupRequest):
+            corr = corr.materialise()
+        cor = F.gelu(self.convc1(corr))
+    cor = F.relu(self.convc2(cor))
+    flo = F.relu(self.convf1(flow))
+    flo = F.relu(self.convf2(flo))
+    cor_flo = torch.cat([cor, flo, motion_hidden_state], dim=1)
+    out = F.relu(self.final_conv(cor_flo))
+    out, motion_hidden_state = torch.split(out, [126, 64], dim=1)
+    return torch.cat([out, flow], dim=1), motion_hidden_state

@@ -138,3 +138,22 @@ def test_flow_head_oracle_matches_reference_module():
     got = O.flow_head3d(x, dict(fh.state_dict()))
     assert got.shape == want.shape == (2, 2, 3, 5, 7)
     assert float((got - want).abs().max()) <= 1e-5
+
+
+def test_motion_corr_front_oracle_matches_reference_module():
+    import importlib
+    from oracle import ref_import
+    if not ref_import.available():
+        pytest.skip("reference tree not present")
+    ref_import.load_reference()
+    upd = importlib.import_module("models.core.ppmtereo_update")
+    torch.manual_seed(2)
+    pc = upd.PCBlock4_Deep_nopool_res(36, 256, k_conv=[1, 7]).eval()
+    corr = torch.randn(2, 36, 9, 13, generator=torch.Generator().manual_seed(3)) * 2
+    with torch.no_grad():
+        want = torch.nn.functional.gelu(pc(corr))
+    got = O.motion_corr_front(corr, dict(pc.state_dict()))
+    assert got.shape == want.shape == (2, 256, 9, 13)
+    assert float((got - want).abs().max()) <= 2e-6
+    lo = O.motion_corr_front(corr, dict(pc.state_dict()), mode="bf16")
+    assert float((lo - want).abs().max()) <= 3e-2 * float(want.abs().max())
