@@ -414,7 +414,7 @@ struct MotionFrontAParams {
   float* x2;                       // (B, 36, h, w) fp32
 };
 
-__global__ void __launch_bounds__(kLookupThreads)
+__global__ void __launch_bounds__(kLookupThreads, 3)      // <= 168 registers: 12 warps / SM for the gather's latency
 motion_front_a_kernel(const MotionFrontAParams p) {
   __shared__ __align__(16) float sw[mf::kASize];
   for (int i = threadIdx.x; i < mf::kASize; i += kLookupThreads) sw[i] = __ldg(p.wts + i);
