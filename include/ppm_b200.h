@@ -172,6 +172,26 @@ PPM_API int ppm_convex_upsample(const float* flow, const void* mask, int mask_dt
                         int rate, float* out, void* stream);
 
 /* ---------------------------------------------------------------------------------------
+ * K5c  SequenceUpdateBlock3D.forward (models/core/ppmtereo_update.py:971-1003) for a block without update-time /
+ * update-space attention and with the 2-D convex mask (PPMStereo's update_block08 / update_block04), one call:
+ *   net = gru(net, cat[inp, motion_features, motion_features_global]);  delta_flow = flow_head(net);
+ *   mask = 0.25 * mask_2d(net)      (mask_2d = Conv3x3(128,256) -> ReLU -> Conv1x1(256, n_mask), :~905)
+ * The 384-channel cat is never materialised (x_parts[3] are packed straight into the GRU's operand) and all tensors
+ * are frame-major (b*T, C, H, W) contiguous as the reference holds them outside the unit (no rearrange copies).
+ * net (b*T,128,H,W) fp32 or bf16 (type promotion as ppm_sepconv_gru3d); x_parts[i] (b*T,128,H,W), x_dtypes[i].
+ * gru_weights / gru_biases, flow_*: as ppm_sepconv_gru3d / ppm_flow_head3d.  mask_w1: bf16 [9][256][128] (tap order
+ * ih*3 + iw), mask_b1 fp32 [256]; mask_w2: bf16 [1][192][256] with rows n_mask..191 zero, mask_b2 fp32 [192].
+ * Outputs: net_out (b*T,128,H,W) net_dtype; mask_out (b*T,n_mask,H,W) bf16 (the 0.25 included: exact);
+ * dflow_out (b*T,2,H,W) bf16.  workspace: ppm_update_block3d_workspace bytes, 256-byte aligned. */
+PPM_API int ppm_update_block3d_workspace(int b, int T, int H, int W, size_t* bytes);
+PPM_API int ppm_update_block3d(const void* net, int net_dtype, const void* const* x_parts, const int* x_dtypes,
+                       const void* const* gru_weights, const float* const* gru_biases, const void* flow_w1,
+                       const float* flow_b1, const void* flow_w2, const float* flow_b2, const void* mask_w1,
+                       const float* mask_b1, const void* mask_w2, const float* mask_b2, int n_mask, int b, int T,
+                       int H, int W, void* workspace, size_t workspace_bytes, void* net_out, void* mask_out,
+                       void* dflow_out, void* stream);
+
+/* ---------------------------------------------------------------------------------------
  * K6  lookup fused into the motion encoder's front end.
  * Replaces `cor = F.gelu(self.convc1(corr))` of BasicMotionEncoder_v2.forward (models/core/ppmtereo_update.py:466),
  * convc1 = PCBlock4_Deep_nopool_res(36, 256, k_conv=[1, 7]) (:91-116), together with the CorrBlock1D.__call__ that

@@ -21,6 +21,7 @@ inline memory-block glue, copies on the compute stream):
   gru3d           SKSepConvGRU3D                                             ppmtereo_update.py:254-312
   flow_head       FlowHead3D                                                 ppmtereo_update.py:670-678
   mask_head       mask_2d                                                    ppmtereo_update.py:~905
+  update_block    installed arm only: SequenceUpdateBlock3D.forward as a whole (= gru3d + flow_head + mask_head + upd_attn)
   upsample        convex_upsample                                            ppmstereo.py:185-197
 """
 from __future__ import annotations
@@ -100,6 +101,11 @@ def _hook_model(tm: PhaseTimer, model):
         tm.module(ub.encoder, "motion_encoder")
         tm.module(ub.aggregator.to_v, "to_v")
         tm.module(ub.uncertainty, "uncertainty")
+        if hasattr(type(ub), "_ppm_reference_forward"):
+            # installed: SequenceUpdateBlock3D.forward is one call (K5c) on the levels without update attention, so its
+            # sub-modules never run there -- time the block as a whole (= gru3d + flow_head + mask_head + upd_attn)
+            tm.module(ub, "update_block")
+            continue
         tm.module(ub.gru, "gru3d")
         tm.module(ub.flow_head, "flow_head")
         tm.module(ub.mask_2d, "mask_head")

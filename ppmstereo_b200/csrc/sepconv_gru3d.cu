@@ -59,7 +59,9 @@ struct GruGemmParams {
   float* hstate;                     // [P, 128] the hidden state itself, fp32 storage (read by R / ZR / Q, rewritten by Q)
   int h_fp32;                        // 1: the caller's h is fp32 -> products / sums with h are fp32 ops (see below)
   const __nv_bfloat16* zbuf;         // Q: Z [P, 128]
-  void* out;                         // Q, last stage: (b, 128, T, H, W) contiguous, or nullptr
+  void* out;                         // Q (last stage) / RELU / LINEAR: strided (b, C, T, H, W) result, or nullptr:
+  long long out_sb, out_sc, out_st;  //   element (bb, ch, t, y, x) at bb*out_sb + ch*out_sc + t*out_st + y*W + x
+  float out_scale;                   // LINEAR: results multiplied by this (a power of two: exact) before the store
   int out_dtype;
   int N;                             // GEMM N: 64, 128, 192 or 256 (output channels padded with zero weights)
   int n_valid;                       // RELU / LINEAR: output channels actually stored (<= N)
@@ -317,6 +319,9 @@ gru_gemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constan
               if (mode == GR_EPI_RELU) {
                 #pragma unroll
                 for (int e = 0; e < 8; ++e) v[e] = fmaxf(v[e], 0.f);
+              } else {
+                #pragma unroll
+                for (int e = 0; e < 8; ++e) v[e] *= p.out_scale;
               }
               if (p.dst0) {
                 if (col0 + g * 8 + 8 <= p.n_valid) {
@@ -329,9 +334,8 @@ gru_gemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constan
                 }
               }
               if (p.out) {
-                const long long cs = static_cast<long long>(p.T) * HW;
-                const long long o = ((static_cast<long long>(bb) * p.n_valid + col0 + g * 8) * p.T + t) * HW +
-                                    static_cast<long long>(y) * p.W + x;
+                const long long cs = p.out_sc;
+                const long long o = bb * p.out_sb + (col0 + g * 8) * p.out_sc + t * p.out_st + static_cast<long long>(y) * p.W + x;
                 #pragma unroll
                 for (int e = 0; e < 8; ++e) {
                   if (col0 + g * 8 + e < p.n_valid) {
@@ -363,8 +367,8 @@ gru_gemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constan
             *reinterpret_cast<float4*>(hs + 4) = make_float4(v[4], v[5], v[6], v[7]);
             *reinterpret_cast<uint4*>(p.hbuf + pos * kGrHidden + ch) = gr_pack8(v);
             if (p.out) {
-              const long long o = ((static_cast<long long>(bb) * kGrHidden + ch) * p.T + t) * HW + static_cast<long long>(y) * p.W + x;
-              const long long cs = static_cast<long long>(p.T) * HW;
+              const long long o = bb * p.out_sb + ch * p.out_sc + t * p.out_st + static_cast<long long>(y) * p.W + x;
+              const long long cs = p.out_sc;
               if (p.out_dtype == PPM_BF16) {
                 __nv_bfloat16* ob = static_cast<__nv_bfloat16*>(p.out) + o;
                 #pragma unroll
@@ -430,6 +434,12 @@ static int gru_launch(const CUtensorMap& a0, const CUtensorMap& a1, const CUtens
   p.b = s.b; p.T = s.T; p.H = s.H; p.W = s.W; p.bw = s.bw; p.bh = s.bh;
   p.tiles_x = s.tiles_x; p.tiles_y = s.tiles_y; p.n_tiles = s.n_tiles;
   p.t_fastest = p.kt > 1 && p.kw == 1 && p.kh == 1 ? 1 : 0;
+  if (p.out && p.out_sc == 0) {                           // default: contiguous (b, C, T, H, W)
+    const long long HW = static_cast<long long>(s.H) * s.W;
+    const int C = (p.mode == GR_EPI_Q) ? kGrHidden : p.n_valid;
+    p.out_st = HW; p.out_sc = HW * s.T; p.out_sb = HW * s.T * C;
+  }
+  if (p.out_scale == 0.f) p.out_scale = 1.f;
   const int smem = kGrStages * (kGrABytes + p.N * 128) + 1024;
   static std::mutex mu;
   static bool attr_done[64] = {};
@@ -458,6 +468,90 @@ static int gru_pack(const void* src, long long sb, long long sc, long long st_, 
   gru_pack_kernel<SrcT><<<grid, 256, 0, st>>>(static_cast<const SrcT*>(src), sb, sc, st_, s.T, HW, C, dst_c, c_off, dst, dst32);
   PPM_CUDA(cudaGetLastError());
   return PPM_OK;
+}
+
+// The eight GEMMs of one unit on packed operands (X, Hb, Hs filled by the caller).  out strides 0 = contiguous (b,128,T,H,W).
+static int gru_unit(const GruShape& s, __nv_bfloat16* X, __nv_bfloat16* Hb, __nv_bfloat16* RH, __nv_bfloat16* Z,
+                    __nv_bfloat16* G, float* Hs, const void* const* weights, const float* const* biases, int h_fp32,
+                    void* out, int out_dtype, long long out_sb, long long out_sc, long long out_st, cudaStream_t st) {
+  int rc;
+  CUtensorMap mX, mH, mRH, mG, mW[8];
+  if ((rc = gru_act_map(&mX, X, 384, s))) return rc;
+  if ((rc = gru_act_map(&mH, Hb, 128, s))) return rc;
+  if ((rc = gru_act_map(&mRH, RH, 128, s))) return rc;
+  if ((rc = gru_act_map(&mG, G, 256, s))) return rc;
+  const int w_cin[8] = {512, 128, 128, 512, 512, 512, 512, 512};
+  const int w_n[8] = {256, 128, 128, 128, 256, 128, 256, 128};
+  const int w_taps[8] = {15, 5, 5, 5, 5, 5, 5, 5};
+  for (int i = 0; i < 8; ++i)
+    if ((rc = gru_w_map(&mW[i], weights[i], w_cin[i], w_n[i], w_taps[i]))) return rc;
+
+  GruGemmParams p{};
+  p.hbuf = Hb; p.hstate = Hs; p.h_fp32 = h_fp32; p.zbuf = Z; p.out = nullptr; p.out_dtype = out_dtype;
+  // ---- stage 1: along W.  z / r = Conv(15) -> GELU -> Conv(5) (ppmtereo_update.py:257-266)
+  p.bias = biases[0]; p.N = 256; p.kw = 15; p.kh = 1; p.kt = 1; p.mode = GR_EPI_GELU;
+  p.seg0_chunks = 2; p.seg0_c0 = 0; p.seg1_chunks = 6; p.dst0 = G; p.dst1 = nullptr;
+  if ((rc = gru_launch(mH, mX, mW[0], p, s, st))) return rc;
+  p.bias = biases[1]; p.N = 128; p.kw = 5; p.mode = GR_EPI_Z; p.seg0_chunks = 2; p.seg0_c0 = 0; p.seg1_chunks = 0; p.dst0 = Z;
+  if ((rc = gru_launch(mG, mG, mW[1], p, s, st))) return rc;
+  p.bias = biases[2]; p.mode = GR_EPI_R; p.seg0_c0 = 128; p.dst0 = nullptr; p.dst1 = RH;
+  if ((rc = gru_launch(mG, mG, mW[2], p, s, st))) return rc;
+  p.bias = biases[3]; p.mode = GR_EPI_Q; p.seg0_c0 = 0; p.seg0_chunks = 2; p.seg1_chunks = 6;
+  if ((rc = gru_launch(mRH, mX, mW[3], p, s, st))) return rc;
+  // ---- stages 2 (along H) and 3 (along T): z | r as one N = 256 GEMM, then q
+  for (int stage = 2; stage <= 3; ++stage) {
+    const int wi = stage == 2 ? 4 : 6;
+    p.kw = 1; p.kh = stage == 2 ? 5 : 1; p.kt = stage == 3 ? 5 : 1;
+    p.bias = biases[wi]; p.N = 256; p.mode = GR_EPI_ZR; p.seg0_chunks = 2; p.seg0_c0 = 0; p.seg1_chunks = 6;
+    p.dst0 = Z; p.dst1 = RH; p.out = nullptr;
+    if ((rc = gru_launch(mH, mX, mW[wi], p, s, st))) return rc;
+    p.bias = biases[wi + 1]; p.N = 128; p.mode = GR_EPI_Q; p.out = stage == 3 ? out : nullptr;
+    p.out_sb = out_sb; p.out_sc = out_sc; p.out_st = out_st;
+    if ((rc = gru_launch(mRH, mX, mW[wi + 1], p, s, st))) return rc;
+  }
+  return PPM_OK;
+}
+
+// Flow head on a channels-last bf16 state `a_in` [P,128]; Hd = [P,256] scratch.  out strides 0 = contiguous (b,2,T,H,W).
+static int flow_head_unit(const GruShape& s, const __nv_bfloat16* a_in, __nv_bfloat16* Hd, const void* w1, const float* b1,
+                          const void* w2, const float* b2, void* out, int out_dtype, long long out_sb, long long out_sc,
+                          long long out_st, cudaStream_t st) {
+  int rc;
+  CUtensorMap mA, mH, mW1, mW2;
+  if ((rc = gru_act_map(&mA, a_in, 128, s))) return rc;
+  if ((rc = gru_act_map(&mH, Hd, 256, s))) return rc;
+  if ((rc = gru_w_map(&mW1, w1, 128, 256, 27))) return rc;
+  if ((rc = gru_w_map(&mW2, w2, 256, 64, 27))) return rc;
+  GruGemmParams p{};
+  p.kw = 3; p.kh = 3; p.kt = 3; p.out_dtype = out_dtype;
+  p.bias = b1; p.N = 256; p.n_valid = 256; p.mode = GR_EPI_RELU; p.seg0_chunks = 2; p.seg0_c0 = 0; p.seg1_chunks = 0;
+  p.dst0 = Hd; p.dst_ld = 256; p.dst_c0 = 0; p.out = nullptr;
+  if ((rc = gru_launch(mA, mA, mW1, p, s, st))) return rc;
+  p.bias = b2; p.N = 64; p.n_valid = 2; p.mode = GR_EPI_LINEAR; p.seg0_chunks = 4; p.dst0 = nullptr; p.out = out;
+  p.out_sb = out_sb; p.out_sc = out_sc; p.out_st = out_st;
+  return gru_launch(mH, mH, mW2, p, s, st);
+}
+
+// mask_2d head (ppmtereo_update.py:~905, used at :996): 0.25 * Conv1x1(relu(Conv3x3(net))), 128 -> 256 -> 144, per frame
+// (a 3 x 3 x 1 footprint).  w2 / b2 padded to N = 192.
+static int mask_head_unit(const GruShape& s, const __nv_bfloat16* a_in, __nv_bfloat16* Hd, const void* w1, const float* b1,
+                          const void* w2, const float* b2, int n_mask, void* out, int out_dtype, long long out_sb,
+                          long long out_sc, long long out_st, cudaStream_t st) {
+  int rc;
+  CUtensorMap mA, mH, mW1, mW2;
+  if ((rc = gru_act_map(&mA, a_in, 128, s))) return rc;
+  if ((rc = gru_act_map(&mH, Hd, 256, s))) return rc;
+  if ((rc = gru_w_map(&mW1, w1, 128, 256, 9))) return rc;
+  if ((rc = gru_w_map(&mW2, w2, 256, 192, 1))) return rc;
+  GruGemmParams p{};
+  p.kw = 3; p.kh = 3; p.kt = 1; p.out_dtype = out_dtype;
+  p.bias = b1; p.N = 256; p.n_valid = 256; p.mode = GR_EPI_RELU; p.seg0_chunks = 2; p.seg0_c0 = 0; p.seg1_chunks = 0;
+  p.dst0 = Hd; p.dst_ld = 256; p.dst_c0 = 0; p.out = nullptr;
+  if ((rc = gru_launch(mA, mA, mW1, p, s, st))) return rc;
+  p.kw = 1; p.kh = 1;
+  p.bias = b2; p.N = 192; p.n_valid = n_mask; p.mode = GR_EPI_LINEAR; p.seg0_chunks = 4; p.dst0 = nullptr; p.out = out;
+  p.out_scale = 0.25f; p.out_sb = out_sb; p.out_sc = out_sc; p.out_st = out_st;
+  return gru_launch(mH, mH, mW2, p, s, st);
 }
 
 }  // namespace ppm
@@ -504,40 +598,7 @@ extern "C" int ppm_sepconv_gru3d(const void* h, int h_dtype, int64_t hsb, int64_
   if (h_dtype == PPM_BF16) rc = gru_pack<__nv_bfloat16>(h, hsb, hsc, hst, s, 128, 128, 0, Hb, Hs, st);
   else rc = gru_pack<float>(h, hsb, hsc, hst, s, 128, 128, 0, Hb, Hs, st);
   if (rc) return rc;
-  CUtensorMap mX, mH, mRH, mG, mW[8];
-  if ((rc = gru_act_map(&mX, X, 384, s))) return rc;
-  if ((rc = gru_act_map(&mH, Hb, 128, s))) return rc;
-  if ((rc = gru_act_map(&mRH, RH, 128, s))) return rc;
-  if ((rc = gru_act_map(&mG, G, 256, s))) return rc;
-  const int w_cin[8] = {512, 128, 128, 512, 512, 512, 512, 512};
-  const int w_n[8] = {256, 128, 128, 128, 256, 128, 256, 128};
-  const int w_taps[8] = {15, 5, 5, 5, 5, 5, 5, 5};
-  for (int i = 0; i < 8; ++i)
-    if ((rc = gru_w_map(&mW[i], weights[i], w_cin[i], w_n[i], w_taps[i]))) return rc;
-
-  GruGemmParams p{};
-  p.hbuf = Hb; p.hstate = Hs; p.h_fp32 = h_dtype == PPM_F32 ? 1 : 0; p.zbuf = Z; p.out = nullptr; p.out_dtype = out_dtype;
-  // ---- stage 1: along W.  z / r = Conv(15) -> GELU -> Conv(5) (ppmtereo_update.py:257-266)
-  p.bias = biases[0]; p.N = 256; p.kw = 15; p.kh = 1; p.kt = 1; p.mode = GR_EPI_GELU;
-  p.seg0_chunks = 2; p.seg0_c0 = 0; p.seg1_chunks = 6; p.dst0 = G; p.dst1 = nullptr;
-  if ((rc = gru_launch(mH, mX, mW[0], p, s, st))) return rc;
-  p.bias = biases[1]; p.N = 128; p.kw = 5; p.mode = GR_EPI_Z; p.seg0_chunks = 2; p.seg0_c0 = 0; p.seg1_chunks = 0; p.dst0 = Z;
-  if ((rc = gru_launch(mG, mG, mW[1], p, s, st))) return rc;
-  p.bias = biases[2]; p.mode = GR_EPI_R; p.seg0_c0 = 128; p.dst0 = nullptr; p.dst1 = RH;
-  if ((rc = gru_launch(mG, mG, mW[2], p, s, st))) return rc;
-  p.bias = biases[3]; p.mode = GR_EPI_Q; p.seg0_c0 = 0; p.seg0_chunks = 2; p.seg1_chunks = 6;
-  if ((rc = gru_launch(mRH, mX, mW[3], p, s, st))) return rc;
-  // ---- stages 2 (along H) and 3 (along T): z | r as one N = 256 GEMM, then q
-  for (int stage = 2; stage <= 3; ++stage) {
-    const int wi = stage == 2 ? 4 : 6;
-    p.kw = 1; p.kh = stage == 2 ? 5 : 1; p.kt = stage == 3 ? 5 : 1;
-    p.bias = biases[wi]; p.N = 256; p.mode = GR_EPI_ZR; p.seg0_chunks = 2; p.seg0_c0 = 0; p.seg1_chunks = 6;
-    p.dst0 = Z; p.dst1 = RH; p.out = nullptr;
-    if ((rc = gru_launch(mH, mX, mW[wi], p, s, st))) return rc;
-    p.bias = biases[wi + 1]; p.N = 128; p.mode = GR_EPI_Q; p.out = stage == 3 ? out : nullptr;
-    if ((rc = gru_launch(mRH, mX, mW[wi + 1], p, s, st))) return rc;
-  }
-  return PPM_OK;
+  return gru_unit(s, X, Hb, RH, Z, G, Hs, weights, biases, h_dtype == PPM_F32 ? 1 : 0, out, out_dtype, 0, 0, 0, st);
 }
 
 // ------------------------------------------------------------------------------------------------ FlowHead3D
@@ -582,17 +643,74 @@ extern "C" int ppm_flow_head3d(const void* x, int x_dtype, int64_t xsb, int64_t 
     if (rc) return rc;
     a_in = Xc;
   }
-  CUtensorMap mA, mH, mW1, mW2;
-  if ((rc = gru_act_map(&mA, a_in, 128, s))) return rc;
-  if ((rc = gru_act_map(&mH, Hd, 256, s))) return rc;
-  if ((rc = gru_w_map(&mW1, w1, 128, 256, 27))) return rc;
-  if ((rc = gru_w_map(&mW2, w2, 256, 64, 27))) return rc;
-  GruGemmParams p{};
-  p.kw = 3; p.kh = 3; p.kt = 3; p.out_dtype = out_dtype;
-  p.bias = b1; p.N = 256; p.n_valid = 256; p.mode = GR_EPI_RELU; p.seg0_chunks = 2; p.seg0_c0 = 0; p.seg1_chunks = 0;
-  p.dst0 = Hd; p.dst_ld = 256; p.dst_c0 = 0; p.out = nullptr;
-  if ((rc = gru_launch(mA, mA, mW1, p, s, st))) return rc;
-  p.bias = b2; p.N = 64; p.n_valid = 2; p.mode = GR_EPI_LINEAR; p.seg0_chunks = 4; p.dst0 = nullptr; p.out = out;
-  if ((rc = gru_launch(mH, mH, mW2, p, s, st))) return rc;
+  return flow_head_unit(s, a_in, Hd, w1, b1, w2, b2, out, out_dtype, 0, 0, 0, st);
+}
+
+// ------------------------------------------------------------------------------------------------ whole update block
+// SequenceUpdateBlock3D.forward (reference models/core/ppmtereo_update.py:971-1003) for a block WITHOUT update-time /
+// update-space attention (update_block08 / update_block04 of PPMStereo) and with the 2-D convex mask, as one call:
+//   inp_tensor = cat[inp, motion_features, motion_features_global]       -> never materialised: the three tensors are
+//                                                                           packed straight into the GRU's operand
+//   net = gru(net, inp_tensor); delta_flow = flow_head(net); mask = 0.25 * mask_2d(net)
+// All tensors frame-major (b*T, C, H, W) contiguous, as the reference holds them outside the unit; results are written
+// frame-major as well, so neither the `rearrange` copies around the unit nor the 384-channel cat exist.
+extern "C" int ppm_update_block3d_workspace(int b, int T, int H, int W, size_t* bytes) {
+  size_t g = 0;
+  if (int rc = ppm_sepconv_gru3d_workspace(b, T, H, W, &g)) return rc;
+  PPM_CHECK(bytes, PPM_ERR_ARG, "ppm_update_block3d_workspace: null pointer");
+  *bytes = g + static_cast<size_t>(b) * T * H * W * 256 * 2;
   return PPM_OK;
+}
+
+extern "C" int ppm_update_block3d(const void* net, int net_dtype, const void* const* x_parts, const int* x_dtypes,
+                                  const void* const* gru_weights, const float* const* gru_biases, const void* flow_w1,
+                                  const float* flow_b1, const void* flow_w2, const float* flow_b2, const void* mask_w1,
+                                  const float* mask_b1, const void* mask_w2, const float* mask_b2, int n_mask, int b, int T,
+                                  int H, int W, void* workspace, size_t workspace_bytes, void* net_out, void* mask_out,
+                                  void* dflow_out, void* stream) {
+  using namespace ppm;
+  PPM_CHECK(net && x_parts && x_dtypes && gru_weights && gru_biases && flow_w1 && flow_b1 && flow_w2 && flow_b2 && mask_w1 &&
+                mask_b1 && mask_w2 && mask_b2 && workspace && net_out && mask_out && dflow_out,
+            PPM_ERR_ARG, "ppm_update_block3d: null pointer");
+  PPM_CHECK(b > 0 && T > 0 && H > 0 && W > 0 && static_cast<long long>(b) * T <= 65535, PPM_ERR_ARG, "ppm_update_block3d: bad shape");
+  PPM_CHECK(n_mask > 0 && n_mask <= 192, PPM_ERR_UNSUPPORTED, "ppm_update_block3d: n_mask = %d not in (0, 192]", n_mask);
+  PPM_CHECK(net_dtype == PPM_F32 || net_dtype == PPM_BF16, PPM_ERR_ARG, "ppm_update_block3d: bad dtype");
+  for (int i = 0; i < 3; ++i)
+    PPM_CHECK(x_parts[i] && (x_dtypes[i] == PPM_F32 || x_dtypes[i] == PPM_BF16), PPM_ERR_ARG,
+              "ppm_update_block3d: input part %d null or of a bad dtype", i);
+  for (int i = 0; i < 8; ++i)
+    PPM_CHECK(gru_weights[i] && gru_biases[i] && (reinterpret_cast<uintptr_t>(gru_weights[i]) & 15) == 0, PPM_ERR_ARG,
+              "ppm_update_block3d: GRU weight / bias %d null or misaligned", i);
+  size_t need = 0;
+  ppm_update_block3d_workspace(b, T, H, W, &need);
+  PPM_CHECK(workspace_bytes >= need, PPM_ERR_ARG, "ppm_update_block3d: workspace of %zu bytes < %zu needed", workspace_bytes, need);
+  PPM_CHECK((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, PPM_ERR_ARG, "ppm_update_block3d: workspace must be 256-byte aligned");
+  const GruShape s = gru_shape(b, T, H, W);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const long long HW = static_cast<long long>(H) * W;
+  __nv_bfloat16* X = static_cast<__nv_bfloat16*>(workspace);
+  __nv_bfloat16* Hb = X + s.P * 384;
+  __nv_bfloat16* RH = Hb + s.P * 128;
+  __nv_bfloat16* Z = RH + s.P * 128;
+  __nv_bfloat16* G = Z + s.P * 128;
+  float* Hs = reinterpret_cast<float*>(G + s.P * 256);
+  __nv_bfloat16* Hd = reinterpret_cast<__nv_bfloat16*>(Hs + s.P * 128);
+  int rc;
+  // frame-major (b*T, 128, H, W) seen as (b, 128, T, H, W): sb = T*128*HW, sc = HW, st = 128*HW
+  const long long sb = T * 128 * HW, sc = HW, stt = 128 * HW;
+  for (int i = 0; i < 3; ++i) {
+    if (x_dtypes[i] == PPM_BF16) rc = gru_pack<__nv_bfloat16>(x_parts[i], sb, sc, stt, s, 128, 384, 128 * i, X, nullptr, st);
+    else rc = gru_pack<float>(x_parts[i], sb, sc, stt, s, 128, 384, 128 * i, X, nullptr, st);
+    if (rc) return rc;
+  }
+  if (net_dtype == PPM_BF16) rc = gru_pack<__nv_bfloat16>(net, sb, sc, stt, s, 128, 128, 0, Hb, Hs, st);
+  else rc = gru_pack<float>(net, sb, sc, stt, s, 128, 128, 0, Hb, Hs, st);
+  if (rc) return rc;
+  if ((rc = gru_unit(s, X, Hb, RH, Z, G, Hs, gru_weights, gru_biases, net_dtype == PPM_F32 ? 1 : 0, net_out, net_dtype, sb, sc,
+                     stt, st)))
+    return rc;
+  if ((rc = flow_head_unit(s, Hb, Hd, flow_w1, flow_b1, flow_w2, flow_b2, dflow_out, PPM_BF16, T * 2 * HW, HW, 2 * HW, st)))
+    return rc;
+  return mask_head_unit(s, Hb, Hd, mask_w1, mask_b1, mask_w2, mask_b2, n_mask, mask_out, PPM_BF16,
+                        static_cast<long long>(T) * n_mask * HW, HW, static_cast<long long>(n_mask) * HW, st);
 }

@@ -184,3 +184,95 @@ def flow_head_forward(self, x: torch.Tensor) -> torch.Tensor:
             self.__dict__[_ATTR] = impl
         return impl(x)
     return type(self)._ppm_reference_forward(self, x)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# SequenceUpdateBlock3D.forward (models/core/ppmtereo_update.py:971-1003) as one call (K5c)
+# ---------------------------------------------------------------------------------------------------------------
+class UpdateBlock3D:
+    """GRU + flow head + 2-D mask head of one reference ``SequenceUpdateBlock3D`` without update attention."""
+
+    def __init__(self, block):
+        self.block = block
+        self.lib = _lib.load()
+        self.gru = SepConvGRU3D(block.gru)
+        self.head = FlowHead3D(block.flow_head)
+        self._mask_versions = None
+        self._ws: Dict[Tuple, torch.Tensor] = {}
+
+    def supported(self) -> bool:
+        blk = self.block
+        try:
+            m1, m2 = blk.mask_2d[0], blk.mask_2d[2]
+            return (getattr(blk, "attention_type", None) is None and not blk.use_convex_3d
+                    and tuple(m1.weight.shape) == (256, HIDDEN, 3, 3) and m2.weight.shape[1:] == (256, 1, 1)
+                    and m2.weight.shape[0] <= 192 and tuple(blk.flow_head.conv1.weight.shape) == (256, HIDDEN, 3, 3, 3)
+                    and tuple(blk.flow_head.conv2.weight.shape) == (2, 256, 3, 3, 3))
+        except (AttributeError, IndexError):
+            return False
+
+    def _mask_params(self):
+        m1, m2 = self.block.mask_2d[0], self.block.mask_2d[2]
+        versions = tuple((c.weight._version, c.weight.data_ptr(), c.bias._version, c.bias.data_ptr()) for c in (m1, m2))
+        if versions != self._mask_versions:
+            self.mw1 = _pack_weight(m1)                                                  # (9, 256, 128)
+            w2 = _pack_weight(m2)                                                        # (1, n_mask, 256)
+            self.n_mask = w2.shape[1]
+            self.mw2 = torch.zeros(1, 192, 256, dtype=torch.bfloat16, device=w2.device)
+            self.mw2[:, :self.n_mask] = w2
+            self.mb1 = m1.bias.detach().to(torch.bfloat16).float().contiguous()
+            self.mb2 = torch.zeros(192, device=w2.device)
+            self.mb2[:self.n_mask] = m2.bias.detach().to(torch.bfloat16).float()
+            self._mask_versions = versions
+
+    def __call__(self, net, inp, motion_features, motion_features_global, t: int):
+        parts = []
+        for name, x in (("net", net), ("inp", inp), ("motion_features", motion_features),
+                        ("motion_features_global", motion_features_global)):
+            if not x.is_cuda or x.dim() != 4 or x.shape[1] != HIDDEN:
+                raise RuntimeError(f"{name} must be a CUDA tensor (b*T, {HIDDEN}, h, w), got {tuple(x.shape)}")
+            if x.dtype not in (torch.float32, torch.bfloat16):
+                x = x.float()
+            parts.append(x.contiguous())
+        net, xs = parts[0], parts[1:]
+        bt, _, H, W = net.shape
+        b = bt // t
+        if any(tuple(x.shape) != tuple(net.shape) for x in xs):
+            raise RuntimeError("net, inp, motion_features, motion_features_global must share their shape")
+        wptr, bptr = self.gru._params()
+        self.head._params()
+        self._mask_params()
+        key = (b, t, H, W, net.device)
+        ws = self._ws.get(key)
+        if ws is None:
+            n = ctypes.c_size_t()
+            _lib.check(self.lib.ppm_update_block3d_workspace(b, t, H, W, ctypes.byref(n)), "ppm_update_block3d_workspace")
+            self._ws.clear()
+            ws = self._ws[key] = torch.empty(n.value, dtype=torch.uint8, device=net.device)
+        net_out = torch.empty_like(net)
+        mask = torch.empty(bt, self.n_mask, H, W, dtype=torch.bfloat16, device=net.device)
+        dflow = torch.empty(bt, 2, H, W, dtype=torch.bfloat16, device=net.device)
+        xp = _lib.ptr_array(xs)
+        xd = (ctypes.c_int * 3)(*[_lib.dtype_code(x) for x in xs])
+        _lib.check(self.lib.ppm_update_block3d(net.data_ptr(), _lib.dtype_code(net), xp, xd, wptr, bptr,
+                                               self.head.w1.data_ptr(), self.head.b1.data_ptr(), self.head.w2.data_ptr(),
+                                               self.head.b2.data_ptr(), self.mw1.data_ptr(), self.mb1.data_ptr(),
+                                               self.mw2.data_ptr(), self.mb2.data_ptr(), self.n_mask, b, t, H, W,
+                                               ws.data_ptr(), ws.numel(), net_out.data_ptr(), mask.data_ptr(),
+                                               dflow.data_ptr(), _lib.stream_ptr()), "ppm_update_block3d")
+        return net_out, mask, dflow
+
+
+def update_block_forward(self, net, inp, motion_features, motion_features_global, t=1):
+    """Replacement for ``SequenceUpdateBlock3D.forward`` installed by ``ppmstereo_b200.install``: one call for blocks
+    without update attention in the bf16 autocast regime; the block's own forward otherwise (it then still reaches the
+    patched GRU / flow head classes)."""
+    if (net.is_cuda and net.dtype in (torch.bfloat16, torch.float32) and torch.is_autocast_enabled()
+            and torch.get_autocast_gpu_dtype() == torch.bfloat16 and not torch.is_grad_enabled()):
+        impl = self.__dict__.get(_ATTR)
+        if impl is None:
+            impl = UpdateBlock3D(self)
+            self.__dict__[_ATTR] = impl
+        if impl.supported():
+            return impl(net, inp, motion_features, motion_features_global, t)
+    return type(self)._ppm_reference_forward(self, net, inp, motion_features, motion_features_global, t=t)

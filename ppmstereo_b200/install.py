@@ -17,7 +17,7 @@ import torch.nn.functional as F
 import sys
 
 from .corr import CorrBlock1D
-from .gru import flow_head_forward, gru_forward
+from .gru import flow_head_forward, gru_forward, update_block_forward
 from .motion import LookupRequest, encoder_forward
 from .memory import C, PPMMemory, softmax_scale
 from .upsample import convex_upsample
@@ -135,7 +135,8 @@ def _update_classes(ppmstereo_module):
     models/core/ppmstereo.py:17-24)."""
     upd = sys.modules.get(ppmstereo_module.SequenceUpdateBlock3D.__module__)
     pairs = [(getattr(upd, "SKSepConvGRU3D", None), gru_forward), (getattr(upd, "FlowHead3D", None), flow_head_forward),
-             (getattr(upd, "BasicMotionEncoder_v2", None), encoder_forward)]
+             (getattr(upd, "BasicMotionEncoder_v2", None), encoder_forward),
+             (getattr(upd, "SequenceUpdateBlock3D", None), update_block_forward)]
     return [(c, f) for c, f in pairs if c is not None]
 
 

@@ -204,3 +204,41 @@ def test_no_write_outside_output_and_workspace(env, flow_head, shape):
     assert bool((ws[:lo] == 0x5A).all()) and bool((ws[lo + n.value:] == 0x5A).all())
     assert bool((outbuf[:1024] == -7.0).all()) and bool((outbuf[1024 + n_out:] == -7.0).all())
     assert torch.equal(outbuf[1024:1024 + n_out].view(b, 2, T, H, W), want_f)
+
+
+# ------------------------------------------------------------------------------------------------ whole update block (K5c)
+@pytest.mark.parametrize("shape", [(1, 4, 6, 9), (2, 3, 23, 40), (1, 6, 46, 80)])
+def test_update_block_vs_reference_forward_under_autocast(env, shape):
+    """SequenceUpdateBlock3D.forward (no update attention, 2-D mask) as ONE call -- GRU + flow head + mask head, the
+    384-channel cat never built, frame-major in and out -- against the reference block on torch/cuDNN."""
+    P, _ = env
+    upd = importlib.import_module("models.core.ppmtereo_update")
+    torch.manual_seed(9)
+    blk = upd.SequenceUpdateBlock3D(hidden_dim=128, cor_planes=36, mask_size=4).cuda().eval()
+    b, T, H, W = shape
+    g = torch.Generator(device="cuda").manual_seed(sum(shape))
+    rn = lambda c: torch.randn(b * T, c, H, W, generator=g, device="cuda")
+    net, inp, mf, mfg = torch.tanh(rn(128)), torch.relu(rn(128)).bfloat16(), rn(128), rn(128)
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        want_net, want_mask, want_df = blk(net, inp, mf, mfg, t=T)
+    k = P.UpdateBlock3D(blk)
+    assert k.supported()
+    got_net, got_mask, got_df = k(net, inp, mf, mfg, T)
+    # the heads' own arithmetic: the reference heads applied to OUR GRU result (the 3 % one-ulp differences of `net` would
+    # otherwise smear over every output of the 3 x 3 convolutions behind it)
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        net5 = got_net.reshape(b, T, 128, H, W).permute(0, 2, 1, 3, 4)
+        same_in_mask = 0.25 * blk.mask_2d(got_net)
+        same_in_df = blk.flow_head(net5).permute(0, 2, 1, 3, 4).reshape(b * T, 2, H, W)
+    checks = (("net", got_net, want_net, 0.93), ("mask (same input)", got_mask, same_in_mask, 0.97),
+              ("delta_flow (same input)", got_df, same_in_df, 0.93), ("mask", got_mask, want_mask, 0.0),
+              ("delta_flow", got_df, want_df, 0.0))
+    for name, got, want, min_same in checks:
+        assert got.shape == want.shape and got.dtype == want.dtype, (name, got.shape, want.shape, got.dtype, want.dtype)
+        d = (got.float() - want.float()).abs()
+        scale = max(1.0, float(want.float().abs().max()))
+        same = float((d <= 1e-6).float().mean())
+        print(f"update block {shape} {name}: {same * 100:.2f} % identical, max |diff| {float(d.max()):.4f} of {scale:.2f}")
+        assert float(d.max()) <= 2.0 ** -6 * scale, name
+        assert float(d.mean()) <= 2e-4 * scale, name
+        assert same >= min_same, name
