@@ -478,3 +478,27 @@ def motion_corr_front(corr: torch.Tensor, params: dict, mode: str = "fp32") -> t
     u = rnd(gelu(_conv1x1(x, p["ffn2.0.weight"], p["ffn2.0.bias"], rnd)))
     out = _conv1x1(u, p["ffn2.2.weight"], p["ffn2.2.bias"], rnd)
     return rnd(gelu(out))
+
+
+def motion_encoder(flow: torch.Tensor, corr: torch.Tensor, motion_hidden_state: torch.Tensor, params: dict,
+                   mode: str = "fp32") -> Tuple[torch.Tensor, torch.Tensor]:
+    """BasicMotionEncoder_v2.forward (models/core/ppmtereo_update.py:458-482) with ``motion_hidden_state`` given
+    (init_conv, :462-464, is the caller's on the first iteration).  flow (B,2,h,w), corr (B,36,h,w),
+    motion_hidden_state (B,64,h,w); params: the encoder's state dict.  Every Conv2d is written as a sum over its kernel
+    offsets of shifted channel contractions (conv3d_shifted with a one-frame time axis); mode "bf16" = the autocast
+    regime, each convolution bf16(bf16(acc) + bias).  Returns (motion_features (B,128,h,w) fp32 -- the cat with the fp32
+    flow promotes --, new motion_hidden_state (B,64,h,w))."""
+    rnd = bf16_round if mode == "bf16" else (lambda t: t)
+    relu = torch.relu
+
+    def conv(x, name):
+        w, b = params[name + ".weight"], params[name + ".bias"]
+        return conv3d_shifted(x.unsqueeze(2), w.unsqueeze(2), b, rnd).squeeze(2)
+
+    pc = {k[len("convc1."):]: v for k, v in params.items() if k.startswith("convc1.")}
+    cor = motion_corr_front(corr, pc, mode)
+    cor = relu(conv(cor, "convc2"))
+    flo = relu(conv(flow.float(), "convf1"))
+    flo = relu(conv(flo, "convf2"))
+    out = relu(conv(torch.cat([cor, flo, rnd(motion_hidden_state.float())], dim=1), "final_conv"))
+    return torch.cat([out[:, :126], flow.float()], dim=1), out[:, 126:190]

@@ -34,6 +34,11 @@ int make_tensor_map(CUtensorMap* map, CUtensorMapDataType dtype, int rank, const
                     const uint64_t* dims, const uint64_t* strides_bytes, const uint32_t* box,
                     CUtensorMapSwizzle swizzle);
 
+// K6 (csrc/corr_lookup.cu): fused lookup + motion-encoder front end; used by ppm_motion_corr_front and ppm_motion_encoder.
+int motion_front_launch(const void* level0, const float* flow, const float* corr, const float* weights_a,
+                        const float* weights_b, int B, int H, int W1, int W2, float* x2_ws, void* cor, int channels_last,
+                        cudaStream_t st);
+
 // ---------------------------------------------------------------- device helpers
 #ifdef __CUDACC__
 

@@ -474,7 +474,7 @@ constexpr int kMfBSmem = mf::kBSize * 4 + mf::kC * kMfTH * kMfTW * 2;
 
 __global__ void __launch_bounds__(kMfBThreads, 1)
 motion_front_b_kernel(const float* __restrict__ x2, const float* __restrict__ wts, __nv_bfloat16* __restrict__ cor,
-                      int H, int W) {
+                      int H, int W, int channels_last) {
   extern __shared__ __align__(16) uint8_t mf_smem[];
   float* sw = reinterpret_cast<float*>(mf_smem);
   __nv_bfloat16* tile = reinterpret_cast<__nv_bfloat16*>(mf_smem + mf::kBSize * 4);
@@ -539,7 +539,9 @@ motion_front_b_kernel(const float* __restrict__ x2, const float* __restrict__ wt
     u[o] = mf_r(mf_gelu(mf_r(mf_r(acc) + sw[mf::kBc + o])));
   }
   // ---- cor = bf16(gelu(ffn2.2(u))), 16 output channels at a time (weights transposed: [c][o])
-  __nv_bfloat16* dst = cor + static_cast<long long>(frame) * mf::kOut * HW + pix;
+  // NCHW (the reference's layout) or channels-last [pixel][256] (operand of the shifted-GEMM convolutions, K5/K7)
+  __nv_bfloat16* dst = channels_last ? cor + (static_cast<long long>(frame) * HW + pix) * mf::kOut
+                                     : cor + static_cast<long long>(frame) * mf::kOut * HW + pix;
   for (int o0 = 0; o0 < mf::kOut; o0 += 16) {
     float acc[16];
     #pragma unroll
@@ -555,9 +557,19 @@ motion_front_b_kernel(const float* __restrict__ x2, const float* __restrict__ wt
       }
     }
     #pragma unroll
-    for (int j = 0; j < 16; ++j) {
-      const float v = mf_r(mf_r(acc[j]) + sw[mf::kBd + o0 + j]);
-      dst[static_cast<long long>(o0 + j) * HW] = __float2bfloat16_rn(mf_gelu(v));   // the encoder's outer F.gelu
+    for (int j = 0; j < 16; ++j)
+      acc[j] = mf_gelu(mf_r(mf_r(acc[j]) + sw[mf::kBd + o0 + j]));                   // the encoder's outer F.gelu
+    if (channels_last) {
+      uint4 v0, v1;
+      v0.x = pack_bf16x2(acc[0], acc[1]); v0.y = pack_bf16x2(acc[2], acc[3]);
+      v0.z = pack_bf16x2(acc[4], acc[5]); v0.w = pack_bf16x2(acc[6], acc[7]);
+      v1.x = pack_bf16x2(acc[8], acc[9]); v1.y = pack_bf16x2(acc[10], acc[11]);
+      v1.z = pack_bf16x2(acc[12], acc[13]); v1.w = pack_bf16x2(acc[14], acc[15]);
+      *reinterpret_cast<uint4*>(dst + o0) = v0;
+      *reinterpret_cast<uint4*>(dst + o0 + 8) = v1;
+    } else {
+      #pragma unroll
+      for (int j = 0; j < 16; ++j) dst[static_cast<long long>(o0 + j) * HW] = __float2bfloat16_rn(acc[j]);
     }
   }
 }
@@ -619,10 +631,11 @@ extern "C" int ppm_corr_lookup_l0(const void* level0, const float* flow, int B, 
 // K6 entry: see the section header above.  level0 / flow as ppm_corr_lookup_l0 (fused lookup), or corr != NULL to start
 // from a materialised (B, 36, H, W1) fp32 lookup result.  weights_a / weights_b: fp32 arrays (bf16-representable values)
 // in the MfA / MfB layouts; x2_ws: B*36*H*W1 floats of scratch; cor: (B, 256, H, W1) bf16.
-extern "C" int ppm_motion_corr_front(const void* level0, const float* flow, const float* corr, const float* weights_a,
-                                     const float* weights_b, int B, int H, int W1, int W2, float* x2_ws, void* cor,
-                                     void* stream) {
-  using namespace ppm;
+namespace ppm {
+// Both K6 kernels; `cor` NCHW (channels_last = 0) or [pixel][256] (channels_last = 1).  Declared in common.cuh.
+int motion_front_launch(const void* level0, const float* flow, const float* corr, const float* weights_a,
+                        const float* weights_b, int B, int H, int W1, int W2, float* x2_ws, void* cor, int channels_last,
+                        cudaStream_t st) {
   PPM_CHECK((corr || (level0 && flow)) && weights_a && weights_b && x2_ws && cor, PPM_ERR_ARG,
             "ppm_motion_corr_front: null pointer");
   PPM_CHECK(B > 0 && H > 0 && W1 > 0 && B <= 65535, PPM_ERR_ARG, "ppm_motion_corr_front: bad shape");
@@ -636,7 +649,6 @@ extern "C" int ppm_motion_corr_front(const void* level0, const float* flow, cons
     a.lk.flow = flow;
   }
   a.corr_in = corr; a.wts = weights_a; a.x2 = x2_ws;
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
   motion_front_a_kernel<<<dim3((a.lk.HW + kLookupThreads - 1) / kLookupThreads, B), kLookupThreads, 0, st>>>(a);
   PPM_CUDA(cudaGetLastError());
   static std::atomic<uint64_t> attr_done{0};
@@ -648,7 +660,16 @@ extern "C" int ppm_motion_corr_front(const void* level0, const float* flow, cons
   }
   PPM_CHECK((H + kMfTileH - 1) / kMfTileH <= 65535, PPM_ERR_UNSUPPORTED, "ppm_motion_corr_front: H too large");
   dim3 grid((W1 + kMfTileW - 1) / kMfTileW, (H + kMfTileH - 1) / kMfTileH, B);
-  motion_front_b_kernel<<<grid, kMfBThreads, kMfBSmem, st>>>(x2_ws, weights_b, static_cast<__nv_bfloat16*>(cor), H, W1);
+  motion_front_b_kernel<<<grid, kMfBThreads, kMfBSmem, st>>>(x2_ws, weights_b, static_cast<__nv_bfloat16*>(cor), H, W1,
+                                                              channels_last);
   PPM_CUDA(cudaGetLastError());
   return PPM_OK;
+}
+}  // namespace ppm
+
+extern "C" int ppm_motion_corr_front(const void* level0, const float* flow, const float* corr, const float* weights_a,
+                                     const float* weights_b, int B, int H, int W1, int W2, float* x2_ws, void* cor,
+                                     void* stream) {
+  return ppm::motion_front_launch(level0, flow, corr, weights_a, weights_b, B, H, W1, W2, x2_ws, cor, 0,
+                                  static_cast<cudaStream_t>(stream));
 }

@@ -62,6 +62,9 @@ struct GruGemmParams {
   void* out;                         // Q (last stage) / RELU / LINEAR: strided (b, C, T, H, W) result, or nullptr:
   long long out_sb, out_sc, out_st;  //   element (bb, ch, t, y, x) at bb*out_sb + ch*out_sc + t*out_st + y*W + x
   float out_scale;                   // LINEAR: results multiplied by this (a power of two: exact) before the store
+  void* out2;                        // RELU / LINEAR: channels >= split_c go here instead (channel index - split_c)
+  long long out2_sb, out2_sc, out2_st;
+  int out2_dtype, split_c;
   int out_dtype;
   int N;                             // GEMM N: 64, 128, 192 or 256 (output channels padded with zero weights)
   int n_valid;                       // RELU / LINEAR: output channels actually stored (<= N)
@@ -334,13 +337,20 @@ gru_gemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constan
                 }
               }
               if (p.out) {
-                const long long cs = p.out_sc;
-                const long long o = bb * p.out_sb + (col0 + g * 8) * p.out_sc + t * p.out_st + static_cast<long long>(y) * p.W + x;
+                const long long sp = static_cast<long long>(y) * p.W + x;
                 #pragma unroll
                 for (int e = 0; e < 8; ++e) {
-                  if (col0 + g * 8 + e < p.n_valid) {
-                    if (p.out_dtype == PPM_BF16) static_cast<__nv_bfloat16*>(p.out)[o + e * cs] = __float2bfloat16_rn(v[e]);
-                    else static_cast<float*>(p.out)[o + e * cs] = v[e];
+                  const int col = col0 + g * 8 + e;
+                  if (col < p.n_valid) {
+                    if (col < p.split_c) {
+                      const long long o = bb * p.out_sb + col * p.out_sc + t * p.out_st + sp;
+                      if (p.out_dtype == PPM_BF16) static_cast<__nv_bfloat16*>(p.out)[o] = __float2bfloat16_rn(v[e]);
+                      else static_cast<float*>(p.out)[o] = v[e];
+                    } else {
+                      const long long o = bb * p.out2_sb + (col - p.split_c) * p.out2_sc + t * p.out2_st + sp;
+                      if (p.out2_dtype == PPM_BF16) static_cast<__nv_bfloat16*>(p.out2)[o] = __float2bfloat16_rn(v[e]);
+                      else static_cast<float*>(p.out2)[o] = v[e];
+                    }
                   }
                 }
               }
@@ -440,6 +450,7 @@ static int gru_launch(const CUtensorMap& a0, const CUtensorMap& a1, const CUtens
     p.out_st = HW; p.out_sc = HW * s.T; p.out_sb = HW * s.T * C;
   }
   if (p.out_scale == 0.f) p.out_scale = 1.f;
+  if (!p.out2) p.split_c = 1 << 30;
   const int smem = kGrStages * (kGrABytes + p.N * 128) + 1024;
   static std::mutex mu;
   static bool attr_done[64] = {};
@@ -713,4 +724,73 @@ extern "C" int ppm_update_block3d(const void* net, int net_dtype, const void* co
     return rc;
   return mask_head_unit(s, Hb, Hd, mask_w1, mask_b1, mask_w2, mask_b2, n_mask, mask_out, PPM_BF16,
                         static_cast<long long>(T) * n_mask * HW, HW, static_cast<long long>(n_mask) * HW, st);
+}
+
+// ------------------------------------------------------------------------------------------------ motion encoder (K7)
+// BasicMotionEncoder_v2.forward (reference models/core/ppmtereo_update.py:458-482) without its two tiny-channel pieces
+// (convf1: 7x7 on the 2 flow channels, init_conv: first iteration only -- both stay on cuDNN):
+//   cor = gelu(convc1(lookup))            K6, written channels-last
+//   cor = relu(convc2(cor))               3x3, 256 -> 192       shifted GEMM, 9 offsets  -> cat[:,   0:192]
+//   flo = relu(convf2(flo1))              3x3, 128 ->  64       (flo1 = relu(convf1(flow)), packed)      -> cat[:, 192:256]
+//   cat[:, 256:320] = motion_hidden_state (packed)              -- torch.cat([cor, flo, mhs]) is never built separately:
+//   out = relu(final_conv(cat))           3x3, 320 -> 190          the three producers write one channels-last buffer
+//   motion_features[:, 0:126] = out[:, :126] (fp32: the reference's cat with the fp32 flow promotes),  mhs = out[:, 126:190]
+extern "C" int ppm_motion_encoder_workspace(int B, int H, int W, size_t* bytes) {
+  PPM_CHECK(B > 0 && H > 0 && W > 0 && bytes, PPM_ERR_ARG, "ppm_motion_encoder_workspace: bad argument");
+  const size_t P = static_cast<size_t>(B) * H * W;
+  *bytes = P * (36 * 4 + (256 + 128 + 320) * 2);          // x2 (fp32), cor, flo1, cat (bf16 channels-last)
+  return PPM_OK;
+}
+
+extern "C" int ppm_motion_encoder(const void* level0, const float* flow, const float* corr, int W2, const float* front_a,
+                                  const float* front_b, const void* flo1, int flo1_dtype, const void* mhs, int mhs_dtype,
+                                  const void* wc2, const float* bc2, const void* wf2, const float* bf2, const void* wfin,
+                                  const float* bfin, int B, int H, int W, void* workspace, size_t workspace_bytes,
+                                  float* motion_features, void* mhs_out, void* stream) {
+  using namespace ppm;
+  PPM_CHECK(flo1 && mhs && wc2 && bc2 && wf2 && bf2 && wfin && bfin && workspace && motion_features && mhs_out, PPM_ERR_ARG,
+            "ppm_motion_encoder: null pointer");
+  PPM_CHECK(B > 0 && H > 0 && W > 0 && B <= 65535, PPM_ERR_ARG, "ppm_motion_encoder: bad shape");
+  PPM_CHECK((flo1_dtype == PPM_F32 || flo1_dtype == PPM_BF16) && (mhs_dtype == PPM_F32 || mhs_dtype == PPM_BF16), PPM_ERR_ARG,
+            "ppm_motion_encoder: bad dtype");
+  size_t need = 0;
+  ppm_motion_encoder_workspace(B, H, W, &need);
+  PPM_CHECK(workspace_bytes >= need, PPM_ERR_ARG, "ppm_motion_encoder: workspace of %zu bytes < %zu needed", workspace_bytes, need);
+  PPM_CHECK((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, PPM_ERR_ARG, "ppm_motion_encoder: workspace must be 256-byte aligned");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const GruShape s = gru_shape(1, B, H, W);                 // B frames of one "batch": 2-D convolutions, kt = 1
+  const long long HW = static_cast<long long>(H) * W;
+  __nv_bfloat16* cor = static_cast<__nv_bfloat16*>(workspace);
+  __nv_bfloat16* flo = cor + s.P * 256;
+  __nv_bfloat16* cat = flo + s.P * 128;
+  float* x2 = reinterpret_cast<float*>(cat + s.P * 320);
+  int rc;
+  if ((rc = motion_front_launch(level0, flow, corr, front_a, front_b, B, H, W, W2, x2, cor, 1, st))) return rc;
+  // frame-major (B, C, H, W) seen as (1, C, B, H, W): sc = HW, st = C*HW
+  if (flo1_dtype == PPM_BF16) rc = gru_pack<__nv_bfloat16>(flo1, 0, HW, 128 * HW, s, 128, 128, 0, flo, nullptr, st);
+  else rc = gru_pack<float>(flo1, 0, HW, 128 * HW, s, 128, 128, 0, flo, nullptr, st);
+  if (rc) return rc;
+  if (mhs_dtype == PPM_BF16) rc = gru_pack<__nv_bfloat16>(mhs, 0, HW, 64 * HW, s, 64, 320, 256, cat, nullptr, st);
+  else rc = gru_pack<float>(mhs, 0, HW, 64 * HW, s, 64, 320, 256, cat, nullptr, st);
+  if (rc) return rc;
+  CUtensorMap mCor, mFlo, mCat, mW;
+  if ((rc = gru_act_map(&mCor, cor, 256, s))) return rc;
+  if ((rc = gru_act_map(&mFlo, flo, 128, s))) return rc;
+  if ((rc = gru_act_map(&mCat, cat, 320, s))) return rc;
+  GruGemmParams p{};
+  p.kw = 3; p.kh = 3; p.kt = 1; p.mode = GR_EPI_RELU; p.seg0_c0 = 0; p.seg1_chunks = 0; p.dst0 = cat; p.dst_ld = 320;
+  // convc2: 256 -> 192
+  if ((rc = gru_w_map(&mW, wc2, 256, 192, 9))) return rc;
+  p.bias = bc2; p.N = 192; p.n_valid = 192; p.seg0_chunks = 4; p.dst_c0 = 0;
+  if ((rc = gru_launch(mCor, mCor, mW, p, s, st))) return rc;
+  // convf2: 128 -> 64
+  if ((rc = gru_w_map(&mW, wf2, 128, 64, 9))) return rc;
+  p.bias = bf2; p.N = 64; p.n_valid = 64; p.seg0_chunks = 2; p.dst_c0 = 192;
+  if ((rc = gru_launch(mFlo, mFlo, mW, p, s, st))) return rc;
+  // final_conv: 320 -> 190, split into motion_features[:, :126] (fp32) and the new hidden state (bf16)
+  if ((rc = gru_w_map(&mW, wfin, 320, 192, 9))) return rc;
+  p.bias = bfin; p.N = 192; p.n_valid = 190; p.seg0_chunks = 5; p.dst0 = nullptr;
+  p.out = motion_features; p.out_dtype = PPM_F32; p.out_sb = 0; p.out_sc = HW; p.out_st = 128 * HW;
+  p.out2 = mhs_out; p.out2_dtype = PPM_BF16; p.out2_sb = 0; p.out2_sc = HW; p.out2_st = 64 * HW; p.split_c = 126;
+  return gru_launch(mCat, mCat, mW, p, s, st);
 }

@@ -107,20 +107,119 @@ class MotionCorrFront:
         return out
 
 
+def _pack3x3(conv, n_pad: int):
+    w = conv.weight.detach()
+    co, ci = w.shape[:2]
+    out = torch.zeros(9, n_pad, ci, dtype=torch.bfloat16, device=w.device)
+    out[:, :co] = w.reshape(co, ci, 9).permute(2, 0, 1).to(torch.bfloat16)            # (tap = ih*3 + iw, Cout, Cin)
+    b = torch.zeros(n_pad, device=w.device)
+    b[:co] = _b16(conv.bias)
+    return out.contiguous(), b
+
+
+class MotionEncoder:
+    """``BasicMotionEncoder_v2.forward`` (models/core/ppmtereo_update.py:458-482) as one C-ABI call
+    (``ppm_motion_encoder``, K7) plus the two tiny-channel convolutions left on cuDNN (convf1, and init_conv on the
+    first iteration)."""
+
+    def __init__(self, encoder):
+        self.m = encoder
+        self.front = MotionCorrFront(encoder.convc1)
+        self.lib = self.front.lib
+        self._versions = None
+        self._ws: Dict[Tuple, torch.Tensor] = {}
+
+    def supported(self) -> bool:
+        m = self.m
+        try:
+            return (self.front.supported() and tuple(m.convc2.weight.shape) == (192, 256, 3, 3)
+                    and tuple(m.convf2.weight.shape) == (64, 128, 3, 3)
+                    and tuple(m.final_conv.weight.shape) == (190, 320, 3, 3) and m.convf1.weight.shape[0] == 128)
+        except AttributeError:
+            return False
+
+    def _params(self):
+        m = self.m
+        convs = (m.convc2, m.convf2, m.final_conv)
+        versions = tuple((c.weight._version, c.weight.data_ptr(), c.bias._version, c.bias.data_ptr()) for c in convs)
+        if versions != self._versions:
+            self.wc2, self.bc2 = _pack3x3(m.convc2, 192)
+            self.wf2, self.bf2 = _pack3x3(m.convf2, 64)
+            self.wfin, self.bfin = _pack3x3(m.final_conv, 192)
+            self._versions = versions
+
+    def __call__(self, flow, corr, motion_hidden_state, inp):
+        import ctypes
+        m = self.m
+        if motion_hidden_state is None:
+            motion_hidden_state = m.init_conv(inp)
+        wa, wb = self.front._params()
+        self._params()
+        flow32 = flow.detach().float().contiguous()
+        level0 = corr_ptr = lk_flow = None
+        W2 = 0
+        keep = None
+        if isinstance(corr, LookupRequest):
+            blk = corr.block
+            if getattr(blk, "_l0_only", False):
+                keep = blk._level0
+                level0, W2 = keep.data_ptr(), blk._w2
+                lk_flow = flow32 if corr.flow is flow else corr.flow.detach().float().contiguous()
+            else:
+                corr = corr.materialise()
+        if level0 is None:
+            if not corr.is_cuda or corr.dim() != 4 or corr.shape[1] != 36:
+                raise RuntimeError(f"corr must be a CUDA tensor (B, 36, h, w), got {tuple(corr.shape)}")
+            keep = corr.float().contiguous()
+            corr_ptr = keep.data_ptr()
+        B, _, H, W = flow32.shape
+        flo1 = F.relu(m.convf1(flow)).contiguous()
+        mhs = motion_hidden_state
+        if mhs.dtype not in (torch.float32, torch.bfloat16):
+            mhs = mhs.float()
+        mhs = mhs.contiguous()
+        if tuple(mhs.shape) != (B, 64, H, W):
+            raise RuntimeError(f"motion_hidden_state must be ({B}, 64, {H}, {W}), got {tuple(mhs.shape)}")
+        dev = flow32.device
+        key = (B, H, W, dev)
+        ws = self._ws.get(key)
+        if ws is None:
+            n = ctypes.c_size_t()
+            _lib.check(self.lib.ppm_motion_encoder_workspace(B, H, W, ctypes.byref(n)), "ppm_motion_encoder_workspace")
+            self._ws.clear()
+            ws = self._ws[key] = torch.empty(n.value, dtype=torch.uint8, device=dev)
+        feat = torch.empty(B, 128, H, W, dtype=torch.float32, device=dev)
+        mhs_out = torch.empty(B, 64, H, W, dtype=torch.bfloat16, device=dev)
+        _lib.check(self.lib.ppm_motion_encoder(level0, lk_flow.data_ptr() if lk_flow is not None else None, corr_ptr, W2,
+                                               wa.data_ptr(), wb.data_ptr(), flo1.data_ptr(), _lib.dtype_code(flo1),
+                                               mhs.data_ptr(), _lib.dtype_code(mhs), self.wc2.data_ptr(),
+                                               self.bc2.data_ptr(), self.wf2.data_ptr(), self.bf2.data_ptr(),
+                                               self.wfin.data_ptr(), self.bfin.data_ptr(), B, H, W, ws.data_ptr(),
+                                               ws.numel(), feat.data_ptr(), mhs_out.data_ptr(), _lib.stream_ptr()),
+                   "ppm_motion_encoder")
+        feat[:, 126:] = flow32
+        return feat, mhs_out
+
+
 def _kernel_regime(t: torch.Tensor) -> bool:
     return (t.is_cuda and torch.is_autocast_enabled() and torch.get_autocast_gpu_dtype() == torch.bfloat16
             and not torch.is_grad_enabled())
 
 
 def encoder_forward(self, flow, corr, motion_hidden_state, inp):
-    """Replacement for ``BasicMotionEncoder_v2.forward`` (models/core/ppmtereo_update.py:458-482): identical, except that
-    ``F.gelu(self.convc1(corr))`` is one fused call in the bf16 autocast regime; ``corr`` may be a LookupRequest."""
+    """Replacement for ``BasicMotionEncoder_v2.forward`` (models/core/ppmtereo_update.py:458-482): one ``ppm_motion_encoder``
+    call (K7) in the bf16 autocast regime with an fp32 flow; otherwise the reference's lines with
+    ``F.gelu(self.convc1(corr))`` fused (K6) where that applies.  ``corr`` may be a LookupRequest."""
+    enc = self.__dict__.get(_ATTR)
+    if enc is None:
+        enc = self.__dict__[_ATTR] = MotionEncoder(self)
+    regime = _kernel_regime(flow)
+    if regime and flow.dtype == torch.float32 and enc.supported():
+        return enc(flow, corr, motion_hidden_state, inp)
+    front = enc.front
     if motion_hidden_state is None:
         motion_hidden_state = self.init_conv(inp)
-    front = self.__dict__.get(_ATTR)
-    if front is None:
-        front = self.__dict__[_ATTR] = MotionCorrFront(self.convc1)
-    if _kernel_regime(flow) and front.supported():
+    if regime and front.supported():
         cor = front(corr)
     else:
         if isinstance(corr, LookupRequest):

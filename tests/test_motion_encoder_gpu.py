@@ -1,0 +1,180 @@
+"""K7: BasicMotionEncoder_v2.forward as one call (ppm_motion_encoder) -- against the reference's module run by torch /
+cuDNN under bf16 autocast on the same GPU (staged sources), against the CPU oracle's bf16-mode restatement, fused lookup
+vs materialised lookup, the first-iteration path (motion_hidden_state None -> init_conv), and the installed class.
+
+Tolerances: the three 3x3 convolutions accumulate 2304 / 1152 / 2880 products in fp32 in another order than cuDNN; a
+result that falls on the other side of a bf16 rounding boundary differs by one bf16 ulp (2^-8 relative) and such flips
+feed the next convolution.  The bars are the ones the K5 / K5b tests use for the same kernel: >= 93 % of all outputs
+bit-identical, max |diff| <= 2^-6 of the tensor's scale, mean |diff| <= 2e-4 of it."""
+import importlib
+
+import pytest
+import torch
+
+from oracle import ppm_oracle as O
+from oracle import ref_import
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def env():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    if not ref_import.available():
+        pytest.skip("reference sources not staged")
+    import ppmstereo_b200 as P
+    ref_import.load_reference()
+    upd = importlib.import_module("models.core.ppmtereo_update")
+    torch.manual_seed(11)
+    enc = upd.BasicMotionEncoder_v2(36).cuda().eval()
+    return P, enc, upd
+
+
+def _inputs(B, H, W, seed):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    flow = torch.randn(B, 2, H, W, generator=g, device="cuda") * 4
+    corr = torch.randn(B, 36, H, W, generator=g, device="cuda") * 2
+    mhs = torch.randn(B, 64, H, W, generator=g, device="cuda").bfloat16()
+    inp = torch.randn(B, 128, H, W, generator=g, device="cuda")
+    return flow, corr, mhs, inp
+
+
+def _compare(tag, got, want, min_same=0.93):
+    assert got.shape == want.shape and got.dtype == want.dtype, (tag, got.shape, want.shape, got.dtype, want.dtype)
+    d = (got.float() - want.float()).abs()
+    scale = max(1.0, float(want.float().abs().max()))
+    same = float((got == want).float().mean())
+    print(f"K7 {tag}: {same * 100:.2f} % bit-identical to torch/cuDNN, max |diff| {float(d.max()):.4f} of {scale:.2f}, mean {float(d.mean()):.2e}")
+    assert float(d.max()) <= 2.0 ** -6 * scale
+    assert float(d.mean()) <= 2e-4 * scale
+    assert same >= min_same
+
+
+@pytest.mark.parametrize("shape", [(1, 5, 7), (2, 16, 32), (3, 23, 40), (2, 46, 80), (20, 92, 160)])
+def test_vs_reference_module_under_autocast(env, shape):
+    P, enc, _ = env
+    flow, corr, mhs, inp = _inputs(*shape, seed=sum(shape))
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        want_f, want_h = enc(flow, corr, mhs, inp)
+        got_f, got_h = P.MotionEncoder(enc)(flow, corr, mhs, inp)
+    assert want_f.dtype == torch.float32 and want_h.dtype == torch.bfloat16
+    _compare(f"{shape} features", got_f[:, :126], want_f[:, :126])
+    _compare(f"{shape} hidden", got_h, want_h.contiguous())
+    assert torch.equal(got_f[:, 126:], flow)
+
+
+def test_first_iteration_runs_init_conv(env):
+    P, enc, _ = env
+    flow, corr, _, inp = _inputs(2, 23, 40, seed=3)
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        want_f, want_h = enc(flow, corr, None, inp)
+        got_f, got_h = P.MotionEncoder(enc)(flow, corr, None, inp)
+    _compare("first iteration features", got_f[:, :126], want_f[:, :126])
+    _compare("first iteration hidden", got_h, want_h.contiguous())
+
+
+def test_vs_cpu_oracle_bf16_mode(env):
+    P, enc, _ = env
+    flow, corr, mhs, inp = _inputs(2, 9, 13, seed=1)
+    params = {k: v.detach().float().cpu() for k, v in enc.state_dict().items()}
+    want_f, want_h = O.motion_encoder(flow.cpu(), corr.cpu(), mhs.float().cpu(), params, mode="bf16")
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        got_f, got_h = P.MotionEncoder(enc)(flow, corr, mhs, inp)
+    for got, want in ((got_f.cpu(), want_f), (got_h.float().cpu(), want_h)):
+        d = (got - want).abs()
+        scale = max(1.0, float(want.abs().max()))
+        assert float(d.max()) <= 2.0 ** -6 * scale and float(d.mean()) <= 2e-4 * scale
+        assert float((d == 0).float().mean()) >= 0.93
+
+
+@pytest.mark.parametrize("shape", [(2, 256, 6, 64), (3, 256, 23, 40)])
+def test_fused_lookup_equals_materialised_lookup(env, shape):
+    P, enc, _ = env
+    B, D, H, W = shape
+    g = torch.Generator(device="cuda").manual_seed(W)
+    f1 = torch.randn(B, D, H, W, generator=g, device="cuda").bfloat16()
+    f2 = torch.randn(B, D, H, W, generator=g, device="cuda").bfloat16()
+    flow = torch.zeros(B, 2, H, W, device="cuda")
+    flow[:, 0] = torch.rand(B, H, W, generator=g, device="cuda") * -(W * 0.6) + 8.0
+    mhs = torch.randn(B, 64, H, W, generator=g, device="cuda").bfloat16()
+    blk = P.CorrBlock1D(f1, f2)
+    assert blk._l0_only
+    impl = P.MotionEncoder(enc)
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        a_f, a_h = impl(flow, P.LookupRequest(blk, flow), mhs, None)
+        b_f, b_h = impl(flow, blk(flow), mhs, None)
+    assert torch.equal(a_f, b_f) and torch.equal(a_h, b_h)
+
+
+def test_installed_class_forward_and_fallback(env):
+    """install() puts encoder_forward on the class: the kernel in the bf16 autocast / no-grad regime, the reference's
+    own lines otherwise (fp32: must equal the untouched module exactly)."""
+    P, enc, upd = env
+    inst = importlib.import_module("ppmstereo_b200.install")
+    flow, corr, mhs, inp = _inputs(2, 16, 32, seed=9)
+    with torch.no_grad():
+        want32 = enc(flow, corr, mhs.float(), inp)
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            want16 = enc(flow, corr, mhs, inp)
+    ppm = importlib.import_module("models.core.ppmstereo")
+    P.install(ppm)
+    try:
+        assert hasattr(upd.BasicMotionEncoder_v2, "_ppm_reference_forward")
+        with torch.no_grad():
+            got32 = enc(flow, corr, mhs.float(), inp)
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                got16 = enc(flow, corr, mhs, inp)
+    finally:
+        P.uninstall(ppm)
+    assert not hasattr(upd.BasicMotionEncoder_v2, "_ppm_reference_forward")
+    assert torch.equal(got32[0], want32[0]) and torch.equal(got32[1], want32[1])
+    _compare("installed features", got16[0], want16[0])
+    _compare("installed hidden", got16[1], want16[1].contiguous())
+    assert inst is not None
+
+
+def test_no_write_outside_outputs(env):
+    """Guard bands around both outputs and the workspace survive a call (compute-sanitizer is closed on this pool)."""
+    P, enc, _ = env
+    import ctypes
+    from ppmstereo_b200 import _lib
+    B, H, W = 2, 13, 21
+    flow, corr, mhs, inp = _inputs(B, H, W, seed=4)
+    impl = P.MotionEncoder(enc)
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        want_f, want_h = impl(flow, corr, mhs, inp)
+        flo1 = torch.relu(enc.convf1(flow)).contiguous()
+    n = ctypes.c_size_t()
+    _lib.check(impl.lib.ppm_motion_encoder_workspace(B, H, W, ctypes.byref(n)), "ws")
+    G = 4096
+    ws = torch.full((n.value + 2 * G,), 0x5A, dtype=torch.uint8, device="cuda")
+    feat = torch.full((B * 128 * H * W + 2 * G,), -77.0, device="cuda")
+    hid = torch.full((B * 64 * H * W + 2 * G,), -77.0, device="cuda").bfloat16()
+    wa, wb = impl.front._params()
+    c32 = corr.float().contiguous()
+    _lib.check(impl.lib.ppm_motion_encoder(None, None, c32.data_ptr(), 0, wa.data_ptr(), wb.data_ptr(), flo1.data_ptr(),
+                                           _lib.dtype_code(flo1), mhs.data_ptr(), _lib.dtype_code(mhs),
+                                           impl.wc2.data_ptr(), impl.bc2.data_ptr(), impl.wf2.data_ptr(),
+                                           impl.bf2.data_ptr(), impl.wfin.data_ptr(), impl.bfin.data_ptr(), B, H, W,
+                                           ws.data_ptr() + G, n.value, feat.data_ptr() + G * 4, hid.data_ptr() + G * 2,
+                                           _lib.stream_ptr()), "ppm_motion_encoder")
+    torch.cuda.synchronize()
+    assert bool((ws[:G] == 0x5A).all()) and bool((ws[-G:] == 0x5A).all())
+    assert bool((feat[:G] == -77.0).all()) and bool((feat[-G:] == -77.0).all())
+    assert bool((hid[:G] == -77.0).all()) and bool((hid[-G:] == -77.0).all())
+    body = feat[G:-G].view(B, 128, H, W)
+    assert torch.equal(body[:, :126], want_f[:, :126])
+    assert bool((body[:, 126:] == -77.0).all())                 # the flow channels are the caller's to fill
+    assert torch.equal(hid[G:-G].view(B, 64, H, W), want_h)
+
+
+def test_rejects_bad_arguments(env):
+    P, enc, _ = env
+    lib = P.MotionEncoder(enc).lib
+    buf = torch.zeros(1024, device="cuda")
+    p = buf.data_ptr()
+    rc = lib.ppm_motion_encoder(None, None, p, 0, p, p, p, 0, p, 0, p, p, p, p, p, p, 1, 4, 4, p, 16, p, p, None)
+    assert rc != 0 and "workspace" in lib.ppm_last_error().decode()
+    rc = lib.ppm_motion_encoder(None, None, p, 0, p, p, None, 0, p, 0, p, p, p, p, p, p, 1, 4, 4, p, 1 << 20, p, p, None)
+    assert rc != 0 and "null" in lib.ppm_last_error().decode()

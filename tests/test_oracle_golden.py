@@ -157,3 +157,27 @@ def test_motion_corr_front_oracle_matches_reference_module():
     assert float((got - want).abs().max()) <= 2e-6
     lo = O.motion_corr_front(corr, dict(pc.state_dict()), mode="bf16")
     assert float((lo - want).abs().max()) <= 3e-2 * float(want.abs().max())
+
+
+def test_motion_encoder_oracle_matches_reference_module():
+    import importlib
+    from oracle import ref_import
+    if not ref_import.available():
+        pytest.skip("reference tree not present")
+    ref_import.load_reference()
+    upd = importlib.import_module("models.core.ppmtereo_update")
+    torch.manual_seed(4)
+    enc = upd.BasicMotionEncoder_v2(36).eval()
+    g = torch.Generator().manual_seed(5)
+    flow = torch.randn(2, 2, 7, 11, generator=g) * 3
+    corr = torch.randn(2, 36, 7, 11, generator=g) * 2
+    mhs = torch.randn(2, 64, 7, 11, generator=g)
+    with torch.no_grad():
+        want_f, want_h = enc(flow, corr, mhs, None)
+    got_f, got_h = O.motion_encoder(flow, corr, mhs, dict(enc.state_dict()))
+    assert got_f.shape == want_f.shape == (2, 128, 7, 11) and got_h.shape == want_h.shape == (2, 64, 7, 11)
+    assert float((got_f - want_f).abs().max()) <= 5e-6 and float((got_h - want_h).abs().max()) <= 5e-6
+    assert torch.equal(got_f[:, 126:], flow)
+    lo_f, lo_h = O.motion_encoder(flow, corr, mhs, dict(enc.state_dict()), mode="bf16")
+    assert float((lo_f - want_f).abs().max()) <= 3e-2 * float(want_f.abs().max())
+    assert float((lo_h - want_h).abs().max()) <= 3e-2 * max(1.0, float(want_h.abs().max()))
