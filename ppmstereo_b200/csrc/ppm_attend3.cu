@@ -470,14 +470,16 @@ struct MapKey { const void* base; int hw, frames, kind, dev; };
 struct MapEntry { MapKey k; CUtensorMap m; };
 constexpr int kMapCache = 16;
 
-static int cached_map(const CUtensorMap** out, const void* base, int hw, int frames, int kind) {
+// The map is COPIED out: a later call may overwrite the slot (round-robin), so a pointer into the cache taken for Q' could
+// silently become the map of V when V misses while Q' hits -- seen as a rare ~1e-3 px deviation of one attention call.
+static int cached_map(CUtensorMap* out, const void* base, int hw, int frames, int kind) {
   static thread_local MapEntry cache[kMapCache];
   static thread_local int n_used = 0, next = 0;
   int dev = 0;
   PPM_CUDA(cudaGetDevice(&dev));
   for (int i = 0; i < n_used; ++i) {
     const MapKey& k = cache[i].k;
-    if (k.base == base && k.hw == hw && k.frames == frames && k.kind == kind && k.dev == dev) { *out = &cache[i].m; return PPM_OK; }
+    if (k.base == base && k.hw == hw && k.frames == frames && k.kind == kind && k.dev == dev) { *out = cache[i].m; return PPM_OK; }
   }
   MapEntry& e = cache[next];
   const uint32_t box[3] = {64, 128, 1};
@@ -494,7 +496,7 @@ static int cached_map(const CUtensorMap** out, const void* base, int hw, int fra
   }
   if (rc) { e.k = MapKey{nullptr, 0, 0, -1, -1}; return rc; }
   e.k = MapKey{base, hw, frames, kind, dev};
-  *out = &e.m;
+  *out = e.m;
   if (n_used < kMapCache) ++n_used;
   next = (next + 1) % kMapCache;
   return PPM_OK;
@@ -522,7 +524,7 @@ extern "C" int ppm_memory_attend_band(const void* Q, const void* K, const void* 
   PPM_CHECK(b * T <= 65535, PPM_ERR_UNSUPPORTED, "ppm_memory_attend: b*T > 65535");
   PPM_CHECK(((reinterpret_cast<uintptr_t>(Q) | reinterpret_cast<uintptr_t>(K) | reinterpret_cast<uintptr_t>(V)) & 15) == 0,
             PPM_ERR_ARG, "ppm_memory_attend: packed operands must be 16-byte aligned");
-  const CUtensorMap *mq, *mk, *mv;
+  CUtensorMap mq, mk, mv;
   if (int rc = cached_map(&mq, Q, hw, b * T, 0)) return rc;
   if (int rc = cached_map(&mk, K, hw, b * T * Kp, 1)) return rc;
   if (int rc = cached_map(&mv, V, hw, b * T, 2)) return rc;
@@ -534,6 +536,6 @@ extern "C" int ppm_memory_attend_band(const void* Q, const void* K, const void* 
   p.q_begin = q_begin; p.q_end = q_begin + q_count;
   const int n_qtiles = (q_count + 2 * kA3Tile - 1) / (2 * kA3Tile);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (mf_dtype == PPM_BF16) return launch_attend3<0, __nv_bfloat16>(*mq, *mk, *mv, p, n_qtiles, b * T, st);
-  return launch_attend3<0, float>(*mq, *mk, *mv, p, n_qtiles, b * T, st);
+  if (mf_dtype == PPM_BF16) return launch_attend3<0, __nv_bfloat16>(mq, mk, mv, p, n_qtiles, b * T, st);
+  return launch_attend3<0, float>(mq, mk, mv, p, n_qtiles, b * T, st);
 }

@@ -311,6 +311,31 @@ def test_frame_major_bf16_value_is_used_in_place(P, shape):
     assert torch.equal(outs[0][0], outs[1][0])
 
 
+def test_value_operand_at_many_addresses_with_resident_query_and_key(P):
+    """Regression: the library keeps the TMA descriptors of recent operands in a 16-slot round-robin cache.  A value
+    operand at a NEW address (every to_v output inside a fresh CUDA-graph pool, every allocator miss) with the query
+    and key operands still cached used to overwrite the slot the query's (or key's) descriptor had just been taken
+    from -- that one attention call then ran with the value's descriptor in the query's place.  40 in-place value
+    tensors at 40 addresses, same contents: every result must equal the first bit for bit."""
+    b, T, h, w = 1, 6, 8, 16
+    t = make_case(b, T, h, w, seed=77)
+    beta = torch.tensor([0.5], device="cuda")
+    mem = P.PPMMemory(t["query"].cuda(), t["key"].cuda(), None, top_k=5)
+    mem.pick(t["sim"].cuda(), t["strive_before"].clone().cuda(), t["uncertainty"].cuda())
+    mf = t["motion_features"].cuda()
+    src = torch.randn(b * T, 128, h, w, generator=torch.Generator().manual_seed(3)).bfloat16().cuda()
+    values = [src.clone() for _ in range(40)]                                   # all alive: 40 distinct addresses
+    assert len({v.data_ptr() for v in values}) == 40
+    outs = []
+    for v in values:
+        mem.pack_kv(v.reshape(b, T, 128, h, w).permute(0, 2, 1, 3, 4))
+        assert mem.v_packed.data_ptr() == v.data_ptr()                          # used in place: the address is the operand's
+        outs.append(mem.aggregate(mf, beta))
+    torch.cuda.synchronize()
+    bad = [i for i, o in enumerate(outs) if not torch.equal(o, outs[0])]
+    assert not bad, f"attention calls {bad} differ from call 0"
+
+
 # ------------------------------------------------------------------------------------------------------------
 # The reference's GPU dtype flow (bf16 autocast, ppmstereo.py:617), pinned against the reference's LITERAL torch op
 # sequence executed by torch on the GPU under autocast -- needs no reference code, only torch.  What is pinned:
