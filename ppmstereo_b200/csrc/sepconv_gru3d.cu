@@ -129,6 +129,36 @@ __global__ void __launch_bounds__(256) gru_pack_kernel(const SrcT* __restrict__ 
   }
 }
 
+// 7 x 7 neighbourhood of the two flow channels as a K-major GEMM operand: row p = pixel, column k = c*49 + ih*7 + iw
+// (the order of Conv2d.weight.reshape(Cout, 98)), columns 98..127 zero; values bf16(flow) (autocast's cast of the conv
+// input), zero outside the image (the conv's padding).  One thread = one pixel x 8 columns (a 16-byte store).
+__global__ void __launch_bounds__(256) flow_im2col_kernel(const float* __restrict__ flow, int H, int W, long long P,
+                                                          __nv_bfloat16* __restrict__ dst) {
+  const long long i = static_cast<long long>(blockIdx.x) * 256 + threadIdx.x;
+  const long long pix = i >> 4;
+  if (pix >= P) return;
+  const int g = static_cast<int>(i & 15);
+  const int HW = H * W;
+  const int frame = static_cast<int>(pix / HW), r = static_cast<int>(pix - static_cast<long long>(frame) * HW);
+  const int y = r / W, x = r - y * W;
+  const float* f = flow + static_cast<long long>(frame) * 2 * HW;
+  float v[8];
+  #pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    const int k = g * 8 + e;
+    float val = 0.f;
+    if (k < 98) {
+      const int c = k >= 49, kk = k - c * 49, ih = kk / 7, iw = kk - ih * 7;
+      const int yy = y + ih - 3, xx = x + iw - 3;
+      if (yy >= 0 && yy < H && xx >= 0 && xx < W) val = __ldg(f + c * HW + yy * W + xx);
+    }
+    v[e] = val;
+  }
+  uint4 o;
+  o.x = pack_bf16x2(v[0], v[1]); o.y = pack_bf16x2(v[2], v[3]); o.z = pack_bf16x2(v[4], v[5]); o.w = pack_bf16x2(v[6], v[7]);
+  *reinterpret_cast<uint4*>(dst + pix * 128 + g * 8) = o;
+}
+
 // ------------------------------------------------------------------------------------------------ epilogue math
 // fp32 evaluation + one rounding, as torch's CUDA elementwise kernels do for bf16 tensors (opmath = float).
 __device__ __forceinline__ float gr_gelu(float x) { return 0.5f * x * (1.f + erff(x * 0.70710678118654752440f)); }
@@ -727,11 +757,12 @@ extern "C" int ppm_update_block3d(const void* net, int net_dtype, const void* co
 }
 
 // ------------------------------------------------------------------------------------------------ motion encoder (K7)
-// BasicMotionEncoder_v2.forward (reference models/core/ppmtereo_update.py:458-482) without its two tiny-channel pieces
-// (convf1: 7x7 on the 2 flow channels, init_conv: first iteration only -- both stay on cuDNN):
+// BasicMotionEncoder_v2.forward (reference models/core/ppmtereo_update.py:458-482) with motion_hidden_state given
+// (init_conv, first iteration only, stays with the caller):
+//   flo1 = relu(convf1(flow))             7x7, 2 -> 128         im2col pack + one K = 128 GEMM
 //   cor = gelu(convc1(lookup))            K6, written channels-last
 //   cor = relu(convc2(cor))               3x3, 256 -> 192       shifted GEMM, 9 offsets  -> cat[:,   0:192]
-//   flo = relu(convf2(flo1))              3x3, 128 ->  64       (flo1 = relu(convf1(flow)), packed)      -> cat[:, 192:256]
+//   flo = relu(convf2(flo1))              3x3, 128 ->  64       -> cat[:, 192:256]
 //   cat[:, 256:320] = motion_hidden_state (packed)              -- torch.cat([cor, flo, mhs]) is never built separately:
 //   out = relu(final_conv(cat))           3x3, 320 -> 190          the three producers write one channels-last buffer
 //   motion_features[:, 0:126] = out[:, :126] (fp32: the reference's cat with the fp32 flow promotes),  mhs = out[:, 126:190]
@@ -743,16 +774,15 @@ extern "C" int ppm_motion_encoder_workspace(int B, int H, int W, size_t* bytes) 
 }
 
 extern "C" int ppm_motion_encoder(const void* level0, const float* flow, const float* corr, int W2, const float* front_a,
-                                  const float* front_b, const void* flo1, int flo1_dtype, const void* mhs, int mhs_dtype,
+                                  const float* front_b, const void* wf1, const float* bf1, const void* mhs, int mhs_dtype,
                                   const void* wc2, const float* bc2, const void* wf2, const float* bf2, const void* wfin,
                                   const float* bfin, int B, int H, int W, void* workspace, size_t workspace_bytes,
                                   float* motion_features, void* mhs_out, void* stream) {
   using namespace ppm;
-  PPM_CHECK(flo1 && mhs && wc2 && bc2 && wf2 && bf2 && wfin && bfin && workspace && motion_features && mhs_out, PPM_ERR_ARG,
-            "ppm_motion_encoder: null pointer");
+  PPM_CHECK(flow && wf1 && bf1 && mhs && wc2 && bc2 && wf2 && bf2 && wfin && bfin && workspace && motion_features && mhs_out,
+            PPM_ERR_ARG, "ppm_motion_encoder: null pointer");
   PPM_CHECK(B > 0 && H > 0 && W > 0 && B <= 65535, PPM_ERR_ARG, "ppm_motion_encoder: bad shape");
-  PPM_CHECK((flo1_dtype == PPM_F32 || flo1_dtype == PPM_BF16) && (mhs_dtype == PPM_F32 || mhs_dtype == PPM_BF16), PPM_ERR_ARG,
-            "ppm_motion_encoder: bad dtype");
+  PPM_CHECK(mhs_dtype == PPM_F32 || mhs_dtype == PPM_BF16, PPM_ERR_ARG, "ppm_motion_encoder: bad dtype");
   size_t need = 0;
   ppm_motion_encoder_workspace(B, H, W, &need);
   PPM_CHECK(workspace_bytes >= need, PPM_ERR_ARG, "ppm_motion_encoder: workspace of %zu bytes < %zu needed", workspace_bytes, need);
@@ -764,29 +794,39 @@ extern "C" int ppm_motion_encoder(const void* level0, const float* flow, const f
   __nv_bfloat16* flo = cor + s.P * 256;
   __nv_bfloat16* cat = flo + s.P * 128;
   float* x2 = reinterpret_cast<float*>(cat + s.P * 320);
+  __nv_bfloat16* col = cor;                                 // the flow branch runs first: its im2col operand borrows cor
   int rc;
-  if ((rc = motion_front_launch(level0, flow, corr, front_a, front_b, B, H, W, W2, x2, cor, 1, st))) return rc;
-  // frame-major (B, C, H, W) seen as (1, C, B, H, W): sc = HW, st = C*HW
-  if (flo1_dtype == PPM_BF16) rc = gru_pack<__nv_bfloat16>(flo1, 0, HW, 128 * HW, s, 128, 128, 0, flo, nullptr, st);
-  else rc = gru_pack<float>(flo1, 0, HW, 128 * HW, s, 128, 128, 0, flo, nullptr, st);
-  if (rc) return rc;
-  if (mhs_dtype == PPM_BF16) rc = gru_pack<__nv_bfloat16>(mhs, 0, HW, 64 * HW, s, 64, 320, 256, cat, nullptr, st);
-  else rc = gru_pack<float>(mhs, 0, HW, 64 * HW, s, 64, 320, 256, cat, nullptr, st);
-  if (rc) return rc;
-  CUtensorMap mCor, mFlo, mCat, mW;
+  CUtensorMap mCor, mFlo, mCat, mCol, mW;
   if ((rc = gru_act_map(&mCor, cor, 256, s))) return rc;
   if ((rc = gru_act_map(&mFlo, flo, 128, s))) return rc;
   if ((rc = gru_act_map(&mCat, cat, 320, s))) return rc;
+  if ((rc = gru_act_map(&mCol, col, 128, s))) return rc;
   GruGemmParams p{};
-  p.kw = 3; p.kh = 3; p.kt = 1; p.mode = GR_EPI_RELU; p.seg0_c0 = 0; p.seg1_chunks = 0; p.dst0 = cat; p.dst_ld = 320;
-  // convc2: 256 -> 192
-  if ((rc = gru_w_map(&mW, wc2, 256, 192, 9))) return rc;
-  p.bias = bc2; p.N = 192; p.n_valid = 192; p.seg0_chunks = 4; p.dst_c0 = 0;
-  if ((rc = gru_launch(mCor, mCor, mW, p, s, st))) return rc;
-  // convf2: 128 -> 64
+  p.mode = GR_EPI_RELU; p.seg0_c0 = 0; p.seg1_chunks = 0;
+  // flo = relu(convf1(flow)): 7x7 on 2 channels = one K = 98 (padded 128) GEMM on the im2col operand
+  {
+    const long long threads = s.P * 16;
+    flow_im2col_kernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, st>>>(flow, H, W, s.P, col);
+    PPM_CUDA(cudaGetLastError());
+  }
+  if ((rc = gru_w_map(&mW, wf1, 128, 128, 1))) return rc;
+  p.kw = 1; p.kh = 1; p.kt = 1; p.bias = bf1; p.N = 128; p.n_valid = 128; p.seg0_chunks = 2;
+  p.dst0 = flo; p.dst_ld = 128; p.dst_c0 = 0;
+  if ((rc = gru_launch(mCol, mCol, mW, p, s, st))) return rc;
+  // convf2: 128 -> 64 -> cat[:, 192:256]
+  p.kw = 3; p.kh = 3; p.dst0 = cat; p.dst_ld = 320;
   if ((rc = gru_w_map(&mW, wf2, 128, 64, 9))) return rc;
   p.bias = bf2; p.N = 64; p.n_valid = 64; p.seg0_chunks = 2; p.dst_c0 = 192;
   if ((rc = gru_launch(mFlo, mFlo, mW, p, s, st))) return rc;
+  // frame-major (B, C, H, W) seen as (1, C, B, H, W): sc = HW, st = C*HW
+  if (mhs_dtype == PPM_BF16) rc = gru_pack<__nv_bfloat16>(mhs, 0, HW, 64 * HW, s, 64, 320, 256, cat, nullptr, st);
+  else rc = gru_pack<float>(mhs, 0, HW, 64 * HW, s, 64, 320, 256, cat, nullptr, st);
+  if (rc) return rc;
+  // cor = gelu(convc1(lookup)) channels-last (K6), then convc2: 256 -> 192 -> cat[:, 0:192]
+  if ((rc = motion_front_launch(level0, level0 ? flow : nullptr, corr, front_a, front_b, B, H, W, W2, x2, cor, 1, st))) return rc;
+  if ((rc = gru_w_map(&mW, wc2, 256, 192, 9))) return rc;
+  p.bias = bc2; p.N = 192; p.n_valid = 192; p.seg0_chunks = 4; p.dst_c0 = 0;
+  if ((rc = gru_launch(mCor, mCor, mW, p, s, st))) return rc;
   // final_conv: 320 -> 190, split into motion_features[:, :126] (fp32) and the new hidden state (bf16)
   if ((rc = gru_w_map(&mW, wfin, 320, 192, 9))) return rc;
   p.bias = bfin; p.N = 192; p.n_valid = 190; p.seg0_chunks = 5; p.dst0 = nullptr;

@@ -119,8 +119,7 @@ def _pack3x3(conv, n_pad: int):
 
 class MotionEncoder:
     """``BasicMotionEncoder_v2.forward`` (models/core/ppmtereo_update.py:458-482) as one C-ABI call
-    (``ppm_motion_encoder``, K7) plus the two tiny-channel convolutions left on cuDNN (convf1, and init_conv on the
-    first iteration)."""
+    (``ppm_motion_encoder``, K7); init_conv (first iteration only) stays on cuDNN."""
 
     def __init__(self, encoder):
         self.m = encoder
@@ -134,15 +133,19 @@ class MotionEncoder:
         try:
             return (self.front.supported() and tuple(m.convc2.weight.shape) == (192, 256, 3, 3)
                     and tuple(m.convf2.weight.shape) == (64, 128, 3, 3)
-                    and tuple(m.final_conv.weight.shape) == (190, 320, 3, 3) and m.convf1.weight.shape[0] == 128)
+                    and tuple(m.final_conv.weight.shape) == (190, 320, 3, 3)
+                    and tuple(m.convf1.weight.shape) == (128, 2, 7, 7))
         except AttributeError:
             return False
 
     def _params(self):
         m = self.m
-        convs = (m.convc2, m.convf2, m.final_conv)
+        convs = (m.convf1, m.convc2, m.convf2, m.final_conv)
         versions = tuple((c.weight._version, c.weight.data_ptr(), c.bias._version, c.bias.data_ptr()) for c in convs)
         if versions != self._versions:
+            self.wf1 = torch.zeros(1, 128, 128, dtype=torch.bfloat16, device=m.convf1.weight.device)
+            self.wf1[0, :, :98] = m.convf1.weight.detach().reshape(128, 98).to(torch.bfloat16)   # column = c*49 + ih*7 + iw
+            self.bf1 = _b16(m.convf1.bias).contiguous()
             self.wc2, self.bc2 = _pack3x3(m.convc2, 192)
             self.wf2, self.bf2 = _pack3x3(m.convf2, 64)
             self.wfin, self.bfin = _pack3x3(m.final_conv, 192)
@@ -173,7 +176,6 @@ class MotionEncoder:
             keep = corr.float().contiguous()
             corr_ptr = keep.data_ptr()
         B, _, H, W = flow32.shape
-        flo1 = F.relu(m.convf1(flow)).contiguous()
         mhs = motion_hidden_state
         if mhs.dtype not in (torch.float32, torch.bfloat16):
             mhs = mhs.float()
@@ -190,8 +192,8 @@ class MotionEncoder:
             ws = self._ws[key] = torch.empty(n.value, dtype=torch.uint8, device=dev)
         feat = torch.empty(B, 128, H, W, dtype=torch.float32, device=dev)
         mhs_out = torch.empty(B, 64, H, W, dtype=torch.bfloat16, device=dev)
-        _lib.check(self.lib.ppm_motion_encoder(level0, lk_flow.data_ptr() if lk_flow is not None else None, corr_ptr, W2,
-                                               wa.data_ptr(), wb.data_ptr(), flo1.data_ptr(), _lib.dtype_code(flo1),
+        _lib.check(self.lib.ppm_motion_encoder(level0, (lk_flow if lk_flow is not None else flow32).data_ptr(), corr_ptr, W2,
+                                               wa.data_ptr(), wb.data_ptr(), self.wf1.data_ptr(), self.bf1.data_ptr(),
                                                mhs.data_ptr(), _lib.dtype_code(mhs), self.wc2.data_ptr(),
                                                self.bc2.data_ptr(), self.wf2.data_ptr(), self.bf2.data_ptr(),
                                                self.wfin.data_ptr(), self.bfin.data_ptr(), B, H, W, ws.data_ptr(),

@@ -2,7 +2,7 @@
 cuDNN under bf16 autocast on the same GPU (staged sources), against the CPU oracle's bf16-mode restatement, fused lookup
 vs materialised lookup, the first-iteration path (motion_hidden_state None -> init_conv), and the installed class.
 
-Tolerances: the three 3x3 convolutions accumulate 2304 / 1152 / 2880 products in fp32 in another order than cuDNN; a
+Tolerances: the 7x7 and the three 3x3 convolutions accumulate 98 / 2304 / 1152 / 2880 products in fp32 in another order than cuDNN; a
 result that falls on the other side of a bf16 rounding boundary differs by one bf16 ulp (2^-8 relative) and such flips
 feed the next convolution.  The bars are the ones the K5 / K5b tests use for the same kernel: >= 93 % of all outputs
 bit-identical, max |diff| <= 2^-6 of the tensor's scale, mean |diff| <= 2e-4 of it."""
@@ -144,7 +144,6 @@ def test_no_write_outside_outputs(env):
     impl = P.MotionEncoder(enc)
     with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
         want_f, want_h = impl(flow, corr, mhs, inp)
-        flo1 = torch.relu(enc.convf1(flow)).contiguous()
     n = ctypes.c_size_t()
     _lib.check(impl.lib.ppm_motion_encoder_workspace(B, H, W, ctypes.byref(n)), "ws")
     G = 4096
@@ -153,8 +152,8 @@ def test_no_write_outside_outputs(env):
     hid = torch.full((B * 64 * H * W + 2 * G,), -77.0, device="cuda").bfloat16()
     wa, wb = impl.front._params()
     c32 = corr.float().contiguous()
-    _lib.check(impl.lib.ppm_motion_encoder(None, None, c32.data_ptr(), 0, wa.data_ptr(), wb.data_ptr(), flo1.data_ptr(),
-                                           _lib.dtype_code(flo1), mhs.data_ptr(), _lib.dtype_code(mhs),
+    _lib.check(impl.lib.ppm_motion_encoder(None, flow.data_ptr(), c32.data_ptr(), 0, wa.data_ptr(), wb.data_ptr(),
+                                           impl.wf1.data_ptr(), impl.bf1.data_ptr(), mhs.data_ptr(), _lib.dtype_code(mhs),
                                            impl.wc2.data_ptr(), impl.bc2.data_ptr(), impl.wf2.data_ptr(),
                                            impl.bf2.data_ptr(), impl.wfin.data_ptr(), impl.bfin.data_ptr(), B, H, W,
                                            ws.data_ptr() + G, n.value, feat.data_ptr() + G * 4, hid.data_ptr() + G * 2,
@@ -174,7 +173,7 @@ def test_rejects_bad_arguments(env):
     lib = P.MotionEncoder(enc).lib
     buf = torch.zeros(1024, device="cuda")
     p = buf.data_ptr()
-    rc = lib.ppm_motion_encoder(None, None, p, 0, p, p, p, 0, p, 0, p, p, p, p, p, p, 1, 4, 4, p, 16, p, p, None)
+    rc = lib.ppm_motion_encoder(None, p, p, 0, p, p, p, p, p, 0, p, p, p, p, p, p, 1, 4, 4, p, 16, p, p, None)
     assert rc != 0 and "workspace" in lib.ppm_last_error().decode()
-    rc = lib.ppm_motion_encoder(None, None, p, 0, p, p, None, 0, p, 0, p, p, p, p, p, p, 1, 4, 4, p, 1 << 20, p, p, None)
+    rc = lib.ppm_motion_encoder(None, p, p, 0, p, p, None, p, p, 0, p, p, p, p, p, p, 1, 4, 4, p, 1 << 20, p, p, None)
     assert rc != 0 and "null" in lib.ppm_last_error().decode()
