@@ -233,6 +233,24 @@ PPM_API int ppm_motion_encoder(const void* level0, const float* flow, const floa
                        float* motion_features, void* mhs_out, void* stream);
 
 /* ---------------------------------------------------------------------------------------
+ * K8  value projection + uncertainty head: the two lines of the update iteration between the motion encoder and the
+ * memory read (models/core/ppmstereo.py:492-495), bf16 autocast regime:
+ *   value       = aggregator.to_v(motion_features)           Conv2d(128,128,1,bias=False)   ppmtereo_update.py:646, :948
+ *   uncertainty = update_block.uncertainty(cat[net, value])   Conv2d(256,128,3) ReLU Conv2d(128,1,1) Sigmoid   :889-893
+ * Three GEMMs on the K5 kernel; the value GEMM's epilogue stores NCHW bf16 (the memory read's V operand, used in place)
+ * and channels-last (second operand segment of the 3x3 convolution: torch.cat is never executed).
+ * motion_features, net: (B,128,H,W) fp32 or bf16.  wv: bf16 [1][128][128], bv fp32 [128] (zeros: to_v has no bias);
+ * wu1: bf16 [9][128][256] (tap = ih*3 + iw; input channels net 0..127, value 128..255), bu1 fp32 [128];
+ * wu2: bf16 [1][64][128] (row 0 = the weight, rows 1..63 zero), bu2 fp32 [64].
+ * Outputs: value (B,128,H,W) bf16, uncertainty (B,1,H,W) bf16 = bf16(sigmoid(bf16 conv)).
+ * workspace: ppm_value_uncertainty_workspace bytes, 256-byte aligned. */
+PPM_API int ppm_value_uncertainty_workspace(int B, int H, int W, size_t* bytes);
+PPM_API int ppm_value_uncertainty(const void* motion_features, int mf_dtype, const void* net, int net_dtype, const void* wv,
+                          const float* bv, const void* wu1, const float* bu1, const void* wu2, const float* bu2, int B,
+                          int H, int W, void* workspace, size_t workspace_bytes, void* value, void* uncertainty,
+                          void* stream);
+
+/* ---------------------------------------------------------------------------------------
  * K5  SKSepConvGRU3D (models/core/ppmtereo_update.py:254-312, called from
  * SequenceUpdateBlock3D.forward :971-1003), in the reference's bf16 autocast regime:
  *   per stage s = 1 (along W), 2 (along H), 3 (along T):

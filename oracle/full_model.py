@@ -15,7 +15,7 @@ inline memory-block glue, copies on the compute stream):
   corr_lookup     CorrBlock1D.__call__                                       corr.py:74-94
   motion_encoder  BasicMotionEncoder_v2                                      ppmtereo_update.py:445-482
   to_v            Aggregate.to_v                                             ppmtereo_update.py:646
-  uncertainty     the uncertainty head                                       ppmtereo_update.py:889-893
+  uncertainty     the uncertainty head (installed: K8 = to_v + the head)     ppmtereo_update.py:889-893
   memory_read     installed: PPMMemory.read (+ per-level prep); reference: flash_attn_func calls only
   upd_attn        TimeAttnBlock + SpaceAttnBlock of update_block16           ppmtereo_update.py:593-631
   gru3d           SKSepConvGRU3D                                             ppmtereo_update.py:254-312
@@ -137,6 +137,8 @@ def run_clip(model, ppm, video, kernel_size: int, iters: int, installed: bool, s
                 tm.function(mem_mod.PPMMemory, "similarity", "memory_read")
                 tm.function(mem_mod.PPMMemory, "read", "memory_read")
                 tm.function(inst, "convex_upsample", "upsample")
+                motion_mod = importlib.import_module("ppmstereo_b200.motion")
+                tm.function(motion_mod.ValueUncertainty, "__call__", "uncertainty")      # K8: to_v + uncertainty head
             else:
                 tm.function(ppm.CorrBlock1D, "__init__", "corr_build")
                 tm.function(ppm.CorrBlock1D, "__call__", "corr_lookup")

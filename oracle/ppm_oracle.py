@@ -502,3 +502,21 @@ def motion_encoder(flow: torch.Tensor, corr: torch.Tensor, motion_hidden_state: 
     flo = relu(conv(flo, "convf2"))
     out = relu(conv(torch.cat([cor, flo, rnd(motion_hidden_state.float())], dim=1), "final_conv"))
     return torch.cat([out[:, :126], flow.float()], dim=1), out[:, 126:190]
+
+
+def value_uncertainty(motion_features: torch.Tensor, net: torch.Tensor, to_v_weight: torch.Tensor, unc_params: dict,
+                      mode: str = "fp32") -> Tuple[torch.Tensor, torch.Tensor]:
+    """``value = aggregator.to_v(motion_features)`` (Conv2d(128,128,1,bias=False), ppmtereo_update.py:646, called at
+    :948) and ``uncertainty = update_block.uncertainty(cat[net, value])`` (Conv2d(256,128,3) ReLU Conv2d(128,1,1)
+    Sigmoid, :889-893; called at models/core/ppmstereo.py:495).  unc_params: the Sequential's state dict ('0.weight',
+    '0.bias', '2.weight', '2.bias').  mode "bf16": each conv bf16(bf16(acc) + bias), sigmoid evaluated in fp32 on the bf16
+    conv output and rounded once."""
+    rnd = bf16_round if mode == "bf16" else (lambda t: t)
+
+    def conv(x, w, b):
+        b = torch.zeros(w.shape[0]) if b is None else b
+        return conv3d_shifted(x.unsqueeze(2), w.unsqueeze(2), b, rnd).squeeze(2)
+
+    value = conv(motion_features.float(), to_v_weight, None)
+    hid = torch.relu(conv(torch.cat([rnd(net.float()), value], dim=1), unc_params["0.weight"], unc_params["0.bias"]))
+    return value, rnd(torch.sigmoid(conv(hid, unc_params["2.weight"], unc_params["2.bias"])))

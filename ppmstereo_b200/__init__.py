@@ -17,12 +17,12 @@ from .pipeline import StagedRunner
 from . import shard
 from .upsample import convex_upsample
 from .gru import FlowHead3D, SepConvGRU3D, UpdateBlock3D
-from .motion import LookupRequest, MotionCorrFront, MotionEncoder
+from .motion import LookupRequest, MotionCorrFront, MotionEncoder, ValueUncertainty
 from .rowband import RowBandMemory, gather_bands, row_bands
 from .window import FrameFeatureCache, forward_batch_test
 from . import window
 from . import rowband
 
 __all__ = ["CorrBlock1D", "build_pyramid", "lookup", "lookup_l0", "PPMMemory", "ppm_memory_read", "softmax_scale",
-           "temporal_pe_table", "install", "uninstall", "forward_update_block", "StagedRunner", "shard", "convex_upsample", "SepConvGRU3D", "FlowHead3D", "UpdateBlock3D", "MotionCorrFront", "MotionEncoder", "LookupRequest", "RowBandMemory", "gather_bands", "row_bands",
+           "temporal_pe_table", "install", "uninstall", "forward_update_block", "StagedRunner", "shard", "convex_upsample", "SepConvGRU3D", "FlowHead3D", "UpdateBlock3D", "MotionCorrFront", "MotionEncoder", "ValueUncertainty", "LookupRequest", "RowBandMemory", "gather_bands", "row_bands",
            "FrameFeatureCache", "forward_batch_test", "window"]

@@ -55,6 +55,9 @@ SIGNATURES = {
     "ppm_motion_encoder": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
                                    c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
                                    c_void_p, c_size_t, c_void_p, c_void_p, c_void_p]),
+    "ppm_value_uncertainty_workspace": (c_int, [c_int, c_int, c_int, POINTER(c_size_t)]),
+    "ppm_value_uncertainty": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                      c_void_p, c_int, c_int, c_int, c_void_p, c_size_t, c_void_p, c_void_p, c_void_p]),
     "ppm_update_block3d_workspace": (c_int, [c_int, c_int, c_int, c_int, POINTER(c_size_t)]),
     "ppm_update_block3d": (c_int, [c_void_p, c_int, POINTER(c_void_p), POINTER(c_int), POINTER(c_void_p), POINTER(c_void_p),
                                    c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int,

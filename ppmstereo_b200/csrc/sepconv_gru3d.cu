@@ -48,7 +48,8 @@ enum GruEpilogue : int {
   GR_EPI_ZR = 3,       // N = 256: columns 0-127 as GR_EPI_Z, 128-255 as GR_EPI_R
   GR_EPI_Q = 4,        // q = bf16(tanh(bf16(acc + bias))); h = bf16(bf16(bf16(1-z)*h) + bf16(z*q)) -> hbuf (+ NCTHW out)
   GR_EPI_RELU = 5,     // out = relu(c)   -> dst0 [P, dst_ld] at channel dst_c0 (channels-last bf16) and / or NCTHW `out`
-  GR_EPI_LINEAR = 6    // out = c         -> likewise          (c = bf16(bf16(acc) + bias) in every mode)
+  GR_EPI_LINEAR = 6,   // out = c         -> likewise          (c = bf16(bf16(acc) + bias) in every mode)
+  GR_EPI_SIGMOID = 7   // out = bf16(sigmoid(c))  -> likewise
 };
 
 struct GruGemmParams {
@@ -347,11 +348,14 @@ gru_gemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constan
             #pragma unroll
             for (int e = 0; e < 8; ++e) v[e] = __fmul_rn(bf16_round_f(gr_sigmoid(v[e])), h[e]);
             *reinterpret_cast<uint4*>(p.dst1 + pos * kGrHidden + ch) = gr_pack8(v);
-          } else if (mode == GR_EPI_RELU || mode == GR_EPI_LINEAR) {
+          } else if (mode == GR_EPI_RELU || mode == GR_EPI_LINEAR || mode == GR_EPI_SIGMOID) {
             if (col0 + g * 8 < p.n_valid) {
               if (mode == GR_EPI_RELU) {
                 #pragma unroll
                 for (int e = 0; e < 8; ++e) v[e] = fmaxf(v[e], 0.f);
+              } else if (mode == GR_EPI_SIGMOID) {
+                #pragma unroll
+                for (int e = 0; e < 8; ++e) v[e] = bf16_round_f(gr_sigmoid(v[e]));
               } else {
                 #pragma unroll
                 for (int e = 0; e < 8; ++e) v[e] *= p.out_scale;
@@ -833,4 +837,68 @@ extern "C" int ppm_motion_encoder(const void* level0, const float* flow, const f
   p.out = motion_features; p.out_dtype = PPM_F32; p.out_sb = 0; p.out_sc = HW; p.out_st = 128 * HW;
   p.out2 = mhs_out; p.out2_dtype = PPM_BF16; p.out2_sb = 0; p.out2_sc = HW; p.out2_st = 64 * HW; p.split_c = 126;
   return gru_launch(mCat, mCat, mW, p, s, st);
+}
+
+// ------------------------------------------------------------------------------------------------ value + uncertainty (K8)
+// The two lines of the update iteration between the motion encoder and the memory read (reference
+// models/core/ppmstereo.py:492-495 -> ppmtereo_update.py:945-950 and :936-938):
+//   value = aggregator.to_v(motion_features)                       1x1, 128 -> 128, no bias
+//   uncertainty = sigmoid(conv1x1(relu(conv3x3(cat[net, value]))))  256 -> 128 -> 1
+// value is written twice by its GEMM's epilogue: NCHW bf16 (what the memory read takes in place as its V operand) and
+// channels-last (the second A segment of the 3x3 convolution: the cat is never built).
+extern "C" int ppm_value_uncertainty_workspace(int B, int H, int W, size_t* bytes) {
+  PPM_CHECK(B > 0 && H > 0 && W > 0 && bytes, PPM_ERR_ARG, "ppm_value_uncertainty_workspace: bad argument");
+  *bytes = static_cast<size_t>(B) * H * W * (4 * 128 * 2);          // motion features, net, value, hidden: [P,128] bf16 each
+  return PPM_OK;
+}
+
+extern "C" int ppm_value_uncertainty(const void* motion_features, int mf_dtype, const void* net, int net_dtype,
+                                     const void* wv, const float* bv, const void* wu1, const float* bu1, const void* wu2,
+                                     const float* bu2, int B, int H, int W, void* workspace, size_t workspace_bytes,
+                                     void* value, void* uncertainty, void* stream) {
+  using namespace ppm;
+  PPM_CHECK(motion_features && net && wv && bv && wu1 && bu1 && wu2 && bu2 && workspace && value && uncertainty, PPM_ERR_ARG,
+            "ppm_value_uncertainty: null pointer");
+  PPM_CHECK(B > 0 && H > 0 && W > 0 && B <= 65535, PPM_ERR_ARG, "ppm_value_uncertainty: bad shape");
+  PPM_CHECK((mf_dtype == PPM_F32 || mf_dtype == PPM_BF16) && (net_dtype == PPM_F32 || net_dtype == PPM_BF16), PPM_ERR_ARG,
+            "ppm_value_uncertainty: bad dtype");
+  size_t need = 0;
+  ppm_value_uncertainty_workspace(B, H, W, &need);
+  PPM_CHECK(workspace_bytes >= need, PPM_ERR_ARG, "ppm_value_uncertainty: workspace of %zu bytes < %zu needed", workspace_bytes, need);
+  PPM_CHECK((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, PPM_ERR_ARG, "ppm_value_uncertainty: workspace must be 256-byte aligned");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const GruShape s = gru_shape(1, B, H, W);
+  const long long HW = static_cast<long long>(H) * W;
+  __nv_bfloat16* mfc = static_cast<__nv_bfloat16*>(workspace);
+  __nv_bfloat16* netc = mfc + s.P * 128;
+  __nv_bfloat16* valc = netc + s.P * 128;
+  __nv_bfloat16* hid = valc + s.P * 128;
+  int rc;
+  if (mf_dtype == PPM_BF16) rc = gru_pack<__nv_bfloat16>(motion_features, 0, HW, 128 * HW, s, 128, 128, 0, mfc, nullptr, st);
+  else rc = gru_pack<float>(motion_features, 0, HW, 128 * HW, s, 128, 128, 0, mfc, nullptr, st);
+  if (rc) return rc;
+  if (net_dtype == PPM_BF16) rc = gru_pack<__nv_bfloat16>(net, 0, HW, 128 * HW, s, 128, 128, 0, netc, nullptr, st);
+  else rc = gru_pack<float>(net, 0, HW, 128 * HW, s, 128, 128, 0, netc, nullptr, st);
+  if (rc) return rc;
+  CUtensorMap mMf, mNet, mVal, mHid, mW;
+  if ((rc = gru_act_map(&mMf, mfc, 128, s))) return rc;
+  if ((rc = gru_act_map(&mNet, netc, 128, s))) return rc;
+  if ((rc = gru_act_map(&mVal, valc, 128, s))) return rc;
+  if ((rc = gru_act_map(&mHid, hid, 128, s))) return rc;
+  GruGemmParams p{};
+  p.kt = 1; p.seg0_c0 = 0; p.dst_ld = 128; p.dst_c0 = 0;
+  // value = to_v(motion_features)
+  if ((rc = gru_w_map(&mW, wv, 128, 128, 1))) return rc;
+  p.kw = 1; p.kh = 1; p.mode = GR_EPI_LINEAR; p.bias = bv; p.N = 128; p.n_valid = 128; p.seg0_chunks = 2; p.seg1_chunks = 0;
+  p.dst0 = valc; p.out = value; p.out_dtype = PPM_BF16; p.out_sb = 0; p.out_sc = HW; p.out_st = 128 * HW;
+  if ((rc = gru_launch(mMf, mMf, mW, p, s, st))) return rc;
+  // hidden = relu(conv3x3(cat[net, value]))
+  if ((rc = gru_w_map(&mW, wu1, 256, 128, 9))) return rc;
+  p.kw = 3; p.kh = 3; p.mode = GR_EPI_RELU; p.bias = bu1; p.seg0_chunks = 2; p.seg1_chunks = 2; p.dst0 = hid; p.out = nullptr;
+  if ((rc = gru_launch(mNet, mVal, mW, p, s, st))) return rc;
+  // uncertainty = sigmoid(conv1x1(hidden))
+  if ((rc = gru_w_map(&mW, wu2, 128, 64, 1))) return rc;
+  p.kw = 1; p.kh = 1; p.mode = GR_EPI_SIGMOID; p.bias = bu2; p.N = 64; p.n_valid = 1; p.seg0_chunks = 2; p.seg1_chunks = 0;
+  p.dst0 = nullptr; p.out = uncertainty; p.out_dtype = PPM_BF16; p.out_sb = 0; p.out_sc = HW; p.out_st = HW;
+  return gru_launch(mHid, mHid, mW, p, s, st);
 }

@@ -18,7 +18,7 @@ import sys
 
 from .corr import CorrBlock1D
 from .gru import flow_head_forward, gru_forward, update_block_forward
-from .motion import LookupRequest, encoder_forward
+from .motion import LookupRequest, encoder_forward, value_and_uncertainty
 from .memory import C, PPMMemory, softmax_scale
 from .upsample import convex_upsample
 from .window import forward_batch_test
@@ -76,9 +76,8 @@ def forward_update_block(self, image1, update_block, corr_fn, flow, net, inp, mo
         # K6: when the encoder's front end is fused, the lookup runs inside it (the (B,36,h,w) tensor is never written)
         fused = hasattr(type(update_block.encoder), "_ppm_reference_forward") and getattr(corr_fn, "_l0_only", False)
         out_corrs = LookupRequest(corr_fn, flow) if fused else corr_fn(flow)
-        motion_features, motion_hidden_state, value = update_block.get_motion_and_value(
-            flow, out_corrs, motion_hidden_state, inp)
-        uncertainty_score = update_block.get_uncertainty(torch.cat([net, value], dim=1))
+        motion_features, motion_hidden_state, value, uncertainty_score = value_and_uncertainty(
+            update_block, flow, out_corrs, motion_hidden_state, inp, net)               # K7 + K8
         mf5 = motion_features.reshape(b, t, c, h, w).permute(0, 2, 1, 3, 4)
         v5 = value.reshape(b, t, c, h, w).permute(0, 2, 1, 3, 4)
         motion_features_global, _ = memory.read(v5, mf5, sim_score, strive_time, uncertainty_score, beta, scale)

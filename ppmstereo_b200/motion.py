@@ -17,6 +17,7 @@ from . import _lib
 
 A_FLOATS, B_FLOATS = 4124, 19212          # PPM_MF_A_FLOATS / PPM_MF_B_FLOATS (include/ppm_b200.h)
 _ATTR = "_ppmstereo_b200_front"
+_ATTR_VU = "_ppmstereo_b200_value_uncertainty"
 
 
 class LookupRequest:
@@ -201,6 +202,92 @@ class MotionEncoder:
                    "ppm_motion_encoder")
         feat[:, 126:] = flow32
         return feat, mhs_out
+
+
+class ValueUncertainty:
+    """``value = update_block.aggregator.to_v(motion_features)`` and
+    ``uncertainty = update_block.uncertainty(torch.cat([net, value], dim=1))`` (models/core/ppmstereo.py:492-495;
+    modules at ppmtereo_update.py:646 and :889-893) as one C-ABI call (``ppm_value_uncertainty``, K8)."""
+
+    def __init__(self, update_block):
+        self.blk = update_block
+        self.lib = _lib.load()
+        self._versions = None
+        self._ws: Dict[Tuple, torch.Tensor] = {}
+
+    def supported(self) -> bool:
+        try:
+            tv, u = self.blk.aggregator.to_v, self.blk.uncertainty
+            return (isinstance(tv, torch.nn.Conv2d) and tuple(tv.weight.shape) == (128, 128, 1, 1) and tv.bias is None
+                    and len(u) == 4 and tuple(u[0].weight.shape) == (128, 256, 3, 3) and isinstance(u[1], torch.nn.ReLU)
+                    and tuple(u[2].weight.shape) == (1, 128, 1, 1) and isinstance(u[3], torch.nn.Sigmoid))
+        except (AttributeError, TypeError, IndexError):
+            return False
+
+    def _params(self):
+        tv, u = self.blk.aggregator.to_v, self.blk.uncertainty
+        ps = (tv.weight, u[0].weight, u[0].bias, u[2].weight, u[2].bias)
+        versions = tuple((q._version, q.data_ptr()) for q in ps)
+        if versions != self._versions:
+            dev = tv.weight.device
+            self.wv = tv.weight.detach().reshape(1, 128, 128).to(torch.bfloat16).contiguous()
+            self.bv = torch.zeros(128, device=dev)
+            self.wu1, self.bu1 = _pack3x3(u[0], 128)
+            self.wu2 = torch.zeros(1, 64, 128, dtype=torch.bfloat16, device=dev)
+            self.wu2[0, 0] = u[2].weight.detach().reshape(128).to(torch.bfloat16)
+            self.bu2 = torch.zeros(64, device=dev)
+            self.bu2[0] = _b16(u[2].bias)[0]
+            self._versions = versions
+
+    def __call__(self, motion_features: torch.Tensor, net: torch.Tensor):
+        import ctypes
+        ts = []
+        for name, x in (("motion_features", motion_features), ("net", net)):
+            if not x.is_cuda or x.dim() != 4 or x.shape[1] != 128:
+                raise RuntimeError(f"{name} must be a CUDA tensor (B, 128, h, w), got {tuple(x.shape)}")
+            if x.dtype not in (torch.float32, torch.bfloat16):
+                x = x.float()
+            ts.append(x.detach().contiguous())
+        mf, net = ts
+        if mf.shape != net.shape:
+            raise RuntimeError("motion_features and net must share their shape")
+        self._params()
+        B, _, H, W = mf.shape
+        dev = mf.device
+        key = (B, H, W, dev)
+        ws = self._ws.get(key)
+        if ws is None:
+            n = ctypes.c_size_t()
+            _lib.check(self.lib.ppm_value_uncertainty_workspace(B, H, W, ctypes.byref(n)), "ppm_value_uncertainty_workspace")
+            self._ws.clear()
+            ws = self._ws[key] = torch.empty(n.value, dtype=torch.uint8, device=dev)
+        value = torch.empty(B, 128, H, W, dtype=torch.bfloat16, device=dev)
+        unc = torch.empty(B, 1, H, W, dtype=torch.bfloat16, device=dev)
+        _lib.check(self.lib.ppm_value_uncertainty(mf.data_ptr(), _lib.dtype_code(mf), net.data_ptr(), _lib.dtype_code(net),
+                                                  self.wv.data_ptr(), self.bv.data_ptr(), self.wu1.data_ptr(),
+                                                  self.bu1.data_ptr(), self.wu2.data_ptr(), self.bu2.data_ptr(), B, H, W,
+                                                  ws.data_ptr(), ws.numel(), value.data_ptr(), unc.data_ptr(),
+                                                  _lib.stream_ptr()), "ppm_value_uncertainty")
+        return value, unc
+
+
+def value_and_uncertainty(update_block, flow, corr, motion_hidden_state, inp, net):
+    """The head of one update iteration as ``forward_update_block`` runs it (models/core/ppmstereo.py:492-495):
+    ``get_motion_and_value`` + ``get_uncertainty``.  With the encoder class installed and in the bf16 autocast regime
+    the projection and the uncertainty head are one call (K8); otherwise the block's own methods."""
+    vu = update_block.__dict__.get(_ATTR_VU)
+    if vu is None:
+        vu = update_block.__dict__[_ATTR_VU] = ValueUncertainty(update_block)
+    if (hasattr(type(update_block.encoder), "_ppm_reference_forward") and _kernel_regime(net) and vu.supported()
+            and net.dtype in (torch.float32, torch.bfloat16)):
+        motion_features, motion_hidden_state = update_block.encoder(flow, corr, motion_hidden_state, inp)
+        if motion_features.dtype in (torch.float32, torch.bfloat16):
+            value, uncertainty = vu(motion_features, net)
+            return motion_features, motion_hidden_state, value, uncertainty
+        value = update_block.aggregator.to_v(motion_features)
+    else:
+        motion_features, motion_hidden_state, value = update_block.get_motion_and_value(flow, corr, motion_hidden_state, inp)
+    return motion_features, motion_hidden_state, value, update_block.get_uncertainty(torch.cat([net, value], dim=1))
 
 
 def _kernel_regime(t: torch.Tensor) -> bool:

@@ -181,3 +181,26 @@ def test_motion_encoder_oracle_matches_reference_module():
     lo_f, lo_h = O.motion_encoder(flow, corr, mhs, dict(enc.state_dict()), mode="bf16")
     assert float((lo_f - want_f).abs().max()) <= 3e-2 * float(want_f.abs().max())
     assert float((lo_h - want_h).abs().max()) <= 3e-2 * max(1.0, float(want_h.abs().max()))
+
+
+def test_value_uncertainty_oracle_matches_reference_modules():
+    import importlib
+    from oracle import ref_import
+    if not ref_import.available():
+        pytest.skip("reference tree not present")
+    ref_import.load_reference()
+    upd = importlib.import_module("models.core.ppmtereo_update")
+    torch.manual_seed(6)
+    blk = upd.SequenceUpdateBlock3D(hidden_dim=128, cor_planes=36, mask_size=4).eval()
+    g = torch.Generator().manual_seed(7)
+    mf = torch.randn(2, 128, 6, 9, generator=g)
+    net = torch.tanh(torch.randn(2, 128, 6, 9, generator=g))
+    with torch.no_grad():
+        want_v = blk.aggregator.to_v(mf)
+        want_u = blk.get_uncertainty(torch.cat([net, want_v], dim=1))
+    got_v, got_u = O.value_uncertainty(mf, net, blk.aggregator.to_v.weight.detach(), dict(blk.uncertainty.state_dict()))
+    assert got_v.shape == want_v.shape == (2, 128, 6, 9) and got_u.shape == want_u.shape == (2, 1, 6, 9)
+    assert float((got_v - want_v).abs().max()) <= 2e-6 and float((got_u - want_u).abs().max()) <= 2e-6
+    lo_v, lo_u = O.value_uncertainty(mf, net, blk.aggregator.to_v.weight.detach(), dict(blk.uncertainty.state_dict()), mode="bf16")
+    assert float((lo_v - want_v).abs().max()) <= 2e-2 * float(want_v.abs().max())
+    assert float((lo_u - want_u).abs().max()) <= 1e-2
