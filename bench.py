@@ -552,6 +552,59 @@ def main():
                       "note": "one whole unit (2 pack launches + 8 GEMM launches) replayed from a CUDA graph; FLOPs = 8.85 MFLOP "
                               "per position (SURVEY 8f / DESIGN K5); ncu per-GEMM breakdown in profiles/r02_k5_gru.md"})
         del k5, gh, gx
+
+        def _c2(ci, co, k, groups=1, bias=True):
+            return nn.Conv2d(ci, co, k, padding=k // 2, groups=groups, bias=bias)
+
+        class _FrontLayers(nn.Module):                  # PCBlock4_Deep_nopool_res(36, 256, [1, 7]) layer shapes
+            def __init__(self):
+                super().__init__()
+                self.ffn1 = nn.Sequential(_c2(36, 54, 1), nn.GELU(), _c2(54, 36, 1))
+                self.conv_list = nn.ModuleList([_c2(36, 36, 1, groups=36), _c2(36, 36, 7, groups=36)])
+                self.pw = _c2(36, 36, 1)
+                self.ffn2 = nn.Sequential(_c2(36, 54, 1), nn.GELU(), _c2(54, 256, 1))
+
+        class _EncoderLayers(nn.Module):                # BasicMotionEncoder_v2 layer shapes
+            def __init__(self):
+                super().__init__()
+                self.convc1, self.convc2 = _FrontLayers(), _c2(256, 192, 3)
+                self.convf1, self.convf2, self.final_conv = _c2(2, 128, 7), _c2(128, 64, 3), _c2(320, 190, 3)
+
+        class _ValueLayers(nn.Module):                  # aggregator.to_v + the uncertainty head
+            def __init__(self):
+                super().__init__()
+                self.aggregator = nn.Module()
+                self.aggregator.to_v = _c2(128, 128, 1, bias=False)
+                self.uncertainty = nn.Sequential(_c2(256, 128, 3), nn.ReLU(), _c2(128, 1, 1), nn.Sigmoid())
+
+        k7 = P.MotionEncoder(_EncoderLayers().to(dev))
+        k8 = P.ValueUncertainty(_ValueLayers().to(dev))
+        ef = torch.zeros(T4, 2, h4, w4, device=dev)
+        ef[:, 0] = torch.rand(T4, h4, w4, generator=gk, device=dev) * -40.0
+        f1e = torch.randn(T4, 256, h4, w4, generator=gk, device=dev).bfloat16()
+        f2e = torch.randn(T4, 256, h4, w4, generator=gk, device=dev).bfloat16()
+        eblk = P.CorrBlock1D(f1e, f2e)
+        emh = torch.randn(T4, 64, h4, w4, generator=gk, device=dev).bfloat16()
+        enet = torch.tanh(torch.randn(T4, 128, h4, w4, generator=gk, device=dev))
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            ms7 = time_kernel(lambda: k7(ef, P.LookupRequest(eblk, ef), emh, None), reps=3)
+            emf, _ = k7(ef, P.LookupRequest(eblk, ef), emh, None)
+            ms8 = time_kernel(lambda: k8(emf, enet), reps=3)
+        pos = float(T4 * h4 * w4)
+        f7 = 2.0 * pos * (9 * (256 * 192 + 128 * 64 + 320 * 190) + 98 * 128)
+        f8 = 2.0 * pos * (128 * 128 + 9 * 256 * 128 + 128)
+        other.append({"kernel": "K7 ppm_motion_encoder (BasicMotionEncoder_v2.forward incl. the fused lookup: im2col + K6a + K6b + "
+                                "4 GEMMs + 1 pack; 1/4-res, T=20; not part of the timed hot-path step)",
+                      "bound": "tensor", "achieved": f7 / (ms7 * 1e-3) / 1e12, "peak": tpk, "unit": "TFLOP/s",
+                      "frac": f7 / (ms7 * 1e-3) / 1e12 / tpk, "flops_per_call": f7, "avg_call_ms": ms7, "traffic": None,
+                      "note": "FLOPs = the four convolutions on the tensor cores only; 3.2 of the call's ~6.2 ms are the CUDA-core "
+                              "front end K6a/K6b (DESIGN K6), so frac understates the GEMMs: ncu per launch in "
+                              "profiles/r02_k7_motion_encoder.md; torch/cuDNN path of the reference: 13.1 ms"})
+        other.append({"kernel": "K8 ppm_value_uncertainty (to_v + uncertainty head: 2 packs + 3 GEMMs; 1/4-res, T=20)",
+                      "bound": "tensor", "achieved": f8 / (ms8 * 1e-3) / 1e12, "peak": tpk, "unit": "TFLOP/s",
+                      "frac": f8 / (ms8 * 1e-3) / 1e12 / tpk, "flops_per_call": f8, "avg_call_ms": ms8, "traffic": None,
+                      "note": "0.76 TFLOP per call, of which the 3x3 convolution 0.70; the two K = 128 GEMMs are epilogue / store bound"})
+        del k7, k8, ef, f1e, f2e, eblk, emh, enet, emf
         same_box = None
         try:                                            # the library the reference calls at ppmstereo.py:550, same box
             if args.no_same_box:

@@ -212,7 +212,7 @@ PPM_API int ppm_motion_corr_front(const void* level0, const float* flow, const f
 
 /* ---------------------------------------------------------------------------------------
  * K7  BasicMotionEncoder_v2.forward (models/core/ppmtereo_update.py:458-482) as one call, bf16 autocast regime:
- *   cor = gelu(convc1(lookup))  (K6, written channels-last)     flo = relu(convf2(relu(convf1(flow))))
+ *   cor = gelu(convc1(lookup))  (K6 + one K = 64 GEMM)          flo = relu(convf2(relu(convf1(flow))))
  *   cor = relu(convc2(cor))                                      out = relu(final_conv(cat[cor, flo, mhs]))
  * convf1 (7x7 on the two flow channels) is an im2col pack + one K = 98 (padded to 128) GEMM; the three 3x3
  * convolutions run on the K5 shifted-GEMM kernel (9 offsets, tcgen05); their producers write one
@@ -221,14 +221,16 @@ PPM_API int ppm_motion_corr_front(const void* level0, const float* flow, const f
  * the fp32 flow promotes), channels 126..189 -> mhs_out (bf16).  motion_features[:, 126:128] (= flow) is the
  * caller's to fill.  init_conv (first iteration only) stays with the caller: mhs (B,64,H,W) fp32 or bf16.
  * flow (B,2,H,W) fp32, always required; level0 / corr / W2 / front_a / front_b: as ppm_motion_corr_front
- * (weights_a / weights_b).  wf1: bf16 [1][128][128] = convf1.weight.reshape(128, 98), columns 98..127 zero; bf1 fp32 [128].
+ * (weights_a / weights_b).  wd: bf16 [1][256][64] = convc1.ffn2.2.weight.reshape(256, 54), columns 54..63 zero: the
+ * block's last layer and the outer GELU run as a GEMM on the hidden vector K6b leaves channels-last (its bias is read
+ * from weights_b).  wf1: bf16 [1][128][128] = convf1.weight.reshape(128, 98), columns 98..127 zero; bf1 fp32 [128].
  * wc2: bf16 [9][192][256], wf2: bf16 [9][64][128], wfin: bf16 [9][192][320] (rows 190, 191 zero), tap = ih*3 + iw;
  * bc2 fp32 [192], bf2 fp32 [64], bfin fp32 [192].  Rounding per convolution: bf16(bf16(acc) + bias), then ReLU.
  * workspace: ppm_motion_encoder_workspace bytes, 256-byte aligned. */
 PPM_API int ppm_motion_encoder_workspace(int B, int H, int W, size_t* bytes);
 PPM_API int ppm_motion_encoder(const void* level0, const float* flow, const float* corr, int W2, const float* front_a,
-                       const float* front_b, const void* wf1, const float* bf1, const void* mhs, int mhs_dtype,
-                       const void* wc2, const float* bc2, const void* wf2, const float* bf2, const void* wfin,
+                       const float* front_b, const void* wd, const void* wf1, const float* bf1, const void* mhs,
+                       int mhs_dtype, const void* wc2, const float* bc2, const void* wf2, const float* bf2, const void* wfin,
                        const float* bfin, int B, int H, int W, void* workspace, size_t workspace_bytes,
                        float* motion_features, void* mhs_out, void* stream);
 

@@ -52,7 +52,7 @@ SIGNATURES = {
     "ppm_motion_corr_front": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int,
                                       c_void_p, c_void_p, c_void_p]),
     "ppm_motion_encoder_workspace": (c_int, [c_int, c_int, c_int, POINTER(c_size_t)]),
-    "ppm_motion_encoder": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
+    "ppm_motion_encoder": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
                                    c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
                                    c_void_p, c_size_t, c_void_p, c_void_p, c_void_p]),
     "ppm_value_uncertainty_workspace": (c_int, [c_int, c_int, c_int, POINTER(c_size_t)]),

@@ -35,6 +35,9 @@ int make_tensor_map(CUtensorMap* map, CUtensorMapDataType dtype, int rank, const
                     CUtensorMapSwizzle swizzle);
 
 // K6 (csrc/corr_lookup.cu): fused lookup + motion-encoder front end; used by ppm_motion_corr_front and ppm_motion_encoder.
+constexpr int kMotionFrontBiasD = 18956;   // offset (floats) of the ffn2.2 bias [256] inside weights_b (mf::kBd, corr_lookup.cu)
+// channels_last: 0 = cor (B,256,H,W1) NCHW; 1 = cor [pixel][256]; 2 = only the hidden vector gelu(ffn2.0(x)) as [pixel][64]
+// (54 values + zeros) -- the caller runs the 54 -> 256 convolution + GELU as a GEMM
 int motion_front_launch(const void* level0, const float* flow, const float* corr, const float* weights_a,
                         const float* weights_b, int B, int H, int W1, int W2, float* x2_ws, void* cor, int channels_last,
                         cudaStream_t st);

@@ -394,6 +394,7 @@ constexpr int kBc = kWc + kHid * kC;        // ffn2.0 bias [54] (+2 pad)
 constexpr int kWd = kBc + 56;               // ffn2.2 weight TRANSPOSED [54][256]
 constexpr int kBd = kWd + kHid * kOut;      // ffn2.2 bias [256]
 constexpr int kBSize = kBd + kOut;          // 19212 floats
+static_assert(kBd == ppm::kMotionFrontBiasD, "common.cuh's copy of the ffn2.2 bias offset is stale");
 }  // namespace mf
 
 __device__ __forceinline__ float mf_gelu(float x) { return 0.5f * x * (1.f + erff(x * 0.70710678118654752440f)); }
@@ -537,6 +538,21 @@ motion_front_b_kernel(const float* __restrict__ x2, const float* __restrict__ wt
       acc = fmaf(w4.z, x4r[4 * c4 + 2], acc); acc = fmaf(w4.w, x4r[4 * c4 + 3], acc);
     }
     u[o] = mf_r(mf_gelu(mf_r(mf_r(acc) + sw[mf::kBc + o])));
+  }
+  if (channels_last == 2) {
+    // hidden vector only: [pixel][64] bf16 (54 values + zero padding) = the K-major operand of the 54 -> 256 convolution,
+    // which then runs as a tensor-core GEMM with the GELU in its epilogue (ppm_motion_encoder, K7)
+    uint4* d = reinterpret_cast<uint4*>(cor + (static_cast<long long>(frame) * HW + pix) * 64);
+    #pragma unroll
+    for (int g = 0; g < 8; ++g) {
+      float e[8];
+      #pragma unroll
+      for (int j = 0; j < 8; ++j) e[j] = (g * 8 + j < mf::kHid) ? u[(g * 8 + j < mf::kHid) ? g * 8 + j : 0] : 0.f;
+      uint4 v;
+      v.x = pack_bf16x2(e[0], e[1]); v.y = pack_bf16x2(e[2], e[3]); v.z = pack_bf16x2(e[4], e[5]); v.w = pack_bf16x2(e[6], e[7]);
+      d[g] = v;
+    }
+    return;
   }
   // ---- cor = bf16(gelu(ffn2.2(u))), 16 output channels at a time (weights transposed: [c][o])
   // NCHW (the reference's layout) or channels-last [pixel][256] (operand of the shifted-GEMM convolutions, K5/K7)

@@ -764,7 +764,7 @@ extern "C" int ppm_update_block3d(const void* net, int net_dtype, const void* co
 // BasicMotionEncoder_v2.forward (reference models/core/ppmtereo_update.py:458-482) with motion_hidden_state given
 // (init_conv, first iteration only, stays with the caller):
 //   flo1 = relu(convf1(flow))             7x7, 2 -> 128         im2col pack + one K = 128 GEMM
-//   cor = gelu(convc1(lookup))            K6, written channels-last
+//   cor = gelu(convc1(lookup))            K6 up to the 54-channel hidden vector + a K = 64 GEMM with the GELU epilogue
 //   cor = relu(convc2(cor))               3x3, 256 -> 192       shifted GEMM, 9 offsets  -> cat[:,   0:192]
 //   flo = relu(convf2(flo1))              3x3, 128 ->  64       -> cat[:, 192:256]
 //   cat[:, 256:320] = motion_hidden_state (packed)              -- torch.cat([cor, flo, mhs]) is never built separately:
@@ -778,12 +778,12 @@ extern "C" int ppm_motion_encoder_workspace(int B, int H, int W, size_t* bytes) 
 }
 
 extern "C" int ppm_motion_encoder(const void* level0, const float* flow, const float* corr, int W2, const float* front_a,
-                                  const float* front_b, const void* wf1, const float* bf1, const void* mhs, int mhs_dtype,
-                                  const void* wc2, const float* bc2, const void* wf2, const float* bf2, const void* wfin,
+                                  const float* front_b, const void* wd, const void* wf1, const float* bf1, const void* mhs,
+                                  int mhs_dtype, const void* wc2, const float* bc2, const void* wf2, const float* bf2, const void* wfin,
                                   const float* bfin, int B, int H, int W, void* workspace, size_t workspace_bytes,
                                   float* motion_features, void* mhs_out, void* stream) {
   using namespace ppm;
-  PPM_CHECK(flow && wf1 && bf1 && mhs && wc2 && bc2 && wf2 && bf2 && wfin && bfin && workspace && motion_features && mhs_out,
+  PPM_CHECK(flow && front_b && wd && wf1 && bf1 && mhs && wc2 && bc2 && wf2 && bf2 && wfin && bfin && workspace && motion_features && mhs_out,
             PPM_ERR_ARG, "ppm_motion_encoder: null pointer");
   PPM_CHECK(B > 0 && H > 0 && W > 0 && B <= 65535, PPM_ERR_ARG, "ppm_motion_encoder: bad shape");
   PPM_CHECK(mhs_dtype == PPM_F32 || mhs_dtype == PPM_BF16, PPM_ERR_ARG, "ppm_motion_encoder: bad dtype");
@@ -826,8 +826,18 @@ extern "C" int ppm_motion_encoder(const void* level0, const float* flow, const f
   if (mhs_dtype == PPM_BF16) rc = gru_pack<__nv_bfloat16>(mhs, 0, HW, 64 * HW, s, 64, 320, 256, cat, nullptr, st);
   else rc = gru_pack<float>(mhs, 0, HW, 64 * HW, s, 64, 320, 256, cat, nullptr, st);
   if (rc) return rc;
-  // cor = gelu(convc1(lookup)) channels-last (K6), then convc2: 256 -> 192 -> cat[:, 0:192]
-  if ((rc = motion_front_launch(level0, level0 ? flow : nullptr, corr, front_a, front_b, B, H, W, W2, x2, cor, 1, st))) return rc;
+  // cor = gelu(convc1(lookup)): K6 up to the block's 54-channel hidden vector ([P,64], in the flo buffer, free by now), then
+  // its last layer (54 -> 256) + the outer GELU as one K = 64 GEMM -> cor channels-last
+  __nv_bfloat16* hid = flo;
+  if ((rc = motion_front_launch(level0, level0 ? flow : nullptr, corr, front_a, front_b, B, H, W, W2, x2, hid, 2, st))) return rc;
+  CUtensorMap mHid;
+  if ((rc = gru_act_map(&mHid, hid, 64, s))) return rc;
+  if ((rc = gru_w_map(&mW, wd, 64, 256, 1))) return rc;
+  p.kw = 1; p.kh = 1; p.mode = GR_EPI_GELU; p.bias = front_b + kMotionFrontBiasD; p.N = 256; p.n_valid = 256; p.seg0_chunks = 1;
+  p.dst0 = cor; p.dst_ld = 256; p.dst_c0 = 0;
+  if ((rc = gru_launch(mHid, mHid, mW, p, s, st))) return rc;
+  // convc2: 256 -> 192 -> cat[:, 0:192]
+  p.kw = 3; p.kh = 3; p.mode = GR_EPI_RELU; p.dst0 = cat; p.dst_ld = 320;
   if ((rc = gru_w_map(&mW, wc2, 256, 192, 9))) return rc;
   p.bias = bc2; p.N = 192; p.n_valid = 192; p.seg0_chunks = 4; p.dst_c0 = 0;
   if ((rc = gru_launch(mCor, mCor, mW, p, s, st))) return rc;

@@ -141,9 +141,11 @@ class MotionEncoder:
 
     def _params(self):
         m = self.m
-        convs = (m.convf1, m.convc2, m.convf2, m.final_conv)
+        convs = (m.convc1.ffn2[2], m.convf1, m.convc2, m.convf2, m.final_conv)
         versions = tuple((c.weight._version, c.weight.data_ptr(), c.bias._version, c.bias.data_ptr()) for c in convs)
         if versions != self._versions:
+            self.wd = torch.zeros(1, 256, 64, dtype=torch.bfloat16, device=m.convf1.weight.device)
+            self.wd[0, :, :54] = m.convc1.ffn2[2].weight.detach().reshape(256, 54).to(torch.bfloat16)
             self.wf1 = torch.zeros(1, 128, 128, dtype=torch.bfloat16, device=m.convf1.weight.device)
             self.wf1[0, :, :98] = m.convf1.weight.detach().reshape(128, 98).to(torch.bfloat16)   # column = c*49 + ih*7 + iw
             self.bf1 = _b16(m.convf1.bias).contiguous()
@@ -194,7 +196,7 @@ class MotionEncoder:
         feat = torch.empty(B, 128, H, W, dtype=torch.float32, device=dev)
         mhs_out = torch.empty(B, 64, H, W, dtype=torch.bfloat16, device=dev)
         _lib.check(self.lib.ppm_motion_encoder(level0, (lk_flow if lk_flow is not None else flow32).data_ptr(), corr_ptr, W2,
-                                               wa.data_ptr(), wb.data_ptr(), self.wf1.data_ptr(), self.bf1.data_ptr(),
+                                               wa.data_ptr(), wb.data_ptr(), self.wd.data_ptr(), self.wf1.data_ptr(), self.bf1.data_ptr(),
                                                mhs.data_ptr(), _lib.dtype_code(mhs), self.wc2.data_ptr(),
                                                self.bc2.data_ptr(), self.wf2.data_ptr(), self.bf2.data_ptr(),
                                                self.wfin.data_ptr(), self.bfin.data_ptr(), B, H, W, ws.data_ptr(),

@@ -153,7 +153,7 @@ def test_no_write_outside_outputs(env):
     wa, wb = impl.front._params()
     c32 = corr.float().contiguous()
     _lib.check(impl.lib.ppm_motion_encoder(None, flow.data_ptr(), c32.data_ptr(), 0, wa.data_ptr(), wb.data_ptr(),
-                                           impl.wf1.data_ptr(), impl.bf1.data_ptr(), mhs.data_ptr(), _lib.dtype_code(mhs),
+                                           impl.wd.data_ptr(), impl.wf1.data_ptr(), impl.bf1.data_ptr(), mhs.data_ptr(), _lib.dtype_code(mhs),
                                            impl.wc2.data_ptr(), impl.bc2.data_ptr(), impl.wf2.data_ptr(),
                                            impl.bf2.data_ptr(), impl.wfin.data_ptr(), impl.bfin.data_ptr(), B, H, W,
                                            ws.data_ptr() + G, n.value, feat.data_ptr() + G * 4, hid.data_ptr() + G * 2,
@@ -173,7 +173,7 @@ def test_rejects_bad_arguments(env):
     lib = P.MotionEncoder(enc).lib
     buf = torch.zeros(1024, device="cuda")
     p = buf.data_ptr()
-    rc = lib.ppm_motion_encoder(None, p, p, 0, p, p, p, p, p, 0, p, p, p, p, p, p, 1, 4, 4, p, 16, p, p, None)
+    rc = lib.ppm_motion_encoder(None, p, p, 0, p, p, p, p, p, p, 0, p, p, p, p, p, p, 1, 4, 4, p, 16, p, p, None)
     assert rc != 0 and "workspace" in lib.ppm_last_error().decode()
-    rc = lib.ppm_motion_encoder(None, p, p, 0, p, p, None, p, p, 0, p, p, p, p, p, p, 1, 4, 4, p, 1 << 20, p, p, None)
+    rc = lib.ppm_motion_encoder(None, p, p, 0, p, p, p, None, p, p, 0, p, p, p, p, p, p, 1, 4, 4, p, 1 << 20, p, p, None)
     assert rc != 0 and "null" in lib.ppm_last_error().decode()
