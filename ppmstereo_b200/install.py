@@ -39,8 +39,8 @@ def _inference_only(inp, *params):
 # (scripts/small_clip_probe.py, BASELINE configs[0] size, 5 x 320 x 512, iters 10): eager 76 ms per forward, graph 91 ms
 # (12 frames: 130 vs 157 ms), with spikes to 2x when the allocator recycles the capture pools -- capturing and
 # instantiating a ~400-node graph per (window, level) costs more than 4-19 replays save, and at 720p the device is the
-# bound anyway (device time = wall time).  cuDNN may also pick another convolution algorithm under capture, so replayed
-# results equal the eager ones only to rounding (bit-identical at 320 x 512, 1e-4 px apart at 64 x 256).
+# bound anyway (device time = wall time).  Replayed results are bit-identical to the eager loop's (the small deviations
+# seen earlier in round 2 were a descriptor-cache bug in ppm_memory_attend, fixed).
 GRAPH = {"mode": "never"}           # "never" (default) | "auto" | "always"   (ppmstereo_b200.install(..., graph=...))
 GRAPH_MAX_POSITIONS = 400_000
 GRAPH_STATS = {"captured": 0, "replayed": 0, "eager": 0}
