@@ -176,6 +176,61 @@ __global__ void __launch_bounds__(256) pack_rows_kernel(const T* __restrict__ sr
   }
 }
 
+// Modulated keys, organised by SOURCE frame: K'[(b*T + i)*Kp + n][p][c] = bf16(key[b, c, j, p] * s_in + pe[j][c]) with
+// j = picked[b, i, n].  A CTA stages one [128 channels][64 pixels] slab of key frame j ONCE (128-byte row reads for bf16)
+// and writes it for every (i, n) that picked j -- each key frame is read once instead of once per pick (x Kp on average),
+// and every store is a 16-byte piece of a 256-byte row.  Same arithmetic as pack_rows_kernel<T, 1> (separate fp32
+// multiply and add, one rounding).  Slots with picked < 0 (T < top_k) are zero-filled by the CTAs of frame 0.
+template <typename T>
+__global__ void __launch_bounds__(256) pack_key_kernel(const T* __restrict__ src, long long sb, long long sc, long long st,
+                                                       const float* __restrict__ pe, const int32_t* __restrict__ picked,
+                                                       const float* __restrict__ score_norm, int Tn, int Kp, int hw,
+                                                       __nv_bfloat16* __restrict__ dst) {
+  __shared__ float tile[128][65];
+  __shared__ float s_pe[128];
+  const int p0 = blockIdx.x * 64;
+  const int bb = blockIdx.y / Tn, j = blockIdx.y % Tn;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int32_t* pk = picked + static_cast<long long>(bb) * Tn * Kp;
+  bool any = false;
+  for (int e = lane; e < Tn * Kp; e += 32) { const int v = pk[e]; any |= (v == j) || (j == 0 && v < 0); }
+  if (!__any_sync(0xffffffffu, any)) return;       // nobody picked this frame (every warp sees the same answer)
+  const T* base = src + bb * sb + j * st + p0;
+  #pragma unroll 4
+  for (int k = 0; k < 16; ++k) {
+    const int c = k * 8 + w;
+    tile[c][lane] = (p0 + lane < hw) ? ld_as_float(base + c * sc + lane) : 0.f;
+    tile[c][lane + 32] = (p0 + lane + 32 < hw) ? ld_as_float(base + c * sc + lane + 32) : 0.f;
+  }
+  if (threadIdx.x < 128) s_pe[threadIdx.x] = __ldg(pe + j * 128 + threadIdx.x);
+  __syncthreads();
+  // a warp covers 8 pixels x 4 channel groups: shared-memory bank = (channel + pixel) % 32 is distinct for all 32 lanes,
+  // and each pixel row gets a 64-byte (two full sectors) piece per store instruction
+  const int cg = ((lane & 3) + 4 * (w & 3)) * 8, pr = (w >> 2) * 8 + (lane >> 2);
+  for (int e = 0; e < Tn * Kp; ++e) {
+    const int v = pk[e];
+    const bool zero = v < 0 && j == 0;
+    if (v != j && !zero) continue;
+    const long long item = static_cast<long long>(bb) * Tn * Kp + e;
+    const float s = zero ? 0.f : __ldg(score_norm + item);
+    __nv_bfloat16* out = dst + (item * hw + p0) * 128;
+    #pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int px = q * 16 + pr;
+      if (p0 + px >= hw) continue;
+      uint4 o;
+      if (zero) o = make_uint4(0u, 0u, 0u, 0u);
+      else {
+        float f[8];
+        #pragma unroll
+        for (int u = 0; u < 8; ++u) f[u] = __fadd_rn(__fmul_rn(tile[cg + u][px], s), s_pe[cg + u]);
+        o.x = pack_bf16x2(f[0], f[1]); o.y = pack_bf16x2(f[2], f[3]); o.z = pack_bf16x2(f[4], f[5]); o.w = pack_bf16x2(f[6], f[7]);
+      }
+      *reinterpret_cast<uint4*>(out + px * 128 + cg) = o;
+    }
+  }
+}
+
 // V[(b*T+t), c, p_pad] = bf16(value[b,c,t,p]); pad columns zeroed.
 template <typename T>
 __global__ void __launch_bounds__(256) pack_value_kernel(const T* __restrict__ src, long long sb, long long sc,
@@ -325,16 +380,17 @@ extern "C" int ppm_pack_key(const void* key, int src_dtype, int64_t sb, int64_t 
                             void* k_out, void* stream) {
   if (int rc = check_pack("ppm_pack_key", key, src_dtype, b, T, hw, k_out)) return rc;
   PPM_CHECK(pe && picked && score_norm && Kp > 0, PPM_ERR_ARG, "ppm_pack_key: null pointer or bad Kp");
-  PPM_CHECK(b * T * Kp <= 65535, PPM_ERR_UNSUPPORTED, "ppm_pack_key: b*T*Kp > 65535");
-  dim3 grid((hw + 31) / 32, b * T * Kp);
+  PPM_CHECK(b * T <= 65535, PPM_ERR_UNSUPPORTED, "ppm_pack_key: b*T > 65535");
+  PPM_CHECK((reinterpret_cast<uintptr_t>(k_out) & 15) == 0, PPM_ERR_ARG, "ppm_pack_key: k_out must be 16-byte aligned");
+  dim3 grid((hw + 63) / 64, b * T);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   auto* d = static_cast<__nv_bfloat16*>(k_out);
   if (src_dtype == PPM_BF16)
-    pack_rows_kernel<__nv_bfloat16, 1><<<grid, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(key), sb, sc, st, pe,
-                                                            picked, score_norm, T, Kp, hw, d);
+    pack_key_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(key), sb, sc, st, pe, picked,
+                                                        score_norm, T, Kp, hw, d);
   else
-    pack_rows_kernel<float, 1><<<grid, 256, 0, s>>>(static_cast<const float*>(key), sb, sc, st, pe, picked,
-                                                    score_norm, T, Kp, hw, d);
+    pack_key_kernel<float><<<grid, 256, 0, s>>>(static_cast<const float*>(key), sb, sc, st, pe, picked, score_norm, T, Kp,
+                                                hw, d);
   PPM_CUDA(cudaGetLastError());
   return PPM_OK;
 }

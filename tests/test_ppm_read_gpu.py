@@ -311,6 +311,39 @@ def test_frame_major_bf16_value_is_used_in_place(P, shape):
     assert torch.equal(outs[0][0], outs[1][0])
 
 
+@pytest.mark.parametrize("shape", [(1, 6, 8, 16), (2, 7, 5, 13), (1, 3, 9, 9), (1, 20, 23, 40)])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_modulated_key_pack_equals_torch_op_sequence(P, shape, dtype):
+    """ppm_pack_key (one staged slab per SOURCE frame, written once per pick) against the reference's literal ops run by
+    torch on the GPU: ``(key_j * s + pe_j).to(bf16)`` (ppmstereo.py:541-548) -- bit-identical, incl. ragged 64-pixel
+    tiles, batch 2, frames nobody picked, a frame picked by every query, and zero rows for unused slots (T < top_k)."""
+    b, T, h, w = shape
+    hw, K = h * w, 5
+    g = torch.Generator(device="cuda").manual_seed(T * h + w)
+    q = torch.randn(b, 128, T, h, w, generator=g, device="cuda").to(dtype)
+    k = torch.randn(b, 128, T, h, w, generator=g, device="cuda").to(dtype)
+    mem = P.PPMMemory(q, k, None, top_k=K)
+    sim = torch.rand(b, 1, T, T, generator=g, device="cuda")
+    sim[:, :, :, 0] += 5.0                                                     # frame 0 is in every pick
+    mem.pick(sim, torch.ones(b, 1, T, T, device="cuda"), torch.rand(b * T, 1, h, w, generator=g, device="cuda"))
+    mem.pack_kv(torch.randn(b, 128, T, h, w, generator=g, device="cuda"))
+    torch.cuda.synchronize()
+    got = mem.k_packed.view(b, T, K, hw, 128)
+    pe = P.temporal_pe_table(T, 128, "cuda")
+    picked, score = mem.picked.view(b, T, K).long(), mem.score_norm.view(b, T, K)
+    kk = k.float().reshape(b, 128, T, hw)
+    for bb in range(b):
+        for i in range(T):
+            for n in range(K):
+                j = int(picked[bb, i, n])
+                if j < 0:
+                    assert n >= T and not bool(got[bb, i, n].any())
+                    continue
+                want = (kk[bb, :, j].t() * score[bb, i, n] + pe[j]).to(torch.bfloat16)     # (hw, 128)
+                assert torch.equal(got[bb, i, n], want), (bb, i, n, j)
+    assert int((picked == 0).sum()) == b * T                                   # frame 0: picked by every query frame
+
+
 def test_value_operand_at_many_addresses_with_resident_query_and_key(P):
     """Regression: the library keeps the TMA descriptors of recent operands in a 16-slot round-robin cache.  A value
     operand at a NEW address (every to_v output inside a fresh CUDA-graph pool, every allocator miss) with the query
