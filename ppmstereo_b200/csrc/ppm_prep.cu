@@ -129,42 +129,24 @@ __global__ void __launch_bounds__(256) qam_pick_kernel(const float* __restrict__
 }
 
 // ------------------------------------------------------------------ packing
-// Transposes a [128 channels][32 pixels] slab (pixels contiguous in the NCHW source) into
-// [32 pixels][128 channels] bf16 rows.  MODE 0: + pe (query).  MODE 1: * s + pe (modulated key).
-template <typename T, int MODE>
+// Query operand: transposes a [128 channels][32 pixels] slab (pixels contiguous in the NCHW source) into
+// [32 pixels][128 channels] bf16 rows, + pe (once per level; the per-iteration key operand has its own kernel below).
+template <typename T>
 __global__ void __launch_bounds__(256) pack_rows_kernel(const T* __restrict__ src, long long sb, long long sc,
-                                                        long long st, const float* __restrict__ pe,
-                                                        const int32_t* __restrict__ picked,
-                                                        const float* __restrict__ score_norm, int Tn, int Kp,
-                                                        int hw, __nv_bfloat16* __restrict__ dst) {
+                                                        long long st, const float* __restrict__ pe, int Tn, int hw,
+                                                        __nv_bfloat16* __restrict__ dst) {
   __shared__ float tile[128][33];
   const int p0 = blockIdx.x * 32;
-  const int item = blockIdx.y;                    // MODE 0: b*T + t ; MODE 1: (b*T + i)*Kp + n
-  int bb, t;
-  float s = 1.f;
-  if (MODE == 0) { bb = item / Tn; t = item % Tn; }
-  else {
-    bb = item / (Tn * Kp);
-    t = picked[item];
-    s = score_norm[item];
-  }
+  const int item = blockIdx.y;                    // b*T + t
+  const int bb = item / Tn, t = item % Tn;
   __nv_bfloat16* out = dst + (static_cast<long long>(item) * hw + p0) * 128;
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  if (t < 0) {                                    // unused slot (T < top_k): zero rows
-    for (int e = threadIdx.x; e < 32 * 64; e += 256)
-      if (p0 + e / 64 < hw) reinterpret_cast<uint32_t*>(out)[e] = 0u;
-    return;
-  }
   const T* base = src + bb * sb + t * st + p0;
   #pragma unroll
   for (int k = 0; k < 16; ++k) {
     const int c = k * 8 + w;
     float v = 0.f;
-    if (p0 + lane < hw) {
-      v = ld_as_float(base + c * sc + lane);
-      const float e = __ldg(pe + t * 128 + c);
-      v = MODE == 0 ? __fadd_rn(v, e) : __fadd_rn(__fmul_rn(v, s), e);
-    }
+    if (p0 + lane < hw) v = __fadd_rn(ld_as_float(base + c * sc + lane), __ldg(pe + t * 128 + c));
     tile[c][lane] = v;
   }
   __syncthreads();
@@ -179,8 +161,8 @@ __global__ void __launch_bounds__(256) pack_rows_kernel(const T* __restrict__ sr
 // Modulated keys, organised by SOURCE frame: K'[(b*T + i)*Kp + n][p][c] = bf16(key[b, c, j, p] * s_in + pe[j][c]) with
 // j = picked[b, i, n].  A CTA stages one [128 channels][64 pixels] slab of key frame j ONCE (128-byte row reads for bf16)
 // and writes it for every (i, n) that picked j -- each key frame is read once instead of once per pick (x Kp on average),
-// and every store is a 16-byte piece of a 256-byte row.  Same arithmetic as pack_rows_kernel<T, 1> (separate fp32
-// multiply and add, one rounding).  Slots with picked < 0 (T < top_k) are zero-filled by the CTAs of frame 0.
+// and every store is a 16-byte piece of a 256-byte row.  Arithmetic: separate fp32 multiply and add, one rounding (what
+// torch's `key * s + pe` followed by `.to(bf16)` does).  Slots with picked < 0 (T < top_k) are zero-filled by the CTAs of frame 0.
 template <typename T>
 __global__ void __launch_bounds__(256) pack_key_kernel(const T* __restrict__ src, long long sb, long long sc, long long st,
                                                        const float* __restrict__ pe, const int32_t* __restrict__ picked,
@@ -366,11 +348,9 @@ extern "C" int ppm_pack_query(const void* query, int src_dtype, int64_t sb, int6
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   auto* d = static_cast<__nv_bfloat16*>(q_out);
   if (src_dtype == PPM_BF16)
-    pack_rows_kernel<__nv_bfloat16, 0><<<grid, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(query), sb, sc, st, pe,
-                                                            nullptr, nullptr, T, 1, hw, d);
+    pack_rows_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(query), sb, sc, st, pe, T, hw, d);
   else
-    pack_rows_kernel<float, 0><<<grid, 256, 0, s>>>(static_cast<const float*>(query), sb, sc, st, pe, nullptr,
-                                                    nullptr, T, 1, hw, d);
+    pack_rows_kernel<float><<<grid, 256, 0, s>>>(static_cast<const float*>(query), sb, sc, st, pe, T, hw, d);
   PPM_CUDA(cudaGetLastError());
   return PPM_OK;
 }
