@@ -162,15 +162,14 @@ class MotionEncoder:
         wa, wb = self.front._params()
         self._params()
         flow32 = flow.detach().float().contiguous()
-        level0 = corr_ptr = lk_flow = None
+        level0 = corr_ptr = None
         W2 = 0
         keep = None
         if isinstance(corr, LookupRequest):
             blk = corr.block
-            if getattr(blk, "_l0_only", False):
+            if getattr(blk, "_l0_only", False) and corr.flow is flow:      # the entry point has ONE flow: lookup and convf1
                 keep = blk._level0
                 level0, W2 = keep.data_ptr(), blk._w2
-                lk_flow = flow32 if corr.flow is flow else corr.flow.detach().float().contiguous()
             else:
                 corr = corr.materialise()
         if level0 is None:
@@ -195,7 +194,7 @@ class MotionEncoder:
             ws = self._ws[key] = torch.empty(n.value, dtype=torch.uint8, device=dev)
         feat = torch.empty(B, 128, H, W, dtype=torch.float32, device=dev)
         mhs_out = torch.empty(B, 64, H, W, dtype=torch.bfloat16, device=dev)
-        _lib.check(self.lib.ppm_motion_encoder(level0, (lk_flow if lk_flow is not None else flow32).data_ptr(), corr_ptr, W2,
+        _lib.check(self.lib.ppm_motion_encoder(level0, flow32.data_ptr(), corr_ptr, W2,
                                                wa.data_ptr(), wb.data_ptr(), self.wd.data_ptr(), self.wf1.data_ptr(), self.bf1.data_ptr(),
                                                mhs.data_ptr(), _lib.dtype_code(mhs), self.wc2.data_ptr(),
                                                self.bc2.data_ptr(), self.wf2.data_ptr(), self.bf2.data_ptr(),
