@@ -33,7 +33,8 @@
 
 namespace ppm {
 
-constexpr int kGrThreads = 320;                 // TMA warp, MMA warp, 8 epilogue warps
+constexpr int kGrEpiWarps = 16;                 // 4 TMEM lane quarters x 4 column groups
+constexpr int kGrThreads = 64 + 32 * kGrEpiWarps;   // TMA warp, MMA warp, epilogue warps (576: <= 112 registers each)
 constexpr int kGrM = 128;
 constexpr int kGrKC = 64;                       // channels per K step (128 B of bf16)
 constexpr int kGrABytes = kGrM * kGrKC * 2;     // 16 KB
@@ -207,7 +208,7 @@ gru_gemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constan
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kGrStages; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(&bar_acc_full[a], 1); mbar_init(&bar_acc_empty[a], 8); }
+    for (int a = 0; a < 2; ++a) { mbar_init(&bar_acc_full[a], 1); mbar_init(&bar_acc_empty[a], kGrEpiWarps); }
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc<kGrTmemCols>(&tmem_slot);
@@ -280,11 +281,13 @@ gru_gemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constan
       __syncwarp();
     }
   } else {
-    // ------------------------------------------------------------------------------ epilogue (8 warps)
+    // ------------------------------------------------------------------------------ epilogue (16 warps)
+    // The K = 2560 GEMMs are paced by this code, not by the MMAs (sigmoid / tanh / erf evaluated exactly, state and gate
+    // loads): four warps per scheduler, each owning a quarter of the N columns in 16-column pieces, hide that latency.
     const int quarter = warp & 3;                         // TMEM lanes 32*quarter .. +31 (hardware rule: warp_id % 4)
-    const int half = (warp - 2) >> 2;                     // which half of the N columns
+    const int half = (warp - 2) >> 2;                     // which quarter of the N columns
     const int row = quarter * 32 + lane;
-    const int cols_per_warp = p.N >> 1;
+    const int cols_per_warp = p.N >> 2;                   // 16, 32, 48 or 64
     const int HW = p.H * p.W;
     int i = 0;
     for (long long tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++i) {
@@ -297,25 +300,24 @@ gru_gemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constan
       mbar_wait(&bar_acc_full[buf], use & 1);
       tc_fence_after();
       const uint32_t t_addr = tmem + (static_cast<uint32_t>(quarter * 32) << 16) + buf * 256 + half * cols_per_warp;
-      const int n_chunks_e = cols_per_warp >> 5;
+      const int n_chunks_e = cols_per_warp >> 4;
       for (int c = 0; c < n_chunks_e; ++c) {
-        uint32_t acc[32];
-        tmem_ld_x32(t_addr + c * 32, acc);
-        const int col0 = half * cols_per_warp + c * 32;   // column of acc[0] in the GEMM's N
+        uint32_t acc[16];
+        tmem_ld_x16(t_addr + c * 16, acc);
+        const int col0 = half * cols_per_warp + c * 16;   // column of acc[0] in the GEMM's N
         int mode = p.mode, ch0 = col0;                    // ch0: channel inside the 128-wide gate tensors
         if (mode == GR_EPI_ZR) { mode = col0 < kGrHidden ? GR_EPI_Z : GR_EPI_R; ch0 = col0 & (kGrHidden - 1); }
-        // the chunk's state / gate operands are requested before the accumulator wait: with two epilogue warps per
-        // scheduler nothing else hides their latency (ncu: the epilogue, not the MMAs, paced the K = 2560 GEMMs)
-        float4 hreg[8];
-        uint4 zreg[4];
+        // the chunk's state / gate operands are requested before the accumulator wait
+        float4 hreg[4];
+        uint4 zreg[2];
         if (valid && (mode == GR_EPI_R || mode == GR_EPI_Q)) {
           const float4* hp = reinterpret_cast<const float4*>(p.hstate + pos * kGrHidden + ch0);
           #pragma unroll
-          for (int e = 0; e < 8; ++e) hreg[e] = hp[e];
+          for (int e = 0; e < 4; ++e) hreg[e] = hp[e];
           if (mode == GR_EPI_Q) {
             const uint4* zp = reinterpret_cast<const uint4*>(p.zbuf + pos * kGrHidden + ch0);
             #pragma unroll
-            for (int e = 0; e < 4; ++e) zreg[e] = zp[e];
+            for (int e = 0; e < 2; ++e) zreg[e] = zp[e];
           }
         }
         tmem_ld_wait();
@@ -326,7 +328,7 @@ gru_gemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constan
         }
         if (!valid) continue;
         #pragma unroll
-        for (int g = 0; g < 4; ++g) {                     // 4 groups of 8 channels = one 16-byte store each
+        for (int g = 0; g < 2; ++g) {                     // 2 groups of 8 channels = one 16-byte store each
           float v[8];
           #pragma unroll
           for (int e = 0; e < 8; ++e)
