@@ -76,6 +76,35 @@ def test_argument_errors_are_reported(lib):
     assert lib.ppm_pack_bytes(1, 1, 1, 5, ctypes.byref(q), None, ctypes.byref(v)) == 0 and v.value == 128 * 8 * 2
 
 
+def test_update_iteration_entries_check_arguments_and_size_their_workspaces(lib):
+    """K5 / K5c / K7 / K8: workspace formulas (host-only functions) and the checks that fire before any CUDA call."""
+    n = ctypes.c_size_t()
+    P = 2 * 3 * 5 * 7
+    assert lib.ppm_sepconv_gru3d_workspace(2, 3, 5, 7, ctypes.byref(n)) == 0
+    assert n.value == P * ((384 + 128 + 128 + 128 + 256) * 2 + 128 * 4)
+    assert lib.ppm_update_block3d_workspace(2, 3, 5, 7, ctypes.byref(n)) == 0 and n.value > P * 2560
+    assert lib.ppm_motion_encoder_workspace(6, 5, 7, ctypes.byref(n)) == 0
+    assert n.value == 6 * 5 * 7 * (36 * 4 + (256 + 128 + 320) * 2)
+    assert lib.ppm_value_uncertainty_workspace(6, 5, 7, ctypes.byref(n)) == 0 and n.value == 6 * 5 * 7 * 4 * 128 * 2
+    for fn in (lib.ppm_motion_encoder_workspace, lib.ppm_value_uncertainty_workspace):
+        assert fn(0, 5, 7, ctypes.byref(n)) == 1 and b"bad argument" in lib.ppm_last_error()
+        assert fn(1, 5, 7, None) == 1
+    buf = ctypes.create_string_buffer(4096)
+    a = (ctypes.addressof(buf) + 255) & ~255
+    # motion encoder: null weight, then a workspace that is too small
+    rc = lib.ppm_motion_encoder(None, a, a, 0, a, a, a, None, a, a, 0, a, a, a, a, a, a, 1, 4, 4, a, 1 << 20, a, a, None)
+    assert rc == 1 and b"null" in lib.ppm_last_error()
+    rc = lib.ppm_motion_encoder(None, a, a, 0, a, a, a, a, a, a, 0, a, a, a, a, a, a, 1, 4, 4, a, 16, a, a, None)
+    assert rc == 1 and b"workspace of 16 bytes" in lib.ppm_last_error()
+    rc = lib.ppm_motion_encoder(None, a, a, 0, a, a, a, a, a, a, 7, a, a, a, a, a, a, 1, 4, 4, a, 1 << 20, a, a, None)
+    assert rc == 1 and b"dtype" in lib.ppm_last_error()
+    # value + uncertainty: bad dtype, misaligned workspace
+    rc = lib.ppm_value_uncertainty(a, 5, a, 0, a, a, a, a, a, a, 1, 4, 4, a, 1 << 20, a, a, None)
+    assert rc == 1 and b"dtype" in lib.ppm_last_error()
+    rc = lib.ppm_value_uncertainty(a, 0, a, 0, a, a, a, a, a, a, 1, 4, 4, a + 8, 1 << 20, a, a, None)
+    assert rc == 1 and b"256-byte aligned" in lib.ppm_last_error()
+
+
 def test_cpu_tensors_are_rejected():
     f = torch.zeros(1, 8, 2, 16)
     with pytest.raises(RuntimeError, match="CUDA"):
