@@ -13,6 +13,6 @@ ncu --set full --clock-control none --import-source on -k regex:corr_lookup -s 2
 echo "lookup rc=$?"
 ncu --set full --clock-control none --import-source on -k regex:corr_build -s 2 -c 1 -f -o gpurun_out/prof_build $CMD > gpurun_out/ncu_build.log 2>&1
 echo "build rc=$?"
-ncu --set full --clock-control none --import-source on -k regex:pack_rows_kernel -s 30 -c 1 -f -o gpurun_out/prof_pack $CMD > gpurun_out/ncu_pack.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:pack_key_kernel -s 30 -c 1 -f -o gpurun_out/prof_pack $CMD > gpurun_out/ncu_pack.log 2>&1
 echo "pack rc=$?"
 ls -la gpurun_out/*.ncu-rep
