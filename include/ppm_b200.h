@@ -285,7 +285,9 @@ PPM_API int ppm_sepconv_gru3d_state_offset(int b, int T, int H, int W, size_t* o
  * Conv3d (128 -> 256 -> 2) in the bf16 autocast regime (each conv = bf16(bf16(acc) + bias), relu in bf16), on the K5
  * shifted-GEMM kernel.  x (b,128,T,H,W) indexed x[b*sb + c*sc + t*st + y*W + x], fp32 or bf16 -- or x_cl != NULL: the same
  * tensor already as bf16 channels-last [b*T*H*W][128] (then x may be NULL).  w1: bf16 [27][256][128]; b1: fp32 [256];
- * w2: bf16 [27][64][256] with rows 2..63 zero; b2: fp32 [64] (entries 2..63 ignored).  Tap order (it*3 + ih)*3 + iw.
+ * w2: bf16 [1][64][256], row tap*2 + c = conv2.weight[c, :, tap] (54 rows, rows 54..63 zero): the second layer contracts
+ * the 256 channels once per position for all 27 x 2 (offset, output) pairs and then adds the 27 shifted fp32 planes;
+ * b2: fp32 [64] (entries 2..63 ignored).  Tap order (it*3 + ih)*3 + iw.
  * workspace: ppm_flow_head3d_workspace bytes, 256-byte aligned.  out: (b,2,T,H,W) contiguous, out_dtype. */
 PPM_API int ppm_flow_head3d_workspace(int b, int T, int H, int W, size_t* bytes);
 PPM_API int ppm_flow_head3d(const void* x, int x_dtype, int64_t xsb, int64_t xsc, int64_t xst, const void* x_cl,

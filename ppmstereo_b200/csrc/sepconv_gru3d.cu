@@ -50,7 +50,8 @@ enum GruEpilogue : int {
   GR_EPI_Q = 4,        // q = bf16(tanh(bf16(acc + bias))); h = bf16(bf16(bf16(1-z)*h) + bf16(z*q)) -> hbuf (+ NCTHW out)
   GR_EPI_RELU = 5,     // out = relu(c)   -> dst0 [P, dst_ld] at channel dst_c0 (channels-last bf16) and / or NCTHW `out`
   GR_EPI_LINEAR = 6,   // out = c         -> likewise          (c = bf16(bf16(acc) + bias) in every mode)
-  GR_EPI_SIGMOID = 7   // out = bf16(sigmoid(c))  -> likewise
+  GR_EPI_SIGMOID = 7,  // out = bf16(sigmoid(c))  -> likewise
+  GR_EPI_RAW32 = 8     // out = acc (fp32, no bias, no rounding) -> strided `out` only (partial sums for a later pass)
 };
 
 struct GruGemmParams {
@@ -332,7 +333,8 @@ gru_gemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constan
           float v[8];
           #pragma unroll
           for (int e = 0; e < 8; ++e)
-            v[e] = bf16_round_f(bf16_round_f(__uint_as_float(acc[g * 8 + e])) + s_bias[col0 + g * 8 + e]);
+            v[e] = mode == GR_EPI_RAW32 ? __uint_as_float(acc[g * 8 + e])
+                                        : bf16_round_f(bf16_round_f(__uint_as_float(acc[g * 8 + e])) + s_bias[col0 + g * 8 + e]);
           const int ch = ch0 + g * 8;
           if (mode == GR_EPI_GELU) {
             #pragma unroll
@@ -350,7 +352,7 @@ gru_gemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constan
             #pragma unroll
             for (int e = 0; e < 8; ++e) v[e] = __fmul_rn(bf16_round_f(gr_sigmoid(v[e])), h[e]);
             *reinterpret_cast<uint4*>(p.dst1 + pos * kGrHidden + ch) = gr_pack8(v);
-          } else if (mode == GR_EPI_RELU || mode == GR_EPI_LINEAR || mode == GR_EPI_SIGMOID) {
+          } else if (mode == GR_EPI_RELU || mode == GR_EPI_LINEAR || mode == GR_EPI_SIGMOID || mode == GR_EPI_RAW32) {
             if (col0 + g * 8 < p.n_valid) {
               if (mode == GR_EPI_RELU) {
                 #pragma unroll
@@ -358,7 +360,7 @@ gru_gemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constan
               } else if (mode == GR_EPI_SIGMOID) {
                 #pragma unroll
                 for (int e = 0; e < 8; ++e) v[e] = bf16_round_f(gr_sigmoid(v[e]));
-              } else {
+              } else if (mode == GR_EPI_LINEAR) {
                 #pragma unroll
                 for (int e = 0; e < 8; ++e) v[e] *= p.out_scale;
               }
@@ -434,6 +436,58 @@ gru_gemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constan
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc<kGrTmemCols>(tmem);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ flow head, second layer
+// FlowHead3D.conv2 is 256 -> 2 channels over a 3 x 3 x 3 footprint: as a shifted GEMM it would be 27 x 4 K-steps on an N
+// tile (64 is the narrowest) that is 97 % padding.  Instead the contraction over the 256 channels runs ONCE per position for
+// all 27 x 2 (offset, output) pairs -- a plain K = 256, N = 54 GEMM whose fp32 results are stored as 54 planes --
+//   Y[tap*2 + c][p] = sum_ci W2[c, ci, tap] * hd[p, ci]
+// and this kernel adds the 27 shifted planes per output: out[p, c] = bf16(bf16(sum_tap Y[tap*2 + c][p + off(tap)]) + b[c]),
+// positions outside the volume contributing nothing (the convolution's zero padding).  fp32 throughout until cuDNN's two
+// roundings; the planes are read along x, coalesced.
+__global__ void __launch_bounds__(256) flow_head_gather_kernel(const float* __restrict__ Y, const float* __restrict__ bias,
+                                                               int b, int T, int H, int W, void* __restrict__ out,
+                                                               long long out_sb, long long out_sc, long long out_st,
+                                                               int out_dtype) {
+  const long long P = static_cast<long long>(b) * T * H * W;
+  const long long p = static_cast<long long>(blockIdx.x) * 256 + threadIdx.x;
+  if (p >= P) return;
+  const int x = static_cast<int>(p % W);
+  long long r = p / W;
+  const int y = static_cast<int>(r % H); r /= H;
+  const int t = static_cast<int>(r % T);
+  const int bb = static_cast<int>(r / T);
+  float s0 = 0.f, s1 = 0.f;
+  #pragma unroll
+  for (int it = 0; it < 3; ++it) {
+    const int tt = t + it - 1;
+    if (tt < 0 || tt >= T) continue;
+    #pragma unroll
+    for (int ih = 0; ih < 3; ++ih) {
+      const int yy = y + ih - 1;
+      if (yy < 0 || yy >= H) continue;
+      #pragma unroll
+      for (int iw = 0; iw < 3; ++iw) {
+        const int xx = x + iw - 1;
+        if (xx < 0 || xx >= W) continue;
+        const int tap = (it * 3 + ih) * 3 + iw;
+        const long long q = ((static_cast<long long>(bb) * T + tt) * H + yy) * W + xx;
+        s0 = __fadd_rn(s0, __ldg(Y + (2 * tap) * P + q));
+        s1 = __fadd_rn(s1, __ldg(Y + (2 * tap + 1) * P + q));
+      }
+    }
+  }
+  const float o0 = bf16_round_f(bf16_round_f(s0) + __ldg(bias));
+  const float o1 = bf16_round_f(bf16_round_f(s1) + __ldg(bias + 1));
+  const long long o = bb * out_sb + t * out_st + static_cast<long long>(y) * W + x;
+  if (out_dtype == PPM_BF16) {
+    static_cast<__nv_bfloat16*>(out)[o] = __float2bfloat16_rn(o0);
+    static_cast<__nv_bfloat16*>(out)[o + out_sc] = __float2bfloat16_rn(o1);
+  } else {
+    static_cast<float*>(out)[o] = o0;
+    static_cast<float*>(out)[o + out_sc] = o1;
   }
 }
 
@@ -560,23 +614,31 @@ static int gru_unit(const GruShape& s, __nv_bfloat16* X, __nv_bfloat16* Hb, __nv
 }
 
 // Flow head on a channels-last bf16 state `a_in` [P,128]; Hd = [P,256] scratch.  out strides 0 = contiguous (b,2,T,H,W).
-static int flow_head_unit(const GruShape& s, const __nv_bfloat16* a_in, __nv_bfloat16* Hd, const void* w1, const float* b1,
-                          const void* w2, const float* b2, void* out, int out_dtype, long long out_sb, long long out_sc,
-                          long long out_st, cudaStream_t st) {
+static int flow_head_unit(const GruShape& s, const __nv_bfloat16* a_in, __nv_bfloat16* Hd, float* Y, const void* w1,
+                          const float* b1, const void* w2, const float* b2, void* out, int out_dtype, long long out_sb,
+                          long long out_sc, long long out_st, cudaStream_t st) {
   int rc;
   CUtensorMap mA, mH, mW1, mW2;
   if ((rc = gru_act_map(&mA, a_in, 128, s))) return rc;
   if ((rc = gru_act_map(&mH, Hd, 256, s))) return rc;
   if ((rc = gru_w_map(&mW1, w1, 128, 256, 27))) return rc;
-  if ((rc = gru_w_map(&mW2, w2, 256, 64, 27))) return rc;
+  if ((rc = gru_w_map(&mW2, w2, 256, 64, 1))) return rc;
   GruGemmParams p{};
-  p.kw = 3; p.kh = 3; p.kt = 3; p.out_dtype = out_dtype;
+  p.kw = 3; p.kh = 3; p.kt = 3;
   p.bias = b1; p.N = 256; p.n_valid = 256; p.mode = GR_EPI_RELU; p.seg0_chunks = 2; p.seg0_c0 = 0; p.seg1_chunks = 0;
   p.dst0 = Hd; p.dst_ld = 256; p.dst_c0 = 0; p.out = nullptr;
   if ((rc = gru_launch(mA, mA, mW1, p, s, st))) return rc;
-  p.bias = b2; p.N = 64; p.n_valid = 2; p.mode = GR_EPI_LINEAR; p.seg0_chunks = 4; p.dst0 = nullptr; p.out = out;
-  p.out_sb = out_sb; p.out_sc = out_sc; p.out_st = out_st;
-  return gru_launch(mH, mH, mW2, p, s, st);
+  // conv2 (256 -> 2, 3 x 3 x 3): one K = 256 GEMM for all 27 x 2 (offset, output) pairs -> 54 fp32 planes, then the gather-sum
+  const long long HW = static_cast<long long>(s.H) * s.W;
+  p.kw = 1; p.kh = 1; p.kt = 1;
+  p.bias = b2; p.N = 64; p.n_valid = 54; p.mode = GR_EPI_RAW32; p.seg0_chunks = 4; p.dst0 = nullptr;
+  p.out = Y; p.out_dtype = PPM_F32; p.out_sc = s.P; p.out_sb = HW * s.T; p.out_st = HW;     // planes: Y[j][(b, t, y, x)]
+  if ((rc = gru_launch(mH, mH, mW2, p, s, st))) return rc;
+  if (out_sc == 0) { out_st = HW; out_sc = HW * s.T; out_sb = HW * s.T * 2; }               // contiguous (b, 2, T, H, W)
+  flow_head_gather_kernel<<<static_cast<unsigned>((s.P + 255) / 256), 256, 0, st>>>(Y, b2, s.b, s.T, s.H, s.W, out, out_sb,
+                                                                                    out_sc, out_st, out_dtype);
+  PPM_CUDA(cudaGetLastError());
+  return PPM_OK;
 }
 
 // mask_2d head (ppmtereo_update.py:~905, used at :996): 0.25 * Conv1x1(relu(Conv3x3(net))), 128 -> 256 -> 144, per frame
@@ -690,7 +752,8 @@ extern "C" int ppm_flow_head3d(const void* x, int x_dtype, int64_t xsb, int64_t 
     if (rc) return rc;
     a_in = Xc;
   }
-  return flow_head_unit(s, a_in, Hd, w1, b1, w2, b2, out, out_dtype, 0, 0, 0, st);
+  // the 54 fp32 planes (256 B per position) reuse the Xc region: conv1 has consumed it by the time conv2's GEMM writes
+  return flow_head_unit(s, a_in, Hd, reinterpret_cast<float*>(Xc), w1, b1, w2, b2, out, out_dtype, 0, 0, 0, st);
 }
 
 // ------------------------------------------------------------------------------------------------ whole update block
@@ -756,7 +819,9 @@ extern "C" int ppm_update_block3d(const void* net, int net_dtype, const void* co
   if ((rc = gru_unit(s, X, Hb, RH, Z, G, Hs, gru_weights, gru_biases, net_dtype == PPM_F32 ? 1 : 0, net_out, net_dtype, sb, sc,
                      stt, st)))
     return rc;
-  if ((rc = flow_head_unit(s, Hb, Hd, flow_w1, flow_b1, flow_w2, flow_b2, dflow_out, PPM_BF16, T * 2 * HW, HW, 2 * HW, st)))
+  // (the flow head's 54 fp32 planes go where the GRU's packed input was: the GRU is done with it)
+  if ((rc = flow_head_unit(s, Hb, Hd, reinterpret_cast<float*>(X), flow_w1, flow_b1, flow_w2, flow_b2, dflow_out, PPM_BF16,
+                           T * 2 * HW, HW, 2 * HW, st)))
     return rc;
   return mask_head_unit(s, Hb, Hd, mask_w1, mask_b1, mask_w2, mask_b2, n_mask, mask_out, PPM_BF16,
                         static_cast<long long>(T) * n_mask * HW, HW, static_cast<long long>(n_mask) * HW, st);

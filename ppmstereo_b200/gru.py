@@ -144,8 +144,10 @@ class FlowHead3D:
         if versions != self._versions:
             self.w1 = _pack_weight(c1)                                                   # (27, 256, 128)
             w2 = _pack_weight(c2)                                                        # (27, 2, 256)
-            self.w2 = torch.zeros(w2.shape[0], 64, w2.shape[2], dtype=torch.bfloat16, device=w2.device)
-            self.w2[:, :w2.shape[1]] = w2
+            # second layer: ONE weight tile whose row tap*2 + c is W2[c, :, tap] (54 rows + zero padding): the kernel
+            # contracts the 256 channels once per position for all 27 x 2 (offset, output) pairs, then sums shifted planes
+            self.w2 = torch.zeros(1, 64, w2.shape[2], dtype=torch.bfloat16, device=w2.device)
+            self.w2[0, :54] = w2.reshape(54, w2.shape[2])
             self.b1 = c1.bias.detach().to(torch.bfloat16).float().contiguous()
             self.b2 = torch.zeros(64, device=w2.device)
             self.b2[:w2.shape[1]] = c2.bias.detach().to(torch.bfloat16).float()
